@@ -1,0 +1,164 @@
+/*
+ * lumenos_b200.h -- C ABI of liblumenos_b200.so: the B200 (sm_100a) implementation of lumenos's
+ * server-side homomorphic Ligero prover hot path.  Plain pointers and sizes only; every entry point
+ * names the reference interface (file:line in ChainSafe/lumenos @ 9f33d62) it replaces.  The Go host
+ * keeps keys, encryption, transcript, Merkle tree and wire format, and binds these symbols through cgo
+ * (see INTEGRATION.md for the shim).
+ *
+ * Data conventions (identical to rlwe.Ciphertext.Value[p].Coeffs[limb][j], core/transcript.go:34-35):
+ *   - residues are uint64, NTT domain, NON-Montgomery, canonical [0, q_limb);
+ *   - a ciphertext at level L is the contiguous block  [poly 0..1][limb 0..L][coeff 0..N-1];
+ *   - evaluation keys are NTT + MONTGOMERY form (Lattigo's in-memory form), laid out
+ *     [digit 0..beta-1][component 0..1][limb 0..k+np-1 (Q limbs then P limbs)][coeff].
+ *
+ * Error convention: every function returns 0 on success, a negative lmn_status otherwise, and never
+ * aborts the process (the reference escalates Go errors to panic, fhe/ligero.go:509-512; its cgo
+ * precedent returns int status, vdec/prover.go:220-232).  lmn_last_error() gives the message of the last
+ * failure on the calling thread.
+ *
+ * Threading: a context may be used from several host threads for DISTINCT stores; calls on one context
+ * are serialised internally (the reference runs R and Z inner products from two goroutines,
+ * fhe/ligero.go:231-242 -- use lmn_inner_product2 to fuse them instead).
+ */
+#ifndef LUMENOS_B200_H
+#define LUMENOS_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct lmn_ctx lmn_ctx;     /* device context: moduli, NTT tables, keys, workspace  */
+typedef struct lmn_store lmn_store; /* device-resident array of ciphertexts (ref: LigeroProver{Matrix,EncodedMatrix}, fhe/ligero.go:32-37) */
+typedef struct lmn_plan lmn_plan;   /* compiled butterfly plan of fhe.NTT for one size (ref: fhe/ntt.go:20-281) */
+
+typedef enum lmn_status {
+    LMN_OK = 0,
+    LMN_ERR_INVALID = -1,     /* bad argument / shape / level */
+    LMN_ERR_CUDA = -2,        /* CUDA runtime failure (message has the cudaError string) */
+    LMN_ERR_NOKEY = -3,       /* Galois / ring-switch key not loaded */
+    LMN_ERR_UNSUPPORTED = -4, /* parameter outside what the kernels are instantiated for */
+    LMN_ERR_NOMEM = -5
+} lmn_status;
+
+/* BGV parameters as the host holds them (ref: fhe/bfv.go:121-188 GenerateBGVParamsForNTT -> bgv.Parameters).
+ * psi_q / psi_p are the primitive 2N-th roots of unity the host ring uses, in plain (non-Montgomery) form:
+ * ring.ModExp(subRing.PrimitiveRoot, (q-1)/subRing.NthRoot, q).  The library derives its NTT tables from
+ * them so that its NTT domain is the host's NTT domain. */
+typedef struct lmn_params {
+    uint32_t log_n;          /* ring degree N = 2^log_n (4..16)                         */
+    uint32_t num_q;          /* k: number of Q primes (max level = k-1)                  */
+    uint32_t num_p;          /* number of special primes P (reference: 2)                */
+    const uint64_t *q;       /* [num_q] params.Q()                                       */
+    const uint64_t *p;       /* [num_p] params.P()                                       */
+    const uint64_t *psi_q;   /* [num_q]                                                  */
+    const uint64_t *psi_p;   /* [num_p]                                                  */
+    uint64_t t;              /* plaintext modulus (cmd/server/main.go:22)                */
+    /* hypothesis switches for un-vendored Lattigo behaviours; 0xffffffff = library default */
+    uint32_t scalar_centered;       /* default 1: Evaluator.Mul(ct,uint64) centres the scalar mod t      */
+    uint32_t moddown_round_nearest; /* default 1: ModDown is a rounded division by P                      */
+    uint32_t innersum_rowswap_last; /* default 1: rows==N -> InnerSum(N/2) then row swap                  */
+} lmn_params;
+
+/* ---------------- context ---------------- */
+/* replaces fhe.NewBackendBFV (fhe/bfv.go:22-27): binds parameters to one GPU. device < 0 = current device */
+int lmn_ctx_create(const lmn_params *params, int device, lmn_ctx **out);
+void lmn_ctx_destroy(lmn_ctx *ctx);
+const char *lmn_last_error(void);
+/* run all work of this context on an existing CUDA stream (cudaStream_t); NULL = the context's own stream */
+int lmn_ctx_set_stream(lmn_ctx *ctx, void *cuda_stream);
+int lmn_ctx_synchronize(lmn_ctx *ctx);
+/* number of kernels launched by this context since creation (bench.py's gpu_launches) */
+uint64_t lmn_ctx_launch_count(const lmn_ctx *ctx);
+/* columns processed together per inner-product / rescale batch (workspace = batch * ~(5k+4) limbs) */
+int lmn_ctx_set_batch(lmn_ctx *ctx, uint32_t jobs_per_batch);
+
+/* ---------------- device-resident ciphertext store ---------------- */
+/* replaces []*rlwe.Ciphertext held between Commit and Prove (fhe/ligero.go:118-123) */
+int lmn_store_create(lmn_ctx *ctx, uint32_t n_ct, uint32_t level, lmn_store **out);
+/* wrap caller-owned device memory (n_ct * 2*(level+1)*N uint64), e.g. a torch tensor */
+int lmn_store_wrap(lmn_ctx *ctx, void *device_ptr, uint32_t n_ct, uint32_t level, lmn_store **out);
+void lmn_store_destroy(lmn_store *s);
+uint32_t lmn_store_count(const lmn_store *s);
+uint32_t lmn_store_level(const lmn_store *s);
+void *lmn_store_device_ptr(const lmn_store *s);
+size_t lmn_store_bytes(const lmn_store *s);
+/* bulk copies of whole ciphertexts in the contiguous layout above; host memory may be pageable or pinned */
+int lmn_store_upload(lmn_store *s, uint32_t first, uint32_t count, const uint64_t *host);
+int lmn_store_download(const lmn_store *s, uint32_t first, uint32_t count, uint64_t *host);
+/* per-limb copies: Go's Coeffs is [][]uint64 (one slice per limb), and cgo may not pass pointer-to-pointer */
+int lmn_store_upload_limb(lmn_store *s, uint32_t ct, uint32_t poly, uint32_t limb, const uint64_t *host);
+int lmn_store_download_limb(const lmn_store *s, uint32_t ct, uint32_t poly, uint32_t limb, uint64_t *host);
+/* pinned host staging owned by the library (cudaHostAlloc) */
+int lmn_host_alloc(size_t bytes, void **out);
+void lmn_host_free(void *p);
+
+/* ---------------- Encode eval (fhe/code.go + fhe/ntt.go) ---------------- */
+/* compile the butterfly/twiddle/permutation plan of nttInner(size = cols*rho_inv) for
+ * core.NewPrimeField(t, cols*rho_inv): roots_forward[i] = backend.Field().RootForwardUint64(i)
+ * (core/field.go:45-47), cols*rho_inv entries. */
+int lmn_plan_create(lmn_ctx *ctx, uint32_t cols, uint32_t rho_inv, const uint64_t *roots_forward, lmn_plan **out);
+void lmn_plan_destroy(lmn_plan *plan);
+/* ciphertext-level op counts the plan stands for (ServerBFV.MulCounter analogue, fhe/bfv.go:20,34-46) */
+int lmn_plan_counts(const lmn_plan *plan, uint64_t *adds, uint64_t *subs, uint64_t *muls);
+uint32_t lmn_plan_size(const lmn_plan *plan);
+/* replaces fhe.Encode(matrix, rows, rhoInv, backend) (fhe/code.go:8-34): matrix has `cols` max-level cts;
+ * zero_ct is the host-produced encryption of the zero vector (code.go:15-22, random => must come from the
+ * host); encoded receives cols*rho_inv max-level cts in the order fhe.NTT returns them. */
+int lmn_encode(lmn_ctx *ctx, const lmn_plan *plan, const lmn_store *matrix, const lmn_store *zero_ct,
+               uint32_t zero_idx, lmn_store *encoded);
+/* replaces fhe.NTT(values, size, backend) (fhe/ntt.go:12-17) for len(values) == size == plan size:
+ * out[i] = i-th ciphertext of the returned slice. in and out must be distinct stores. */
+int lmn_ntt(lmn_ctx *ctx, const lmn_plan *plan, const lmn_store *in, lmn_store *out);
+
+/* host-only self-check of the plan compiler (no device): evaluates the compiled plan of size n on a plaintext
+ * vector over Z_t in place, which must reproduce core.NTT (core/ntt.go:3-6) -- the equality the reference's own
+ * TestEncode asserts (fhe/code_test.go:100-116).  counts3 (optional) receives {adds, subs, muls}. */
+int lmn_plan_host_check(uint32_t n, const uint64_t *roots_forward, uint64_t t, uint64_t *values, uint64_t *counts3);
+
+/* ---------------- keys ---------------- */
+/* replaces rlwe.MemEvaluationKeySet lookup by Galois element (fhe/ligero_test.go:53-56,
+ * cmd/server/main.go:66-122): evk = gk.Value[d][0][c] Q then P limbs, Montgomery + NTT form */
+int lmn_load_galois_key(lmn_ctx *ctx, uint64_t gal_el, const uint64_t *evk_host);
+/* ring-switch key (fhe/ring_switch.go:16-57, 98-104): evk sk -> embed(sk_small); psi_small = primitive
+ * 2N'-th root of q[0] used by the small ring (0 = derive as psi_q[0]^(N/N')) */
+int lmn_load_ring_switch_key(lmn_ctx *ctx, uint32_t log_n_small, const uint64_t *evk_host, uint64_t psi_small);
+
+/* ---------------- Inner product eval (fhe/ligero.go:299-370 matrixInnerSumEval) ---------------- */
+/* pt_host: plaintext at max level as bgv.Encoder.Encode produced it: [num_q][N], NTT domain (ligero.go:204-205).
+ * For each column i: MulNew(matrix[i], pt) -> InnerSum(.,1,rows) -> Rescale down to level 1 (ligero.go:319-333).
+ * out must hold matrix-count level-1 ciphertexts.  The host multiplies its Scale metadata by
+ * prod_{l=2..L} q_l^-1 mod t (returned by lmn_rescale_scale). */
+int lmn_inner_product(lmn_ctx *ctx, const lmn_store *matrix, const uint64_t *pt_host, uint32_t rows, lmn_store *out);
+/* fused pair: InnerProduct(Matrix, r) and InnerProduct(Matrix, b) reading the matrix once (ligero.go:231-242) */
+int lmn_inner_product2(lmn_ctx *ctx, const lmn_store *matrix, const uint64_t *pt_r_host, const uint64_t *pt_b_host,
+                       uint32_t rows, lmn_store *out_r, lmn_store *out_b);
+/* optional ring switch of every level-1 ciphertext of `in` (ligero.go:336-342, ring_switch.go:106-113):
+ * out is a level-0 store created with lmn_store_create_small */
+int lmn_store_create_small(lmn_ctx *ctx, uint32_t n_ct, lmn_store **out); /* [2][1][N'] per ct */
+int lmn_ring_switch(lmn_ctx *ctx, const lmn_store *in_level1, lmn_store *out_small);
+
+/* ---------------- Query columns eval (fhe/ligero.go:262-280) ---------------- */
+/* out[i] = EncodedMatrix[idx[i]] rescaled to level 1 (duplicates allowed; the reference's in-place second
+ * rescale of a duplicate is a no-op, so duplicates yield identical ciphertexts). */
+int lmn_query_columns(lmn_ctx *ctx, const lmn_store *encoded, const uint32_t *idx, uint32_t n_idx, lmn_store *out);
+/* product of q_l^-1 mod t for l = from_level .. to_level+1: the factor by which bgv Rescale updates Scale */
+uint64_t lmn_rescale_scale(const lmn_ctx *ctx, uint32_t from_level, uint32_t to_level);
+
+/* ---------------- ServerBFV operator level (fhe/bfv.go:13-58; promoted bgv.Evaluator methods) ---------------- */
+/* each operand is (store, index); stores must be at the same level unless noted */
+int lmn_ct_add(lmn_ctx *ctx, const lmn_store *a, uint32_t ai, const lmn_store *b, uint32_t bi, lmn_store *o, uint32_t oi); /* Evaluator.Add, ntt.go:27 */
+int lmn_ct_sub(lmn_ctx *ctx, const lmn_store *a, uint32_t ai, const lmn_store *b, uint32_t bi, lmn_store *o, uint32_t oi); /* Evaluator.Sub, ntt.go:31 */
+int lmn_ct_mul_scalar(lmn_ctx *ctx, const lmn_store *a, uint32_t ai, uint64_t w, lmn_store *o, uint32_t oi);              /* ServerBFV.Mul(ct,uint64), bfv.go:34-37 */
+int lmn_ct_mul_pt(lmn_ctx *ctx, const lmn_store *a, uint32_t ai, const uint64_t *pt_host, lmn_store *o, uint32_t oi);      /* ServerBFV.MulNew(ct,pt), bfv.go:39-42 */
+int lmn_ct_inner_sum(lmn_ctx *ctx, lmn_store *a, uint32_t ai, uint32_t n);                                                 /* Evaluator.InnerSum(ct,1,n,ct), ligero.go:325 */
+int lmn_ct_rescale(lmn_ctx *ctx, const lmn_store *a, uint32_t ai, lmn_store *o, uint32_t oi);                              /* Evaluator.Rescale: o is one level below a, ligero.go:332 */
+int lmn_ct_copy(lmn_ctx *ctx, const lmn_store *a, uint32_t ai, lmn_store *o, uint32_t oi);                                 /* Ciphertext.CopyNew, code.go:12 */
+/* ring.SubRing NTT / INTT of one limb of one polynomial, in place (test hook for the limb kernels) */
+int lmn_limb_ntt(lmn_ctx *ctx, lmn_store *a, uint32_t ai, uint32_t poly, uint32_t limb, int inverse);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,95 @@
+"""ctypes declarations of include/lumenos_b200.h.  Loading fails loudly when the CUDA library is not built:
+there is no CPU fallback in this package."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "liblumenos_b200.so")
+
+u64p = C.POINTER(C.c_uint64)
+u32p = C.POINTER(C.c_uint32)
+vp = C.c_void_p
+
+
+class LmnParams(C.Structure):
+    _fields_ = [("log_n", C.c_uint32), ("num_q", C.c_uint32), ("num_p", C.c_uint32),
+                ("q", u64p), ("p", u64p), ("psi_q", u64p), ("psi_p", u64p), ("t", C.c_uint64),
+                ("scalar_centered", C.c_uint32), ("moddown_round_nearest", C.c_uint32),
+                ("innersum_rowswap_last", C.c_uint32)]
+
+
+# name -> (restype, argtypes); exactly the symbols include/lumenos_b200.h declares
+SIGNATURES = {
+    "lmn_ctx_create": (C.c_int, [C.POINTER(LmnParams), C.c_int, C.POINTER(vp)]),
+    "lmn_ctx_destroy": (None, [vp]),
+    "lmn_last_error": (C.c_char_p, []),
+    "lmn_ctx_set_stream": (C.c_int, [vp, vp]),
+    "lmn_ctx_synchronize": (C.c_int, [vp]),
+    "lmn_ctx_launch_count": (C.c_uint64, [vp]),
+    "lmn_ctx_set_batch": (C.c_int, [vp, C.c_uint32]),
+    "lmn_store_create": (C.c_int, [vp, C.c_uint32, C.c_uint32, C.POINTER(vp)]),
+    "lmn_store_wrap": (C.c_int, [vp, vp, C.c_uint32, C.c_uint32, C.POINTER(vp)]),
+    "lmn_store_create_small": (C.c_int, [vp, C.c_uint32, C.POINTER(vp)]),
+    "lmn_store_destroy": (None, [vp]),
+    "lmn_store_count": (C.c_uint32, [vp]),
+    "lmn_store_level": (C.c_uint32, [vp]),
+    "lmn_store_device_ptr": (vp, [vp]),
+    "lmn_store_bytes": (C.c_size_t, [vp]),
+    "lmn_store_upload": (C.c_int, [vp, C.c_uint32, C.c_uint32, vp]),
+    "lmn_store_download": (C.c_int, [vp, C.c_uint32, C.c_uint32, vp]),
+    "lmn_store_upload_limb": (C.c_int, [vp, C.c_uint32, C.c_uint32, C.c_uint32, vp]),
+    "lmn_store_download_limb": (C.c_int, [vp, C.c_uint32, C.c_uint32, C.c_uint32, vp]),
+    "lmn_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(vp)]),
+    "lmn_host_free": (None, [vp]),
+    "lmn_plan_create": (C.c_int, [vp, C.c_uint32, C.c_uint32, vp, C.POINTER(vp)]),
+    "lmn_plan_destroy": (None, [vp]),
+    "lmn_plan_counts": (C.c_int, [vp, u64p, u64p, u64p]),
+    "lmn_plan_size": (C.c_uint32, [vp]),
+    "lmn_plan_host_check": (C.c_int, [C.c_uint32, vp, C.c_uint64, vp, vp]),
+    "lmn_encode": (C.c_int, [vp, vp, vp, vp, C.c_uint32, vp]),
+    "lmn_ntt": (C.c_int, [vp, vp, vp, vp]),
+    "lmn_load_galois_key": (C.c_int, [vp, C.c_uint64, vp]),
+    "lmn_load_ring_switch_key": (C.c_int, [vp, C.c_uint32, vp, C.c_uint64]),
+    "lmn_inner_product": (C.c_int, [vp, vp, vp, C.c_uint32, vp]),
+    "lmn_inner_product2": (C.c_int, [vp, vp, vp, vp, C.c_uint32, vp, vp]),
+    "lmn_ring_switch": (C.c_int, [vp, vp, vp]),
+    "lmn_query_columns": (C.c_int, [vp, vp, vp, C.c_uint32, vp]),
+    "lmn_rescale_scale": (C.c_uint64, [vp, C.c_uint32, C.c_uint32]),
+    "lmn_ct_add": (C.c_int, [vp, vp, C.c_uint32, vp, C.c_uint32, vp, C.c_uint32]),
+    "lmn_ct_sub": (C.c_int, [vp, vp, C.c_uint32, vp, C.c_uint32, vp, C.c_uint32]),
+    "lmn_ct_mul_scalar": (C.c_int, [vp, vp, C.c_uint32, C.c_uint64, vp, C.c_uint32]),
+    "lmn_ct_mul_pt": (C.c_int, [vp, vp, C.c_uint32, vp, vp, C.c_uint32]),
+    "lmn_ct_inner_sum": (C.c_int, [vp, vp, C.c_uint32, C.c_uint32]),
+    "lmn_ct_rescale": (C.c_int, [vp, vp, C.c_uint32, vp, C.c_uint32]),
+    "lmn_ct_copy": (C.c_int, [vp, vp, C.c_uint32, vp, C.c_uint32]),
+    "lmn_limb_ntt": (C.c_int, [vp, vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int]),
+}
+
+_lib = None
+
+
+class LumenosError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("liblumenos_b200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+def lib():
+    """The loaded C-ABI library.  Raises (never falls back) when liblumenos_b200.so is absent."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise ImportError("liblumenos_b200.so is not built (run `python -m lumenos_b200.build`); "
+                              "lumenos_b200 has no CPU fallback")
+        L = C.CDLL(SO_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            f = getattr(L, name)   # AttributeError if the library does not export a declared symbol
+            f.restype, f.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        raise LumenosError(rc, lib().lmn_last_error().decode())
+    return rc

@@ -1,0 +1,757 @@
+// C ABI of liblumenos_b200 (include/lumenos_b200.h): context, device-resident store, plan upload and the stage
+// drivers that sequence the kernels of kernels.cu on the context's CUDA stream.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/lumenos_b200.h"
+#include "hostmath.hpp"
+#include "kernels.cuh"
+#include "plan.hpp"
+
+using namespace lmn;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string &msg) { g_err = msg; return code; }
+#define CK(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess) return fail(LMN_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+struct lmn_ctx {
+    int device = 0;
+    int logn = 0, n = 0, k = 0, np = 0;
+    u64 t = 0;
+    std::vector<u64> q, p;                  // moduli: mod(i) = i < k ? q[i] : p[i-k]
+    bool scalar_centered = true, round_nearest = true, rowswap_last = true;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    ModDev *d_mods = nullptr;
+    ulonglong2 *d_twf = nullptr, *d_twi = nullptr;
+    DeviceTables T{};
+    std::map<int, std::pair<KsConsts, KsConsts *>> ks;      // per level
+    std::map<int, RescaleConsts *> rs;                      // per level
+    std::map<u64, u64 *> galois;                            // galEl -> device evk
+    // ring switch
+    int logn_small = 0;
+    u64 *d_rs_evk = nullptr;
+    ModDev *d_small_mod = nullptr;
+    ulonglong2 *d_small_tw = nullptr;
+    // workspace
+    uint32_t batch = 64;
+    u64 *ws_col = nullptr, *ws_y = nullptr, *ws_acc = nullptr, *ws_pt = nullptr;
+    uint32_t *ws_idx = nullptr; size_t ws_idx_cap = 0;
+    ulonglong2 *ws_scalar = nullptr;
+    uint32_t ws_jobs = 0;
+    uint64_t launches = 0;
+    std::mutex mu;
+
+    u64 mod(int i) const { return i < k ? q[i] : p[i - k]; }
+    size_t ct_words(int level) const { return 2 * (size_t)(level + 1) * n; }
+    Launch L() { return Launch{stream, &launches}; }
+};
+
+struct lmn_store {
+    lmn_ctx *ctx;
+    u64 *d = nullptr;
+    bool owned = true;
+    uint32_t count = 0, level = 0;
+    uint32_t n = 0;   // ring degree of the entries (ctx->n, or the small ring for ring-switch outputs)
+    size_t words() const { return 2 * (size_t)(level + 1) * n; }
+};
+
+struct lmn_plan {
+    lmn_ctx *ctx;
+    EncodePlan pl;
+    uint16_t *d_scale_after = nullptr;
+    uint32_t *d_out_pos = nullptr;
+    ulonglong2 *d_scal = nullptr;   // [k][nscal]
+    uint32_t cols = 0, rho_inv = 0;
+};
+
+// ------------------------------------------------------------------------------------------------------------
+static bool supported_logn(int l) { return l == 6 || l == 8 || l == 10 || l == 12 || l == 13 || l == 14; }
+
+static void build_mod(ModDev &m, u64 q, int n) {
+    memset(&m, 0, sizeof(m));
+    m.q = q; m.qinv = h_qinv64(q); m.mu = (u64)((((u128)1) << 64) / q);
+    m.ninv = h_invmod((u64)n % q, q); m.ninvs = h_shoup(m.ninv, q);
+}
+static void build_twiddles(u64 q, u64 psi, int logn, std::vector<ulonglong2> &fwd, std::vector<ulonglong2> &inv) {
+    int n = 1 << logn;
+    fwd.resize(n); inv.resize(n);
+    u64 psiinv = h_invmod(psi, q), a = 1, b = 1;
+    for (int j = 0; j < n; j++) {
+        int r = (int)h_bitrev((u64)j, logn);
+        fwd[r] = make_ulonglong2(a, h_shoup(a, q));
+        inv[r] = make_ulonglong2(b, h_shoup(b, q));
+        a = h_mulmod(a, psi, q); b = h_mulmod(b, psiinv, q);
+    }
+}
+
+static void build_ks_consts(const lmn_ctx *c, int level, KsConsts &K) {
+    memset(&K, 0, sizeof(K));
+    const int nq = level + 1, np = c->np, k = c->k;
+    K.nq = nq; K.np = np; K.k = k; K.beta = (nq + np - 1) / np;
+    for (int d = 0; d < K.beta; d++) { K.dig_start[d] = d * np; K.dig_size[d] = std::min(np, nq - d * np); }
+    auto digit_prod = [&](int d, int skip, u64 m) {
+        u64 r = 1 % m;
+        for (int a = 0; a < K.dig_size[d]; a++) { int i = K.dig_start[d] + a; if (i != skip) r = h_mulmod(r, c->q[i] % m, m); }
+        return r;
+    };
+    for (int d = 0; d < K.beta; d++) {
+        for (int a = 0; a < K.dig_size[d]; a++) {
+            int i = K.dig_start[d] + a; u64 qi = c->q[i];
+            u64 ninv = h_invmod((u64)c->n % qi, qi);
+            u64 w = K.dig_size[d] > 1 ? h_mulmod(ninv, h_invmod(digit_prod(d, i, qi), qi), qi) : ninv;
+            K.intt_w[i] = w; K.intt_ws[i] = h_shoup(w, qi);
+        }
+        for (int tix = 0; tix < nq + np; tix++) {
+            u64 m = c->mod(ks_mod_index(tix, nq, k));
+            for (int a = 0; a < K.dig_size[d]; a++) K.mu_c[d][tix][a] = h_mform(digit_prod(d, K.dig_start[d] + a, m), m);
+            u64 qd = digit_prod(d, -1, m);
+            u64 v = h_mulmod((u64)(K.dig_size[d] - 1) % m, qd, m);
+            K.mu_neg[d][tix] = v ? m - v : 0;
+        }
+    }
+    auto p_prod = [&](int skip, u64 m) {
+        u64 r = 1 % m;
+        for (int a = 0; a < np; a++) if (a != skip) r = h_mulmod(r, c->p[a] % m, m);
+        return r;
+    };
+    for (int j = 0; j < np; j++) {
+        u64 pj = c->p[j], ninv = h_invmod((u64)c->n % pj, pj), ci = h_invmod(p_prod(j, pj), pj);
+        u64 w = h_mulmod(ninv, ci, pj);
+        K.pin_w[j] = w; K.pin_ws[j] = h_shoup(w, pj);
+        K.pin_add[j] = c->round_nearest ? h_mulmod((pj - 1) >> 1, ci, pj) : 0;
+    }
+    for (int i = 0; i < nq; i++) {
+        u64 qi = c->q[i], Pm = p_prod(-1, qi);
+        for (int a = 0; a < np; a++) K.md_c[i][a] = h_mform(p_prod(a, qi), qi);
+        u64 half = c->round_nearest ? h_mulmod(h_submod(Pm, 1, qi), h_invmod(2, qi), qi) : 0;
+        u64 v = h_addmod(h_mulmod((u64)(np - 1) % qi, Pm, qi), half, qi);
+        K.md_neg[i] = v ? qi - v : 0;
+        u64 pinv = h_invmod(Pm, qi);
+        K.pinv_w[i] = pinv; K.pinv_ws[i] = h_shoup(pinv, qi);
+    }
+}
+
+static int get_ks(lmn_ctx *c, int level, const KsConsts **host, const KsConsts **dev) {
+    auto it = c->ks.find(level);
+    if (it == c->ks.end()) {
+        KsConsts K; build_ks_consts(c, level, K);
+        KsConsts *d = nullptr;
+        CK(cudaMalloc(&d, sizeof(KsConsts)));
+        CK(cudaMemcpy(d, &K, sizeof(KsConsts), cudaMemcpyHostToDevice));
+        it = c->ks.emplace(level, std::make_pair(K, d)).first;
+    }
+    *host = &it->second.first; *dev = it->second.second;
+    return 0;
+}
+static int get_rs(lmn_ctx *c, int level, const RescaleConsts **dev) {
+    auto it = c->rs.find(level);
+    if (it == c->rs.end()) {
+        RescaleConsts R; memset(&R, 0, sizeof(R));
+        u64 ql = c->q[level];
+        R.half = (ql - 1) >> 1;
+        for (int i = 0; i < level; i++) {
+            u64 qi = c->q[i];
+            R.half_mod[i] = R.half % qi;
+            u64 inv = h_invmod(ql % qi, qi);
+            R.qlinv_w[i] = inv; R.qlinv_ws[i] = h_shoup(inv, qi);
+        }
+        RescaleConsts *d = nullptr;
+        CK(cudaMalloc(&d, sizeof(R)));
+        CK(cudaMemcpy(d, &R, sizeof(R), cudaMemcpyHostToDevice));
+        it = c->rs.emplace(level, d).first;
+    }
+    *dev = it->second;
+    return 0;
+}
+
+static int ensure_workspace(lmn_ctx *c, uint32_t jobs) {
+    if (c->ws_jobs >= jobs) return 0;
+    if (c->ws_col) { cudaFree(c->ws_col); cudaFree(c->ws_y); cudaFree(c->ws_acc); c->ws_col = c->ws_y = c->ws_acc = nullptr; c->ws_jobs = 0; }
+    size_t N = c->n, k = c->k, KP = c->k + c->np;
+    CK(cudaMalloc(&c->ws_col, jobs * 2 * k * N * 8));
+    CK(cudaMalloc(&c->ws_y, jobs * k * N * 8));
+    CK(cudaMalloc(&c->ws_acc, jobs * 2 * KP * N * 8));
+    c->ws_jobs = jobs;
+    return 0;
+}
+static KsJobs jobs_view(lmn_ctx *c, uint32_t first, uint32_t jobs) {
+    size_t N = c->n, k = c->k, KP = c->k + c->np;
+    KsJobs J;
+    J.col_words = 2 * k * N; J.y_words = k * N; J.acc_words = 2 * KP * N;
+    J.col = c->ws_col + first * J.col_words; J.y = c->ws_y + first * J.y_words; J.acc = c->ws_acc + first * J.acc_words;
+    J.jobs = (int)jobs;
+    return J;
+}
+static u64 galois_element(const lmn_ctx *c, uint32_t rot) {  // 5^rot mod 2N
+    u64 mask = 2 * (u64)c->n - 1, g = 1, b = 5;
+    uint32_t e = rot & (uint32_t)(c->n / 2 - 1);
+    while (e) { if (e & 1) g = (g * b) & mask; b = (b * b) & mask; e >>= 1; }
+    return g;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+extern "C" {
+
+const char *lmn_last_error(void) { return g_err.c_str(); }
+
+int lmn_ctx_create(const lmn_params *P, int device, lmn_ctx **out) {
+    if (!P || !out) return fail(LMN_ERR_INVALID, "null argument");
+    if (!supported_logn((int)P->log_n)) return fail(LMN_ERR_UNSUPPORTED, "log_n must be one of 6, 8, 10, 12, 13, 14");
+    if (P->num_q < 1 || P->num_p < 1 || P->num_p > MAX_P || P->num_q + P->num_p > MAX_LIMBS ||
+        (P->num_q + P->num_p - 1) / P->num_p > MAX_DIGITS)
+        return fail(LMN_ERR_UNSUPPORTED, "unsupported modulus chain shape");
+    const u64 two_n = 2ull << P->log_n;
+    for (uint32_t i = 0; i < P->num_q + P->num_p; i++) {
+        u64 m = i < P->num_q ? P->q[i] : P->p[i - P->num_q];
+        u64 psi = i < P->num_q ? P->psi_q[i] : P->psi_p[i - P->num_q];
+        if (m >= (1ull << 59) || m < (1ull << 20) || m % two_n != 1) return fail(LMN_ERR_INVALID, "modulus must be an NTT-friendly prime below 2^59");
+        if (h_powmod(psi, two_n / 2, m) != m - 1) return fail(LMN_ERR_INVALID, "psi is not a primitive 2N-th root of unity");
+    }
+    if (P->t % two_n != 1) return fail(LMN_ERR_INVALID, "plaintext modulus must be 1 mod 2N");  // ref: fhe/bfv.go:136-140
+    if (device >= 0) CK(cudaSetDevice(device)); else CK(cudaGetDevice(&device));
+    int major = 0;
+    CK(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+    if (major < 10) return fail(LMN_ERR_UNSUPPORTED, "liblumenos_b200 requires an sm_100a (B200) device");
+    if (const char *e = kernels_init()) return fail(LMN_ERR_CUDA, std::string("kernel attribute setup: ") + e);
+
+    lmn_ctx *c = new lmn_ctx();
+    c->device = device; c->logn = (int)P->log_n; c->n = 1 << c->logn; c->k = (int)P->num_q; c->np = (int)P->num_p; c->t = P->t;
+    c->q.assign(P->q, P->q + P->num_q); c->p.assign(P->p, P->p + P->num_p);
+    if (P->scalar_centered != 0xffffffffu) c->scalar_centered = P->scalar_centered != 0;
+    if (P->moddown_round_nearest != 0xffffffffu) c->round_nearest = P->moddown_round_nearest != 0;
+    if (P->innersum_rowswap_last != 0xffffffffu) c->rowswap_last = P->innersum_rowswap_last != 0;
+    const int KP = c->k + c->np, N = c->n;
+    std::vector<ModDev> mods(KP);
+    std::vector<ulonglong2> twf((size_t)KP * N), twi((size_t)KP * N), f, iv;
+    for (int i = 0; i < KP; i++) {
+        u64 m = c->mod(i), psi = i < c->k ? P->psi_q[i] : P->psi_p[i - c->k];
+        build_mod(mods[i], m, N);
+        build_twiddles(m, psi, c->logn, f, iv);
+        std::copy(f.begin(), f.end(), twf.begin() + (size_t)i * N);
+        std::copy(iv.begin(), iv.end(), twi.begin() + (size_t)i * N);
+    }
+    cudaError_t e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMalloc(&c->d_mods, sizeof(ModDev) * KP);
+    if (e == cudaSuccess) e = cudaMalloc(&c->d_twf, sizeof(ulonglong2) * KP * N);
+    if (e == cudaSuccess) e = cudaMalloc(&c->d_twi, sizeof(ulonglong2) * KP * N);
+    if (e == cudaSuccess) e = cudaMalloc(&c->ws_pt, sizeof(u64) * 4 * c->k * N);
+    if (e == cudaSuccess) e = cudaMalloc(&c->ws_scalar, sizeof(ulonglong2) * MAX_LIMBS);
+    if (e == cudaSuccess) e = cudaMemcpy(c->d_mods, mods.data(), sizeof(ModDev) * KP, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(c->d_twf, twf.data(), sizeof(ulonglong2) * KP * N, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(c->d_twi, twi.data(), sizeof(ulonglong2) * KP * N, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { int rc = fail(LMN_ERR_CUDA, std::string("context setup: ") + cudaGetErrorString(e)); lmn_ctx_destroy(c); return rc; }
+    c->stream = c->own_stream;
+    c->T = DeviceTables{c->logn, c->n, c->k, c->np, c->d_mods, c->d_twf, c->d_twi};
+    *out = c;
+    return 0;
+}
+
+void lmn_ctx_destroy(lmn_ctx *c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    for (auto &kv : c->ks) cudaFree(kv.second.second);
+    for (auto &kv : c->rs) cudaFree(kv.second);
+    for (auto &kv : c->galois) cudaFree(kv.second);
+    cudaFree(c->d_mods); cudaFree(c->d_twf); cudaFree(c->d_twi); cudaFree(c->ws_pt); cudaFree(c->ws_scalar);
+    cudaFree(c->ws_col); cudaFree(c->ws_y); cudaFree(c->ws_acc); cudaFree(c->ws_idx);
+    cudaFree(c->d_rs_evk); cudaFree(c->d_small_mod); cudaFree(c->d_small_tw);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    delete c;
+}
+int lmn_ctx_set_stream(lmn_ctx *c, void *s) {
+    if (!c) return fail(LMN_ERR_INVALID, "null context");
+    std::lock_guard<std::mutex> g(c->mu);
+    c->stream = s ? (cudaStream_t)s : c->own_stream;
+    return 0;
+}
+int lmn_ctx_synchronize(lmn_ctx *c) {
+    if (!c) return fail(LMN_ERR_INVALID, "null context");
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+uint64_t lmn_ctx_launch_count(const lmn_ctx *c) { return c ? c->launches : 0; }
+int lmn_ctx_set_batch(lmn_ctx *c, uint32_t jobs) {
+    if (!c || jobs < 2 || jobs > 65535) return fail(LMN_ERR_INVALID, "batch must be in [2, 65535]");
+    std::lock_guard<std::mutex> g(c->mu);
+    c->batch = jobs;
+    return 0;
+}
+
+// ---------------- store ----------------
+static int store_new(lmn_ctx *c, void *wrap, uint32_t n_ct, uint32_t level, uint32_t ring_n, lmn_store **out) {
+    if (!c || !out || n_ct == 0) return fail(LMN_ERR_INVALID, "bad store arguments");
+    if ((int)level >= c->k) return fail(LMN_ERR_INVALID, "store level exceeds the modulus chain");
+    lmn_store *s = new lmn_store();
+    s->ctx = c; s->count = n_ct; s->level = level; s->n = ring_n;
+    if (wrap) { s->d = (u64 *)wrap; s->owned = false; }
+    else {
+        cudaSetDevice(c->device);
+        cudaError_t e = cudaMalloc(&s->d, s->words() * 8 * n_ct);
+        if (e != cudaSuccess) { delete s; return fail(LMN_ERR_NOMEM, std::string("store allocation: ") + cudaGetErrorString(e)); }
+    }
+    *out = s;
+    return 0;
+}
+int lmn_store_create(lmn_ctx *c, uint32_t n_ct, uint32_t level, lmn_store **out) { return store_new(c, nullptr, n_ct, level, c ? c->n : 0, out); }
+int lmn_store_wrap(lmn_ctx *c, void *p, uint32_t n_ct, uint32_t level, lmn_store **out) {
+    if (!p) return fail(LMN_ERR_INVALID, "null device pointer");
+    return store_new(c, p, n_ct, level, c ? c->n : 0, out);
+}
+int lmn_store_create_small(lmn_ctx *c, uint32_t n_ct, lmn_store **out) {
+    if (!c || !c->logn_small) return fail(LMN_ERR_NOKEY, "ring-switch key not loaded");
+    return store_new(c, nullptr, n_ct, 0, 1u << c->logn_small, out);
+}
+void lmn_store_destroy(lmn_store *s) {
+    if (!s) return;
+    if (s->owned && s->d) { cudaSetDevice(s->ctx->device); cudaStreamSynchronize(s->ctx->stream); cudaFree(s->d); }
+    delete s;
+}
+uint32_t lmn_store_count(const lmn_store *s) { return s ? s->count : 0; }
+uint32_t lmn_store_level(const lmn_store *s) { return s ? s->level : 0; }
+void *lmn_store_device_ptr(const lmn_store *s) { return s ? s->d : nullptr; }
+size_t lmn_store_bytes(const lmn_store *s) { return s ? s->words() * 8 * s->count : 0; }
+
+int lmn_store_upload(lmn_store *s, uint32_t first, uint32_t count, const uint64_t *host) {
+    if (!s || !host || (uint64_t)first + count > s->count) return fail(LMN_ERR_INVALID, "upload range out of bounds");
+    lmn_ctx *c = s->ctx; std::lock_guard<std::mutex> g(c->mu);
+    CK(cudaMemcpyAsync(s->d + first * s->words(), host, count * s->words() * 8, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+int lmn_store_download(const lmn_store *s, uint32_t first, uint32_t count, uint64_t *host) {
+    if (!s || !host || (uint64_t)first + count > s->count) return fail(LMN_ERR_INVALID, "download range out of bounds");
+    lmn_ctx *c = s->ctx; std::lock_guard<std::mutex> g(c->mu);
+    CK(cudaMemcpyAsync(host, s->d + first * s->words(), count * s->words() * 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+int lmn_store_upload_limb(lmn_store *s, uint32_t ct, uint32_t poly, uint32_t limb, const uint64_t *host) {
+    if (!s || !host || ct >= s->count || poly > 1 || limb > s->level) return fail(LMN_ERR_INVALID, "limb index out of bounds");
+    lmn_ctx *c = s->ctx; std::lock_guard<std::mutex> g(c->mu);
+    u64 *dst = s->d + ct * s->words() + ((size_t)poly * (s->level + 1) + limb) * s->n;
+    CK(cudaMemcpyAsync(dst, host, (size_t)s->n * 8, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+int lmn_store_download_limb(const lmn_store *s, uint32_t ct, uint32_t poly, uint32_t limb, uint64_t *host) {
+    if (!s || !host || ct >= s->count || poly > 1 || limb > s->level) return fail(LMN_ERR_INVALID, "limb index out of bounds");
+    lmn_ctx *c = s->ctx; std::lock_guard<std::mutex> g(c->mu);
+    const u64 *src = s->d + ct * s->words() + ((size_t)poly * (s->level + 1) + limb) * s->n;
+    CK(cudaMemcpyAsync(host, src, (size_t)s->n * 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+int lmn_host_alloc(size_t bytes, void **out) {
+    if (!out) return fail(LMN_ERR_INVALID, "null argument");
+    CK(cudaHostAlloc(out, bytes, cudaHostAllocDefault));
+    return 0;
+}
+void lmn_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+// ---------------- plan ----------------
+static u64 scalar_mod_q(const lmn_ctx *c, u64 w, u64 q) {
+    // bgv.Evaluator.Mul(ct, uint64): scalar mod t, centred when > t/2, Euclidean residue mod q
+    u64 t = c->t; w %= t;
+    if (c->scalar_centered && w > (t >> 1)) { u64 neg = (t - w) % q; return neg ? q - neg : 0; }
+    return w % q;
+}
+int lmn_plan_create(lmn_ctx *c, uint32_t cols, uint32_t rho_inv, const uint64_t *roots, lmn_plan **out) {
+    if (!roots || !out || cols == 0 || rho_inv == 0) return fail(LMN_ERR_INVALID, "bad plan arguments");
+    uint64_t n64 = (uint64_t)cols * rho_inv;
+    if (n64 > (1u << 16)) return fail(LMN_ERR_UNSUPPORTED, "codeword length above 65536");
+    uint32_t n = (uint32_t)n64;
+    lmn_plan *p = new lmn_plan();
+    p->ctx = c; p->cols = cols; p->rho_inv = rho_inv;
+    if (!c) { delete p; return fail(LMN_ERR_INVALID, "null context"); }
+    uint64_t t = c->t;
+    std::string err = compile_encode_plan(n, n, roots, t, ENC_MAX_TILE, p->pl);
+    if (!err.empty()) { delete p; return fail(LMN_ERR_INVALID, err); }
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    const EncodePlan &pl = p->pl;
+    size_t nscal = pl.scalars.size();
+    std::vector<ulonglong2> scal((size_t)c->k * nscal);
+    for (int i = 0; i < c->k; i++)
+        for (size_t s = 1; s < nscal; s++) {
+            u64 w = scalar_mod_q(c, pl.scalars[s], c->q[i]);
+            scal[(size_t)i * nscal + s] = make_ulonglong2(w, h_shoup(w, c->q[i]));
+        }
+    cudaError_t e = cudaMalloc(&p->d_scale_after, pl.scale_after.size() * sizeof(uint16_t));
+    if (e == cudaSuccess) e = cudaMalloc(&p->d_out_pos, pl.out_pos.size() * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMalloc(&p->d_scal, scal.size() * sizeof(ulonglong2));
+    if (e == cudaSuccess) e = cudaMemcpy(p->d_scale_after, pl.scale_after.data(), pl.scale_after.size() * sizeof(uint16_t), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(p->d_out_pos, pl.out_pos.data(), pl.out_pos.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(p->d_scal, scal.data(), scal.size() * sizeof(ulonglong2), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { int rc = fail(LMN_ERR_CUDA, std::string("plan upload: ") + cudaGetErrorString(e)); lmn_plan_destroy(p); return rc; }
+    *out = p;
+    return 0;
+}
+void lmn_plan_destroy(lmn_plan *p) {
+    if (!p) return;
+    if (p->ctx) cudaSetDevice(p->ctx->device);
+    cudaFree(p->d_scale_after); cudaFree(p->d_out_pos); cudaFree(p->d_scal);
+    delete p;
+}
+int lmn_plan_counts(const lmn_plan *p, uint64_t *a, uint64_t *s, uint64_t *m) {
+    if (!p) return fail(LMN_ERR_INVALID, "null plan");
+    if (a) *a = p->pl.adds; if (s) *s = p->pl.subs; if (m) *m = p->pl.muls;
+    return 0;
+}
+uint32_t lmn_plan_size(const lmn_plan *p) { return p ? p->pl.n : 0; }
+
+// Host-only entry points for CPU-side checks of the plan compiler (no device needed).  They evaluate the compiled
+// plan on a plaintext vector over Z_t, i.e. they must reproduce core.NTT (core/ntt.go) -- which is how the
+// reference itself validates fhe.NTT (fhe/code_test.go:100-116).  Not part of the ciphertext data path.
+int lmn_plan_host_check(uint32_t n, const uint64_t *roots, uint64_t t, uint64_t *values, uint64_t *counts3) {
+    if (!roots || !values) return fail(LMN_ERR_INVALID, "null argument");
+    EncodePlan pl;
+    std::string err = compile_encode_plan(n, n, roots, t, ENC_MAX_TILE, pl);
+    if (!err.empty()) return fail(LMN_ERR_INVALID, err);
+    std::vector<u64> v(values, values + n);
+    for (uint32_t s = 0; s < pl.logn; s++) {
+        const uint32_t bit = 1u << pl.stage_bit[s];
+        for (uint32_t lo = 0; lo < n; lo++) {
+            if (lo & bit) continue;
+            u64 a = v[lo], b = v[lo | bit];
+            v[lo] = h_addmod(a, b, t); v[lo | bit] = h_submod(a, b, t);
+        }
+        for (uint32_t x = 0; x < n; x++) {
+            uint16_t id = pl.scale_after[(size_t)s * n + x];
+            if (id) v[x] = h_mulmod(v[x], pl.scalars[id] % t, t);
+        }
+    }
+    for (uint32_t x = 0; x < n; x++) values[pl.out_pos[x]] = v[x];
+    if (counts3) { counts3[0] = pl.adds; counts3[1] = pl.subs; counts3[2] = pl.muls; }
+    return 0;
+}
+
+// ---------------- Encode ----------------
+static int run_plan(lmn_ctx *c, const lmn_plan *p, const u64 *in, uint32_t in_count, const u64 *zero, u64 *out) {
+    const EncodePlan &pl = p->pl;
+    EncPassArgs A; memset(&A, 0, sizeof(A));
+    A.mods = c->d_mods; A.scale_after = p->d_scale_after; A.out_pos = p->d_out_pos; A.scal = p->d_scal;
+    A.nscal = (uint32_t)pl.scalars.size(); A.n = pl.n; A.k = c->k; A.logn = c->logn; A.ct_words = c->ct_words(c->k - 1);
+    A.out = out;
+    Launch L = c->L();
+    if (pl.split == 0) {
+        A.in = in; A.zero = zero; A.in_count = in_count; A.in_by_pos = 0;
+        A.log_tile = (int)pl.logn; A.s0 = 0; A.s1 = (int)pl.logn; A.tile_mul = 0; A.stride = 1;
+        A.lbits = 0; for (uint32_t s = 0; s < pl.logn; s++) A.lbits |= (uint64_t)pl.stage_bit[s] << (4 * s);
+        launch_encode_pass(L, A);
+    } else {
+        const int lg2 = h_log2(pl.n2);
+        // pass 1: size-n1 column transforms + twiddles (fhe/ntt.go:254-274); tile = fixed column c, slots c + r*n2
+        A.in = in; A.zero = zero; A.in_count = in_count; A.in_by_pos = 0;
+        A.log_tile = (int)pl.split; A.s0 = 0; A.s1 = (int)pl.split; A.tile_mul = 1; A.stride = pl.n2;
+        A.lbits = 0; for (uint32_t s = 0; s < pl.split; s++) A.lbits |= (uint64_t)(pl.stage_bit[s] - lg2) << (4 * s);
+        launch_encode_pass(L, A);
+        // pass 2: size-n2 row transforms (fhe/ntt.go:276), in place on the positions pass 1 wrote
+        A.in = out; A.zero = nullptr; A.in_count = pl.n; A.in_by_pos = 1;
+        A.log_tile = lg2; A.s0 = (int)pl.split; A.s1 = (int)pl.logn; A.tile_mul = pl.n2; A.stride = 1;
+        A.lbits = 0; for (uint32_t s = pl.split; s < pl.logn; s++) A.lbits |= (uint64_t)pl.stage_bit[s] << (4 * (s - pl.split));
+        launch_encode_pass(L, A);
+    }
+    CK(cudaGetLastError());
+    return 0;
+}
+int lmn_encode(lmn_ctx *c, const lmn_plan *p, const lmn_store *matrix, const lmn_store *zero, uint32_t zero_idx, lmn_store *enc) {
+    if (!c || !p || !matrix || !zero || !enc) return fail(LMN_ERR_INVALID, "null argument");
+    if (p->ctx != c || matrix->ctx != c || zero->ctx != c || enc->ctx != c) return fail(LMN_ERR_INVALID, "objects belong to different contexts");
+    const uint32_t L = (uint32_t)c->k - 1;
+    if (matrix->level != L || zero->level != L || enc->level != L) return fail(LMN_ERR_INVALID, "Encode operates on max-level ciphertexts");
+    if (matrix->count != p->cols || enc->count != p->pl.n || zero_idx >= zero->count) return fail(LMN_ERR_INVALID, "store sizes do not match the plan");
+    if (enc->d == matrix->d) return fail(LMN_ERR_INVALID, "encoded store must be distinct from the matrix");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    return run_plan(c, p, matrix->d, matrix->count, zero->d + zero_idx * zero->words(), enc->d);
+}
+int lmn_ntt(lmn_ctx *c, const lmn_plan *p, const lmn_store *in, lmn_store *out) {
+    if (!c || !p || !in || !out) return fail(LMN_ERR_INVALID, "null argument");
+    const uint32_t L = (uint32_t)c->k - 1;
+    if (in->level != L || out->level != L || in->count != p->pl.n || out->count != p->pl.n) return fail(LMN_ERR_INVALID, "NTT needs plan-size stores of max-level ciphertexts");
+    if (in->d == out->d) return fail(LMN_ERR_INVALID, "in and out must be distinct stores");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    return run_plan(c, p, in->d, in->count, nullptr, out->d);
+}
+
+// ---------------- keys ----------------
+int lmn_load_galois_key(lmn_ctx *c, uint64_t gal_el, const uint64_t *evk) {
+    if (!c || !evk) return fail(LMN_ERR_INVALID, "null argument");
+    if (!(gal_el & 1) || gal_el >= 2 * (u64)c->n) return fail(LMN_ERR_INVALID, "Galois element must be odd and below 2N");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    if (gal_el == 1) return 0;  // identity: Lattigo's key list may contain it; never used
+    const int beta = (c->k + c->np - 1) / c->np;
+    size_t bytes = (size_t)beta * 2 * (c->k + c->np) * c->n * 8;
+    u64 *d = nullptr;
+    auto it = c->galois.find(gal_el);
+    if (it != c->galois.end()) d = it->second; else CK(cudaMalloc(&d, bytes));
+    CK(cudaMemcpyAsync(d, evk, bytes, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    c->galois[gal_el] = d;
+    return 0;
+}
+int lmn_load_ring_switch_key(lmn_ctx *c, uint32_t logns, const uint64_t *evk, uint64_t psi_small) {
+    if (!c || !evk) return fail(LMN_ERR_INVALID, "null argument");
+    if ((int)logns >= c->logn) return fail(LMN_ERR_INVALID, "small ring must be smaller than the ciphertext ring");
+    bool ok = (logns == 10 && c->logn >= 12) || (logns == 6 && (c->logn == 8 || c->logn == 10)) || (logns == 8 && (c->logn == 10 || c->logn == 12));
+    if (!ok) return fail(LMN_ERR_UNSUPPORTED, "ring switch is instantiated for N' = 1024 (N >= 4096) and the small test rings");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    const int beta = (c->k + c->np - 1) / c->np;
+    size_t bytes = (size_t)beta * 2 * (c->k + c->np) * c->n * 8;
+    if (!c->d_rs_evk) CK(cudaMalloc(&c->d_rs_evk, bytes));
+    CK(cudaMemcpy(c->d_rs_evk, evk, bytes, cudaMemcpyHostToDevice));
+    u64 q0 = c->q[0];
+    if (!psi_small) {
+        // psi_small = psi^(N/N'): read psi back from the forward table (entry bitrev(1) = N/2 holds psi)
+        ulonglong2 w; CK(cudaMemcpy(&w, c->d_twf + c->n / 2, sizeof(w), cudaMemcpyDeviceToHost));
+        psi_small = h_powmod(w.x, (u64)c->n >> logns, q0);
+    }
+    if (h_powmod(psi_small, 1ull << logns, q0) != q0 - 1) return fail(LMN_ERR_INVALID, "psi_small is not a primitive 2N'-th root");
+    ModDev m; build_mod(m, q0, 1 << logns);
+    std::vector<ulonglong2> f, iv; build_twiddles(q0, psi_small, (int)logns, f, iv);
+    if (c->d_small_mod) { cudaFree(c->d_small_mod); cudaFree(c->d_small_tw); }
+    CK(cudaMalloc(&c->d_small_mod, sizeof(ModDev)));
+    CK(cudaMalloc(&c->d_small_tw, sizeof(ulonglong2) << logns));
+    CK(cudaMemcpy(c->d_small_mod, &m, sizeof(m), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(c->d_small_tw, f.data(), sizeof(ulonglong2) << logns, cudaMemcpyHostToDevice));
+    c->logn_small = (int)logns;
+    return 0;
+}
+
+// ---------------- InnerSum on the job workspace ----------------
+static int innersum_jobs(lmn_ctx *c, int level, const KsJobs &J, uint32_t n) {
+    const uint32_t N = (uint32_t)c->n;
+    if (n == 0 || (n & (n - 1)) || n > N) return fail(LMN_ERR_UNSUPPORTED, "InnerSum is implemented for power-of-two n <= N");
+    const KsConsts *Kh, *Kd;
+    if (int rc = get_ks(c, level, &Kh, &Kd)) return rc;
+    const bool full = n == N;
+    const uint32_t m = full ? N / 2 : n;
+    std::vector<u64> gals;
+    if (full && !c->rowswap_last) gals.push_back(2 * (u64)N - 1);
+    for (uint32_t s = 1; s < m; s <<= 1) gals.push_back(galois_element(c, s));
+    if (full && c->rowswap_last) gals.push_back(2 * (u64)N - 1);
+    for (u64 g : gals) if (!c->galois.count(g)) return fail(LMN_ERR_NOKEY, "missing Galois key for element " + std::to_string(g));
+    Launch L = c->L();
+    for (u64 g : gals) launch_rotate_accumulate(L, c->T, Kd, *Kh, J, c->galois[g], (uint32_t)g);
+    CK(cudaGetLastError());
+    return 0;
+}
+static int rescale_jobs_to(lmn_ctx *c, int from_level, int to_level, const KsJobs &J) {
+    Launch L = c->L();
+    for (int l = from_level; l > to_level; l--) {
+        const RescaleConsts *Rd;
+        if (int rc = get_rs(c, l, &Rd)) return rc;
+        launch_rescale_step(L, c->T, Rd, l, J);
+    }
+    CK(cudaGetLastError());
+    return 0;
+}
+
+// ---------------- Inner product eval ----------------
+int lmn_inner_product2(lmn_ctx *c, const lmn_store *matrix, const uint64_t *pt_r, const uint64_t *pt_b, uint32_t rows,
+                       lmn_store *out_r, lmn_store *out_b) {
+    if (!c || !matrix || !pt_r || !out_r || (pt_b && !out_b)) return fail(LMN_ERR_INVALID, "null argument");
+    const int Lmax = c->k - 1, lout = std::min(1, Lmax);
+    if ((int)matrix->level != Lmax) return fail(LMN_ERR_INVALID, "matrix must hold max-level ciphertexts");
+    if ((int)out_r->level != lout || out_r->count != matrix->count || (pt_b && ((int)out_b->level != lout || out_b->count != matrix->count)))
+        return fail(LMN_ERR_INVALID, "output stores must hold one level-1 ciphertext per column");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    const size_t N = c->n, k = c->k;
+    const int nvec = pt_b ? 2 : 1;
+    const uint32_t bc = std::max(1u, c->batch / nvec);
+    if (int rc = ensure_workspace(c, bc * nvec)) return rc;
+    Launch L = c->L();
+    // plaintexts: upload, fold T and the Montgomery factor (tensorStandard's T * pt)
+    u64 *d_pt = c->ws_pt, *d_ptm = c->ws_pt + 2 * k * N;
+    CK(cudaMemcpyAsync(d_pt, pt_r, k * N * 8, cudaMemcpyHostToDevice, c->stream));
+    if (pt_b) CK(cudaMemcpyAsync(d_pt + k * N, pt_b, k * N * 8, cudaMemcpyHostToDevice, c->stream));
+    launch_prep_pt(L, c->T, Lmax, d_pt, c->t, d_ptm);
+    if (pt_b) launch_prep_pt(L, c->T, Lmax, d_pt + k * N, c->t, d_ptm + k * N);
+    const size_t out_words = 2 * (size_t)(lout + 1) * N;
+    for (uint32_t c0 = 0; c0 < matrix->count; c0 += bc) {
+        const uint32_t nc = std::min(bc, matrix->count - c0);
+        KsJobs J = jobs_view(c, 0, nc * nvec);
+        launch_mul_pt(L, c->T, Lmax, matrix->d + c0 * matrix->words(), matrix->words(), (int)nc, d_ptm, pt_b ? d_ptm + k * N : nullptr,
+                      J.col, J.col + nc * J.col_words, J.col_words);
+        if (int rc = innersum_jobs(c, Lmax, J, rows)) return rc;
+        if (int rc = rescale_jobs_to(c, Lmax, lout, J)) return rc;
+        KsJobs Jr = jobs_view(c, 0, nc);
+        launch_pack_out(L, c->T, Jr, lout + 1, out_r->d + c0 * out_words);
+        if (pt_b) { KsJobs Jb = jobs_view(c, nc, nc); launch_pack_out(L, c->T, Jb, lout + 1, out_b->d + c0 * out_words); }
+    }
+    CK(cudaGetLastError());
+    return 0;
+}
+int lmn_inner_product(lmn_ctx *c, const lmn_store *matrix, const uint64_t *pt, uint32_t rows, lmn_store *out) {
+    return lmn_inner_product2(c, matrix, pt, nullptr, rows, out, nullptr);
+}
+
+uint64_t lmn_rescale_scale(const lmn_ctx *c, uint32_t from_level, uint32_t to_level) {
+    if (!c || (int)from_level >= c->k || to_level > from_level) return 0;
+    u64 s = 1;
+    for (uint32_t l = from_level; l > to_level; l--) s = h_mulmod(s, h_invmod(c->q[l] % c->t, c->t), c->t);
+    return s;
+}
+
+// ---------------- Query columns ----------------
+int lmn_query_columns(lmn_ctx *c, const lmn_store *enc, const uint32_t *idx, uint32_t n_idx, lmn_store *out) {
+    if (!c || !enc || !idx || !out || n_idx == 0) return fail(LMN_ERR_INVALID, "null argument");
+    const int Lmax = c->k - 1, lout = std::min(1, Lmax);
+    if ((int)enc->level != Lmax || (int)out->level != lout || out->count < n_idx) return fail(LMN_ERR_INVALID, "query needs max-level input and a level-1 output store with n_idx entries");
+    for (uint32_t i = 0; i < n_idx; i++) if (idx[i] >= enc->count) return fail(LMN_ERR_INVALID, "query index out of range");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    if (c->ws_idx_cap < n_idx) { cudaFree(c->ws_idx); c->ws_idx = nullptr; CK(cudaMalloc(&c->ws_idx, n_idx * sizeof(uint32_t))); c->ws_idx_cap = n_idx; }
+    CK(cudaMemcpyAsync(c->ws_idx, idx, n_idx * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+    const uint32_t bc = c->batch;
+    if (int rc = ensure_workspace(c, bc)) return rc;
+    Launch L = c->L();
+    const size_t out_words = 2 * (size_t)(lout + 1) * c->n;
+    for (uint32_t j0 = 0; j0 < n_idx; j0 += bc) {
+        const uint32_t nj = std::min(bc, n_idx - j0);
+        KsJobs J = jobs_view(c, 0, nj);
+        launch_gather_in(L, c->T, enc->d, enc->words(), c->ws_idx + j0, J);
+        if (int rc = rescale_jobs_to(c, Lmax, lout, J)) return rc;
+        launch_pack_out(L, c->T, J, lout + 1, out->d + j0 * out_words);
+    }
+    CK(cudaGetLastError());
+    return 0;
+}
+
+// ---------------- ring switch ----------------
+int lmn_ring_switch(lmn_ctx *c, const lmn_store *in, lmn_store *out) {
+    if (!c || !in || !out) return fail(LMN_ERR_INVALID, "null argument");
+    if (!c->logn_small) return fail(LMN_ERR_NOKEY, "ring-switch key not loaded");
+    if (in->level != 1 || out->level != 0 || out->n != (1u << c->logn_small) || out->count != in->count)
+        return fail(LMN_ERR_INVALID, "ring switch maps level-1 ciphertexts to level-0 ciphertexts of the small ring");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    const KsConsts *Kh, *Kd;
+    if (int rc = get_ks(c, 0, &Kh, &Kd)) return rc;
+    const uint32_t bc = c->batch;
+    if (int rc = ensure_workspace(c, bc)) return rc;
+    Launch L = c->L();
+    const size_t N = c->n, k = c->k;
+    for (uint32_t j0 = 0; j0 < in->count; j0 += bc) {
+        const uint32_t nj = std::min(bc, in->count - j0);
+        KsJobs J = jobs_view(c, 0, nj);
+        // limb 0 of both polys of each level-1 ct -> col[c][0]   (the key switch runs at level min(1, 0) = 0)
+        CK(cudaMemcpy2DAsync(J.col, k * N * 8, in->d + j0 * in->words(), 2 * N * 8, N * 8, (size_t)nj * 2, cudaMemcpyDeviceToDevice, c->stream));
+        launch_keyswitch_level0(L, c->T, Kd, *Kh, J, c->d_rs_evk);
+        launch_ring_decimate(L, c->T, J, c->logn_small, c->d_small_mod, c->d_small_tw, out->d + j0 * out->words());
+    }
+    CK(cudaGetLastError());
+    return 0;
+}
+
+// ---------------- operator level ----------------
+static int check_pair(lmn_ctx *c, const lmn_store *a, uint32_t ai, const lmn_store *o, uint32_t oi) {
+    if (!c || !a || !o) return fail(LMN_ERR_INVALID, "null argument");
+    if (ai >= a->count || oi >= o->count) return fail(LMN_ERR_INVALID, "ciphertext index out of range");
+    if (a->n != (uint32_t)c->n || o->n != (uint32_t)c->n) return fail(LMN_ERR_INVALID, "operator needs ciphertexts of the context ring");
+    return 0;
+}
+static int addsub(lmn_ctx *c, const lmn_store *a, uint32_t ai, const lmn_store *b, uint32_t bi, lmn_store *o, uint32_t oi, int sub) {
+    if (int rc = check_pair(c, a, ai, o, oi)) return rc;
+    if (!b || bi >= b->count || a->level != b->level || a->level != o->level) return fail(LMN_ERR_INVALID, "operands must share one level");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    launch_addsub(c->L(), c->T, (int)a->level, a->d + ai * a->words(), b->d + bi * b->words(), o->d + oi * o->words(), sub);
+    CK(cudaGetLastError());
+    return 0;
+}
+int lmn_ct_add(lmn_ctx *c, const lmn_store *a, uint32_t ai, const lmn_store *b, uint32_t bi, lmn_store *o, uint32_t oi) { return addsub(c, a, ai, b, bi, o, oi, 0); }
+int lmn_ct_sub(lmn_ctx *c, const lmn_store *a, uint32_t ai, const lmn_store *b, uint32_t bi, lmn_store *o, uint32_t oi) { return addsub(c, a, ai, b, bi, o, oi, 1); }
+int lmn_ct_mul_scalar(lmn_ctx *c, const lmn_store *a, uint32_t ai, uint64_t w, lmn_store *o, uint32_t oi) {
+    if (int rc = check_pair(c, a, ai, o, oi)) return rc;
+    if (a->level != o->level) return fail(LMN_ERR_INVALID, "operands must share one level");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    ulonglong2 ws[MAX_LIMBS];
+    for (int i = 0; i <= (int)a->level; i++) { u64 wi = scalar_mod_q(c, w, c->q[i]); ws[i] = make_ulonglong2(wi, h_shoup(wi, c->q[i])); }
+    CK(cudaMemcpyAsync(c->ws_scalar, ws, sizeof(ulonglong2) * (a->level + 1), cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));  // ws is a stack buffer
+    launch_mul_scalar(c->L(), c->T, (int)a->level, a->d + ai * a->words(), c->ws_scalar, o->d + oi * o->words());
+    CK(cudaGetLastError());
+    return 0;
+}
+int lmn_ct_mul_pt(lmn_ctx *c, const lmn_store *a, uint32_t ai, const uint64_t *pt, lmn_store *o, uint32_t oi) {
+    if (int rc = check_pair(c, a, ai, o, oi)) return rc;
+    if (!pt || a->level != o->level) return fail(LMN_ERR_INVALID, "operands must share one level");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    const size_t N = c->n, nl = a->level + 1;
+    u64 *d_pt = c->ws_pt, *d_ptm = c->ws_pt + 2 * (size_t)c->k * N;
+    CK(cudaMemcpyAsync(d_pt, pt, nl * N * 8, cudaMemcpyHostToDevice, c->stream));
+    Launch L = c->L();
+    launch_prep_pt(L, c->T, (int)a->level, d_pt, c->t, d_ptm);
+    launch_mul_pt(L, c->T, (int)a->level, a->d + ai * a->words(), a->words(), 1, d_ptm, nullptr, o->d + oi * o->words(), nullptr, o->words());
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+// copy a store entry at `level` into / out of job 0's col (limb stride k)
+static int col_load(lmn_ctx *c, const u64 *src, int level) {
+    const size_t N = c->n;
+    CK(cudaMemcpy2DAsync(c->ws_col, c->k * N * 8, src, (size_t)(level + 1) * N * 8, (size_t)(level + 1) * N * 8, 2, cudaMemcpyDeviceToDevice, c->stream));
+    return 0;
+}
+static int col_store(lmn_ctx *c, u64 *dst, int level) {
+    const size_t N = c->n;
+    CK(cudaMemcpy2DAsync(dst, (size_t)(level + 1) * N * 8, c->ws_col, c->k * N * 8, (size_t)(level + 1) * N * 8, 2, cudaMemcpyDeviceToDevice, c->stream));
+    return 0;
+}
+int lmn_ct_inner_sum(lmn_ctx *c, lmn_store *a, uint32_t ai, uint32_t n) {
+    if (int rc = check_pair(c, a, ai, a, ai)) return rc;
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    if (int rc = ensure_workspace(c, 2)) return rc;
+    if (int rc = col_load(c, a->d + ai * a->words(), (int)a->level)) return rc;
+    KsJobs J = jobs_view(c, 0, 1);
+    if (int rc = innersum_jobs(c, (int)a->level, J, n)) return rc;
+    return col_store(c, a->d + ai * a->words(), (int)a->level);
+}
+int lmn_ct_rescale(lmn_ctx *c, const lmn_store *a, uint32_t ai, lmn_store *o, uint32_t oi) {
+    if (int rc = check_pair(c, a, ai, o, oi)) return rc;
+    if (a->level == 0 || o->level + 1 != a->level) return fail(LMN_ERR_INVALID, "Rescale output must be one level below a non-zero input level");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    if (int rc = ensure_workspace(c, 2)) return rc;
+    if (int rc = col_load(c, a->d + ai * a->words(), (int)a->level)) return rc;
+    KsJobs J = jobs_view(c, 0, 1);
+    if (int rc = rescale_jobs_to(c, (int)a->level, (int)a->level - 1, J)) return rc;
+    return col_store(c, o->d + oi * o->words(), (int)o->level);
+}
+int lmn_ct_copy(lmn_ctx *c, const lmn_store *a, uint32_t ai, lmn_store *o, uint32_t oi) {
+    if (int rc = check_pair(c, a, ai, o, oi)) return rc;
+    if (a->level != o->level) return fail(LMN_ERR_INVALID, "operands must share one level");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    CK(cudaMemcpyAsync(o->d + oi * o->words(), a->d + ai * a->words(), a->words() * 8, cudaMemcpyDeviceToDevice, c->stream));
+    return 0;
+}
+int lmn_limb_ntt(lmn_ctx *c, lmn_store *a, uint32_t ai, uint32_t poly, uint32_t limb, int inverse) {
+    if (int rc = check_pair(c, a, ai, a, ai)) return rc;
+    if (poly > 1 || limb > a->level) return fail(LMN_ERR_INVALID, "limb index out of bounds");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    launch_limb_ntt(c->L(), c->T, (int)limb, a->d + ai * a->words() + ((size_t)poly * (a->level + 1) + limb) * c->n, inverse);
+    CK(cudaGetLastError());
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,596 @@
+// CUDA kernels (sm_100a) of the lumenos hot path.  See DESIGN.md for the kernel list and rooflines.
+//
+//   Encode eval      k_encode_pass                      HBM-bound   (fhe/code.go, fhe/ntt.go)
+//   Inner product    k_mul_pt, k_intt_c1, k_vfix, k_mac, k_pintt, k_vpfix, k_down   integer-bound
+//                    (fhe/ligero.go:319-325 = MulNew + InnerSum; lattigo DecomposeNTT / GadgetProduct / ModDown)
+//   Rescale          k_rs_intt, k_rs_apply              integer-bound (fhe/ligero.go:331-333, 271-273)
+#include "kernels.cuh"
+
+#include <cstdio>
+
+namespace lmn {
+
+#define LMN_DISPATCH_LOGN(LOGN_RT, ...)                                     \
+    switch (LOGN_RT) {                                                      \
+        case 6:  { constexpr int LG = 6;  __VA_ARGS__; } break;             \
+        case 8:  { constexpr int LG = 8;  __VA_ARGS__; } break;             \
+        case 10: { constexpr int LG = 10; __VA_ARGS__; } break;             \
+        case 12: { constexpr int LG = 12; __VA_ARGS__; } break;             \
+        case 13: { constexpr int LG = 13; __VA_ARGS__; } break;             \
+        case 14: { constexpr int LG = 14; __VA_ARGS__; } break;             \
+        default: break;                                                     \
+    }
+
+static inline int ntt_threads(int m) { int t = m / 8; return t < 32 ? 32 : (t > 1024 ? 1024 : t); }
+static inline void count(const Launch &L) { if (L.counter) (*L.counter)++; }
+
+// =====================================================================================================
+// elementwise kernels
+// =====================================================================================================
+__global__ void k_addsub(const ModDev *mods, int nlimbs, int logn, const u64 *__restrict__ a, const u64 *__restrict__ b,
+                         u64 *__restrict__ o, int sub) {
+    // grid.y = poly*nlimbs + limb ; grid.x covers N/2 (ulonglong2 vectorised)
+    const int limb = blockIdx.y % nlimbs;
+    const u64 q = mods[limb].q;
+    const size_t off = ((size_t)blockIdx.y << logn);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (1 << (logn - 1))) return;
+    ulonglong2 x = reinterpret_cast<const ulonglong2 *>(a + off)[i];
+    ulonglong2 y = reinterpret_cast<const ulonglong2 *>(b + off)[i];
+    ulonglong2 r;
+    if (sub) { r.x = sub_mod(x.x, y.x, q); r.y = sub_mod(x.y, y.y, q); }
+    else     { r.x = add_mod(x.x, y.x, q); r.y = add_mod(x.y, y.y, q); }
+    reinterpret_cast<ulonglong2 *>(o + off)[i] = r;
+}
+void launch_addsub(const Launch &L, const DeviceTables &T, int level, const u64 *a, const u64 *b, u64 *o, int sub) {
+    int nl = level + 1, half = T.n / 2, bs = half < 256 ? half : 256;
+    dim3 g((half + bs - 1) / bs, 2 * nl);
+    k_addsub<<<g, bs, 0, L.stream>>>(T.mods, nl, T.logn, a, b, o, sub);
+    count(L);
+}
+
+__global__ void k_mul_scalar(const ModDev *mods, int nlimbs, int logn, const u64 *__restrict__ a,
+                             const ulonglong2 *__restrict__ w, u64 *__restrict__ o) {
+    const int limb = blockIdx.y % nlimbs;
+    const u64 q = mods[limb].q;
+    const ulonglong2 ww = w[limb];
+    const size_t off = ((size_t)blockIdx.y << logn);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (1 << (logn - 1))) return;
+    ulonglong2 x = reinterpret_cast<const ulonglong2 *>(a + off)[i];
+    x.x = mul_shoup(x.x, ww.x, ww.y, q);
+    x.y = mul_shoup(x.y, ww.x, ww.y, q);
+    reinterpret_cast<ulonglong2 *>(o + off)[i] = x;
+}
+void launch_mul_scalar(const Launch &L, const DeviceTables &T, int level, const u64 *a, const ulonglong2 *w, u64 *o) {
+    int nl = level + 1, half = T.n / 2, bs = half < 256 ? half : 256;
+    dim3 g((half + bs - 1) / bs, 2 * nl);
+    k_mul_scalar<<<g, bs, 0, L.stream>>>(T.mods, nl, T.logn, a, w, o);
+    count(L);
+}
+
+// ptm = MForm(pt * (T mod q_i))  : folds the factor T of bgv tensorStandard (degree-0 operand) and the Montgomery
+// form into the plaintext once per Prove (ref: fhe/ligero.go:204-205,218-219 -> MulNew at :319)
+__global__ void k_prep_pt(const ModDev *mods, int logn, const u64 *__restrict__ pt, u64 t_mod, u64 *__restrict__ ptm) {
+    const int limb = blockIdx.y;
+    const ModDev md = mods[limb];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (1 << logn)) return;
+    const size_t off = ((size_t)limb << logn) + i;
+    // (pt * T) mod q, then * 2^64 mod q, by 128-bit products reduced with Barrett on the high/low words
+    u64 x = pt[off];
+    u64 tq = t_mod % md.q;
+    // x*tq mod q via Montgomery with R^2: avoid needing R^2 -- use two-step: y = x*tq mod q by 128-bit long reduction
+    u64 lo = x * tq, hi = __umul64hi(x, tq);
+    // reduce hi:lo mod q  (hi < q since x,tq < q): shift-subtract 64 steps (setup kernel, not on the hot path)
+    u64 r = hi % md.q;
+    for (int b = 63; b >= 0; b--) {
+        r = (r << 1) | ((lo >> b) & 1);   // r < 2q < 2^60
+        r = csub(r, md.q);
+    }
+    // MForm: r * 2^64 mod q
+    u64 m = r;
+    for (int b = 0; b < 64; b++) m = csub(m << 1, md.q);
+    ptm[off] = m;
+}
+void launch_prep_pt(const Launch &L, const DeviceTables &T, int level, const u64 *pt, u64 t_mod, u64 *ptm) {
+    int bs = T.n < 256 ? T.n : 256;
+    dim3 g((T.n + bs - 1) / bs, level + 1);
+    k_prep_pt<<<g, bs, 0, L.stream>>>(T.mods, T.logn, pt, t_mod, ptm);
+    count(L);
+}
+
+// ct x pt for one or two plaintexts, reading the matrix ciphertext once
+__global__ void k_mul_pt(const ModDev *mods, int nlimbs, int logn, const u64 *__restrict__ in, uint64_t in_words,
+                         const u64 *__restrict__ ptm0, const u64 *__restrict__ ptm1, u64 *__restrict__ out0,
+                         u64 *__restrict__ out1, uint64_t col_words, int kstride) {
+    // grid: x over N/2, y = poly*nlimbs + limb, z = column
+    const int poly = blockIdx.y / nlimbs, limb = blockIdx.y % nlimbs;
+    const ModDev md = mods[limb];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (1 << (logn - 1))) return;
+    const size_t src = (size_t)blockIdx.z * in_words + (((size_t)poly * nlimbs + limb) << logn);
+    const size_t dst = (size_t)blockIdx.z * col_words + (((size_t)poly * kstride + limb) << logn);
+    ulonglong2 x = reinterpret_cast<const ulonglong2 *>(in + src)[i];
+    ulonglong2 p0 = reinterpret_cast<const ulonglong2 *>(ptm0 + ((size_t)limb << logn))[i];
+    ulonglong2 r;
+    r.x = mont_mul(x.x, p0.x, md.q, md.qinv); r.y = mont_mul(x.y, p0.y, md.q, md.qinv);
+    reinterpret_cast<ulonglong2 *>(out0 + dst)[i] = r;
+    if (ptm1) {
+        ulonglong2 p1 = reinterpret_cast<const ulonglong2 *>(ptm1 + ((size_t)limb << logn))[i];
+        r.x = mont_mul(x.x, p1.x, md.q, md.qinv); r.y = mont_mul(x.y, p1.y, md.q, md.qinv);
+        reinterpret_cast<ulonglong2 *>(out1 + dst)[i] = r;
+    }
+}
+void launch_mul_pt(const Launch &L, const DeviceTables &T, int level, const u64 *in, uint64_t in_words, int ncols,
+                   const u64 *ptm0, const u64 *ptm1, u64 *out0, u64 *out1, uint64_t col_words) {
+    int nl = level + 1, half = T.n / 2, bs = half < 256 ? half : 256;
+    dim3 g((half + bs - 1) / bs, 2 * nl, ncols);
+    // the job col keeps the context-wide limb stride T.k when it is a workspace col, or nl when it is a store entry
+    int kstride = (int)(col_words / 2 >> T.logn);
+    k_mul_pt<<<g, bs, 0, L.stream>>>(T.mods, nl, T.logn, in, in_words, ptm0, ptm1, out0, out1, col_words, kstride);
+    count(L);
+}
+
+// =====================================================================================================
+// single-limb NTT / INTT (test hook; the production kernels fuse these transforms with their neighbours)
+// =====================================================================================================
+template <int LOGN>
+__global__ void __launch_bounds__(1024) k_limb_ntt(const ModDev *mods, const ulonglong2 *tw, int mod_idx, u64 *limb, int inverse) {
+    extern __shared__ u64 sm[];
+    constexpr int N = 1 << LOGN;
+    const ModDev md = mods[mod_idx];
+    const ulonglong2 *t = tw + ((size_t)mod_idx << LOGN);
+    for (int i = threadIdx.x; i < N; i += blockDim.x) sm[PAD(i)] = limb[i];
+    __syncthreads();
+    if (!inverse) {
+        ntt_fwd_smem<LOGN>(sm, t, md.q, 1);
+        for (int i = threadIdx.x; i < N; i += blockDim.x) limb[i] = barrett(sm[PAD(i)], md.q, md.mu);
+    } else {
+        ntt_inv_smem<LOGN>(sm, t, md.q);
+        for (int i = threadIdx.x; i < N; i += blockDim.x) limb[i] = mul_shoup(sm[PAD(i)], md.ninv, md.ninvs, md.q);
+    }
+}
+void launch_limb_ntt(const Launch &L, const DeviceTables &T, int mod_idx, u64 *limb, int inverse) {
+    size_t smem = (size_t)padded_words(T.n) * 8;
+    LMN_DISPATCH_LOGN(T.logn, k_limb_ntt<LG><<<1, ntt_threads(T.n), smem, L.stream>>>(
+                                  T.mods, inverse ? T.tw_inv : T.tw_fwd, mod_idx, limb, inverse));
+    count(L);
+}
+
+// =====================================================================================================
+// Encode eval: one pass of the compiled butterfly plan over a tile of ciphertext slots x 32 coefficients
+// =====================================================================================================
+__global__ void __launch_bounds__(256) k_encode_pass(const EncPassArgs A) {
+    extern __shared__ u64 sm[];  // [tile][ENC_C]
+    const int tile_slots = 1 << A.log_tile;
+    const uint32_t tile = blockIdx.y;
+    const uint64_t lane0 = (uint64_t)blockIdx.x * ENC_C;       // first lane (word offset inside a ciphertext)
+    const int limb = (int)((lane0 >> A.logn) % A.k);
+    const int lane = threadIdx.x & (ENC_C - 1);
+    const int row0 = threadIdx.x / ENC_C, rows_per_it = blockDim.x / ENC_C;
+    const uint32_t slot_base = tile * A.tile_mul;
+
+    // ---- load (slots >= in_count read the shared zero ciphertext: fhe/code.go:24-26) ----
+    for (int l = row0; l < tile_slots; l += rows_per_it) {
+        const uint32_t slot = slot_base + (uint32_t)l * A.stride;
+        const u64 *src;
+        if (A.in_by_pos) src = A.in + (uint64_t)A.out_pos[slot] * A.ct_words;
+        else src = (slot < A.in_count) ? A.in + (uint64_t)slot * A.ct_words : A.zero;
+        sm[l * ENC_C + lane] = src[lane0 + lane];
+    }
+    __syncthreads();
+
+    // ---- butterfly levels ----
+    const ulonglong2 *scal = A.scal + (size_t)limb * A.nscal;
+    const u64 qq = A.mods[limb].q;
+    for (int s = A.s0; s < A.s1; s++) {
+        const int lb = (int)((A.lbits >> (4 * (s - A.s0))) & 15);
+        const uint16_t *sc = A.scale_after + (size_t)s * A.n;
+        for (int p = row0; p < tile_slots / 2; p += rows_per_it) {
+            const int lo = ((p >> lb) << (lb + 1)) | (p & ((1 << lb) - 1));
+            const int hi = lo | (1 << lb);
+            u64 a = sm[lo * ENC_C + lane], b = sm[hi * ENC_C + lane];
+            u64 su = add_mod(a, b, qq), di = sub_mod(a, b, qq);
+            const uint32_t ia = sc[slot_base + (uint32_t)lo * A.stride], ib = sc[slot_base + (uint32_t)hi * A.stride];
+            if (ia) { ulonglong2 w = __ldg(&scal[ia]); su = mul_shoup(su, w.x, w.y, qq); }
+            if (ib) { ulonglong2 w = __ldg(&scal[ib]); di = mul_shoup(di, w.x, w.y, qq); }
+            sm[lo * ENC_C + lane] = su; sm[hi * ENC_C + lane] = di;
+        }
+        __syncthreads();
+    }
+
+    // ---- store to the final position of each slot ----
+    for (int l = row0; l < tile_slots; l += rows_per_it) {
+        const uint32_t slot = slot_base + (uint32_t)l * A.stride;
+        A.out[(uint64_t)A.out_pos[slot] * A.ct_words + lane0 + lane] = sm[l * ENC_C + lane];
+    }
+}
+void launch_encode_pass(const Launch &L, const EncPassArgs &A) {
+    const uint64_t chunks = A.ct_words / ENC_C;
+    const uint32_t tiles = A.n >> A.log_tile;
+    dim3 g((unsigned)chunks, tiles);
+    size_t smem = ((size_t)ENC_C << A.log_tile) * 8;
+    k_encode_pass<<<g, 256, smem, L.stream>>>(A);
+    count(L);
+}
+
+// =====================================================================================================
+// hybrid key switch
+// =====================================================================================================
+// (1) y[i] = INTT(c1[i]) * (Q_d/q_i)^-1 mod q_i        (lattigo DecomposeNTT: INTT of c1, folded with reconstructRNS's y_i)
+template <int LOGN>
+__global__ void __launch_bounds__(1024) k_intt_c1(const ModDev *mods, const ulonglong2 *tw_inv, const KsConsts *C, const KsJobs J, int k) {
+    extern __shared__ u64 sm[];
+    constexpr int N = 1 << LOGN;
+    const int i = blockIdx.x, job = blockIdx.y;
+    const ModDev md = mods[i];
+    const u64 *src = J.col + (size_t)job * J.col_words + ((size_t)(k + i) << LOGN);  // poly 1, limb i
+    u64 *dst = J.y + (size_t)job * J.y_words + ((size_t)i << LOGN);
+    for (int n = threadIdx.x; n < N; n += blockDim.x) sm[PAD(n)] = src[n];
+    __syncthreads();
+    ntt_inv_smem<LOGN>(sm, tw_inv + ((size_t)i << LOGN), md.q);
+    const u64 w = C->intt_w[i], ws = C->intt_ws[i];
+    for (int n = threadIdx.x; n < N; n += blockDim.x) dst[n] = mul_shoup(sm[PAD(n)], w, ws, md.q);
+}
+
+// (2) fold the float64 overflow estimate v of reconstructRNS into the first residue of each multi-prime digit:
+//     y_s0 += (nd - 1 - v) q_s0,  v = floor(sum_a float64(y_a)/float64(q_a))   (same operation order as Go)
+__global__ void k_vfix(const ModDev *mods, const KsConsts *C, const KsJobs J, int logn) {
+    const int d = blockIdx.y, job = blockIdx.z;
+    const int nd = C->dig_size[d], s0 = C->dig_start[d];
+    if (nd < 2) return;
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= (1 << logn)) return;
+    u64 *y = J.y + (size_t)job * J.y_words;
+    double vf = 0.0;
+    for (int a = 0; a < nd; a++) {
+        const u64 ya = y[((size_t)(s0 + a) << logn) + n];
+        vf = __dadd_rn(vf, __ddiv_rn(__ull2double_rn(ya), __ull2double_rn(mods[s0 + a].q)));
+    }
+    const u64 v = __double2ull_rz(vf);
+    y[((size_t)s0 << logn) + n] += (u64)(nd - 1 - (int)v) * mods[s0].q;
+}
+
+// (3) for one target modulus (and one half of the output when the ring is larger than the block transform):
+//     acc_c = sum_d evk[d][c] (.) NTT(ModUp_d(y))       (DecomposeSingleNTT + gadgetProductMultiplePLazy)
+template <int LOGM, int S>
+__global__ void __launch_bounds__(1024) k_mac(const ModDev *mods, const ulonglong2 *tw_fwd, const KsConsts *C,
+                                               const KsJobs J, const u64 *__restrict__ evk) {
+    extern __shared__ u64 sm[];
+    constexpr int M = 1 << LOGM;
+    constexpr int LOGN = LOGM + (S == 2 ? 1 : 0);
+    u64 *data = sm;
+    u64 *acc0 = sm + padded_words(M);
+    u64 *acc1 = acc0 + M;
+    const int tix = blockIdx.x / S, h = blockIdx.x % S, job = blockIdx.y;
+    const int nq = C->nq, k = C->k, KP = k + C->np;
+    const int gm = ks_mod_index(tix, nq, k);
+    const ModDev md = mods[gm];
+    const u64 p = md.q, p2 = 2 * md.q;
+    const ulonglong2 *tw = tw_fwd + ((size_t)gm << LOGN);
+    const u64 *y = J.y + (size_t)job * J.y_words;
+    const u64 *c1 = J.col + (size_t)job * J.col_words + ((size_t)k << LOGN);  // poly 1 (NTT domain)
+    for (int n = threadIdx.x; n < M; n += blockDim.x) { acc0[n] = 0; acc1[n] = 0; }
+
+    const int beta = C->beta;
+    for (int d = 0; d < beta; d++) {
+        const int s0 = C->dig_start[d], nd = C->dig_size[d];
+        const u64 *e0 = evk + ((((size_t)d * 2 + 0) * KP + gm) << LOGN) + (size_t)h * M;
+        const u64 *e1 = evk + ((((size_t)d * 2 + 1) * KP + gm) << LOGN) + (size_t)h * M;
+        if (tix < nq && tix >= s0 && tix < s0 + nd) {
+            // the digit's own limbs are copied from the NTT-domain input (DecomposeSingleNTT)
+            const u64 *x = c1 + ((size_t)tix << LOGN) + (size_t)h * M;
+            for (int n = threadIdx.x; n < M; n += blockDim.x) {
+                const u64 xv = x[n];
+                acc0[n] += mont_mul_lazy(xv, e0[n], p, md.qinv);
+                acc1[n] += mont_mul_lazy(xv, e1[n], p, md.qinv);
+            }
+            continue;
+        }
+        __syncthreads();  // previous digit's readers of `data` are done
+        if (nd == 1) {
+            // single-prime digit: centred lift (DecomposeAndSplit, decompLvl < 0)
+            const u64 qd = mods[s0].q, hq = qd >> 1;
+            const u64 *ys = y + ((size_t)s0 << LOGN);
+            const ulonglong2 w1 = tw[1];
+            for (int n = threadIdx.x; n < M; n += blockDim.x) {
+                u64 vals[S];
+#pragma unroll
+                for (int r = 0; r < S; r++) {
+                    const u64 c = ys[n + r * M];
+                    const bool neg = c >= hq;
+                    const u64 rr = barrett(neg ? qd - c : c, p, md.mu);
+                    vals[r] = neg ? (rr ? p - rr : 0) : rr;
+                }
+                if (S == 2) {
+                    const u64 t = mul_shoup_lazy(vals[1], w1.x, w1.y, p);
+                    data[PAD(n)] = h == 0 ? vals[0] + t : vals[0] - t + p2;
+                } else data[PAD(n)] = vals[0];
+            }
+        } else {
+            u64 cm[MAX_P];
+#pragma unroll
+            for (int a = 0; a < MAX_P; a++) cm[a] = a < nd ? C->mu_c[d][tix][a] : 0;
+            const u64 neg = C->mu_neg[d][tix];
+            const ulonglong2 w1 = tw[1];
+            for (int n = threadIdx.x; n < M; n += blockDim.x) {
+                u64 vals[S];
+#pragma unroll
+                for (int r = 0; r < S; r++) {
+                    u64 lo = 0, hi = neg;
+#pragma unroll
+                    for (int a = 0; a < MAX_P; a++)
+                        if (a < nd) mac128(lo, hi, y[((size_t)(s0 + a) << LOGN) + n + r * M], cm[a]);
+                    vals[r] = csub(mont_reduce_lazy(lo, hi, p, md.qinv), p2);
+                }
+                if (S == 2) {
+                    const u64 t = mul_shoup_lazy(vals[1], w1.x, w1.y, p);
+                    data[PAD(n)] = h == 0 ? vals[0] + t : vals[0] - t + p2;
+                } else data[PAD(n)] = vals[0];
+            }
+        }
+        __syncthreads();
+        ntt_fwd_smem<LOGM>(data, tw, p, S + h);
+        for (int n = threadIdx.x; n < M; n += blockDim.x) {
+            const u64 xv = data[PAD(n)];
+            acc0[n] += mont_mul_lazy(xv, e0[n], p, md.qinv);
+            acc1[n] += mont_mul_lazy(xv, e1[n], p, md.qinv);
+        }
+    }
+    u64 *o0 = J.acc + (size_t)job * J.acc_words + ((size_t)gm << LOGN) + (size_t)h * M;
+    u64 *o1 = o0 + ((size_t)KP << LOGN);
+    for (int n = threadIdx.x; n < M; n += blockDim.x) {
+        o0[n] = barrett(acc0[n], p, md.mu);
+        o1[n] = barrett(acc1[n], p, md.mu);
+    }
+}
+
+// (4) P limbs of the accumulators out of the NTT domain, centred by P/2 and premultiplied by (P/p_j)^-1
+//     (ModDownQPtoQNTT: INTT of the P part, ModUpPtoQ's AddScalar(PHalf) and reconstructRNS's y_j)
+template <int LOGN>
+__global__ void __launch_bounds__(1024) k_pintt(const ModDev *mods, const ulonglong2 *tw_inv, const KsConsts *C, const KsJobs J) {
+    extern __shared__ u64 sm[];
+    constexpr int N = 1 << LOGN;
+    const int j = blockIdx.x, c = blockIdx.y, job = blockIdx.z;
+    const int k = C->k, KP = k + C->np, gm = k + j;
+    const ModDev md = mods[gm];
+    u64 *x = J.acc + (size_t)job * J.acc_words + (((size_t)c * KP + gm) << LOGN);
+    for (int n = threadIdx.x; n < N; n += blockDim.x) sm[PAD(n)] = x[n];
+    __syncthreads();
+    ntt_inv_smem<LOGN>(sm, tw_inv + ((size_t)gm << LOGN), md.q);
+    const u64 w = C->pin_w[j], ws = C->pin_ws[j], ad = C->pin_add[j];
+    for (int n = threadIdx.x; n < N; n += blockDim.x) x[n] = add_mod(mul_shoup(sm[PAD(n)], w, ws, md.q), ad, md.q);
+}
+
+// (5) float64 overflow estimate of the P -> Q conversion folded into the first P residue
+__global__ void k_vpfix(const ModDev *mods, const KsConsts *C, const KsJobs J, int logn) {
+    const int c = blockIdx.y, job = blockIdx.z;
+    const int np = C->np, k = C->k, KP = k + np;
+    if (np < 2) return;
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= (1 << logn)) return;
+    u64 *yp = J.acc + (size_t)job * J.acc_words + (((size_t)c * KP + k) << logn);
+    double vf = 0.0;
+    for (int a = 0; a < np; a++)
+        vf = __dadd_rn(vf, __ddiv_rn(__ull2double_rn(yp[((size_t)a << logn) + n]), __ull2double_rn(mods[k + a].q)));
+    const u64 v = __double2ull_rz(vf);
+    yp[n] += (u64)(np - 1 - (int)v) * mods[k].q;
+}
+
+// (6) ModDown by P, add c0, automorphism, accumulate into the ciphertext:
+//     u_c = (acc_c - NTT(ext_c)) P^-1 (+ c0) ;  mode 0: col_c += pi(u_c)   mode 1: col_c = u_c
+template <int LOGN>
+__global__ void __launch_bounds__(1024) k_down(const ModDev *mods, const ulonglong2 *tw_fwd, const KsConsts *C,
+                                                const KsJobs J, uint32_t gal_el, int mode) {
+    extern __shared__ u64 sm[];
+    constexpr int N = 1 << LOGN;
+    const int i = blockIdx.x, c = blockIdx.y, job = blockIdx.z;
+    const int k = C->k, np = C->np, KP = k + np;
+    const ModDev md = mods[i];
+    const u64 q = md.q, q2 = 2 * md.q;
+    const u64 *accb = J.acc + (size_t)job * J.acc_words + (((size_t)c * KP) << LOGN);
+    const u64 *yp = accb + ((size_t)k << LOGN);
+    u64 cm[MAX_P];
+#pragma unroll
+    for (int a = 0; a < MAX_P; a++) cm[a] = a < np ? C->md_c[i][a] : 0;
+    const u64 neg = C->md_neg[i];
+    for (int n = threadIdx.x; n < N; n += blockDim.x) {
+        u64 lo = 0, hi = neg;
+#pragma unroll
+        for (int a = 0; a < MAX_P; a++)
+            if (a < np) mac128(lo, hi, yp[((size_t)a << LOGN) + n], cm[a]);
+        sm[PAD(n)] = csub(mont_reduce_lazy(lo, hi, q, md.qinv), q2);
+    }
+    __syncthreads();
+    ntt_fwd_smem<LOGN>(sm, tw_fwd + ((size_t)i << LOGN), q, 1);
+    const u64 w = C->pinv_w[i], ws = C->pinv_ws[i];
+    const u64 *aq = accb + ((size_t)i << LOGN);
+    u64 *col = J.col + (size_t)job * J.col_words + (((size_t)c * k + i) << LOGN);
+    for (int n = threadIdx.x; n < N; n += blockDim.x) {
+        const u64 ext = barrett(sm[PAD(n)], q, md.mu);
+        u64 u = mul_shoup(aq[n] + q - ext, w, ws, q);
+        if (c == 0) u = add_mod(u, col[n], q);
+        if (mode == 1) col[n] = u; else sm[PAD(n)] = u;
+    }
+    if (mode == 1) return;
+    __syncthreads();
+    for (int n = threadIdx.x; n < N; n += blockDim.x) {
+        const unsigned src = auto_index((unsigned)n, gal_el, LOGN);
+        col[n] = add_mod(col[n], sm[PAD(src)], q);
+    }
+}
+
+void launch_rotate_accumulate(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch,
+                              const KsJobs &J, const u64 *evk, uint32_t gal_el) {
+    const int N = T.n, nq = Ch.nq, np = Ch.np, jobs = J.jobs;
+    const size_t sm_full = (size_t)padded_words(N) * 8;
+    const int nt_full = ntt_threads(N);
+    LMN_DISPATCH_LOGN(T.logn, k_intt_c1<LG><<<dim3(nq, jobs), nt_full, sm_full, L.stream>>>(T.mods, T.tw_inv, Cd, J, Ch.k));
+    count(L);
+    bool multi = false;
+    for (int d = 0; d < Ch.beta; d++) multi |= Ch.dig_size[d] > 1;
+    if (multi) {
+        int bs = N < 256 ? N : 256;
+        k_vfix<<<dim3((N + bs - 1) / bs, Ch.beta, jobs), bs, 0, L.stream>>>(T.mods, Cd, J, T.logn);
+        count(L);
+    }
+    if (T.logn <= 13) {
+        const size_t smm = ((size_t)padded_words(N) + 2 * (size_t)N) * 8;
+        LMN_DISPATCH_LOGN(T.logn, k_mac<(LG <= 13 ? LG : 13), 1><<<dim3(nq + np, jobs), nt_full, smm, L.stream>>>(
+                                      T.mods, T.tw_fwd, Cd, J, evk));
+    } else {
+        const int M = N / 2;
+        const size_t smm = ((size_t)padded_words(M) + 2 * (size_t)M) * 8;
+        k_mac<13, 2><<<dim3((nq + np) * 2, jobs), ntt_threads(M), smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk);
+    }
+    count(L);
+    LMN_DISPATCH_LOGN(T.logn, k_pintt<LG><<<dim3(np, 2, jobs), nt_full, sm_full, L.stream>>>(T.mods, T.tw_inv, Cd, J));
+    count(L);
+    if (np > 1) {
+        int bs = N < 256 ? N : 256;
+        k_vpfix<<<dim3((N + bs - 1) / bs, 2, jobs), bs, 0, L.stream>>>(T.mods, Cd, J, T.logn);
+        count(L);
+    }
+    LMN_DISPATCH_LOGN(T.logn, k_down<LG><<<dim3(nq, 2, jobs), nt_full, sm_full, L.stream>>>(T.mods, T.tw_fwd, Cd, J, gal_el,
+                                                                                        gal_el == 0 ? 1 : 0));
+    count(L);
+}
+
+void launch_keyswitch_level0(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch,
+                             const KsJobs &J, const u64 *evk) {
+    launch_rotate_accumulate(L, T, Cd, Ch, J, evk, 0 /* mode 1: replace, no automorphism */);
+}
+
+// =====================================================================================================
+// Rescale (bgv.Evaluator.Rescale -> ring.DivRoundByLastModulusNTT)
+// =====================================================================================================
+template <int LOGN>
+__global__ void __launch_bounds__(1024) k_rs_intt(const ModDev *mods, const ulonglong2 *tw_inv, const RescaleConsts *R, const KsJobs J, int k,
+                          int level) {
+    extern __shared__ u64 sm[];
+    constexpr int N = 1 << LOGN;
+    const int c = blockIdx.x, job = blockIdx.y;
+    const ModDev md = mods[level];
+    const u64 *x = J.col + (size_t)job * J.col_words + (((size_t)c * k + level) << LOGN);
+    u64 *r = J.acc + (size_t)job * J.acc_words + ((size_t)c << LOGN);
+    for (int n = threadIdx.x; n < N; n += blockDim.x) sm[PAD(n)] = x[n];
+    __syncthreads();
+    ntt_inv_smem<LOGN>(sm, tw_inv + ((size_t)level << LOGN), md.q);
+    const u64 half = R->half;
+    for (int n = threadIdx.x; n < N; n += blockDim.x)
+        r[n] = add_mod(mul_shoup(sm[PAD(n)], md.ninv, md.ninvs, md.q), half, md.q);
+}
+template <int LOGN>
+__global__ void __launch_bounds__(1024) k_rs_apply(const ModDev *mods, const ulonglong2 *tw_fwd, const RescaleConsts *R, const KsJobs J, int k) {
+    extern __shared__ u64 sm[];
+    constexpr int N = 1 << LOGN;
+    const int i = blockIdx.x, c = blockIdx.y, job = blockIdx.z;
+    const ModDev md = mods[i];
+    const u64 q = md.q;
+    const u64 *r = J.acc + (size_t)job * J.acc_words + ((size_t)c << LOGN);
+    const u64 hm = R->half_mod[i];
+    for (int n = threadIdx.x; n < N; n += blockDim.x) sm[PAD(n)] = sub_mod(barrett(r[n], q, md.mu), hm, q);
+    __syncthreads();
+    ntt_fwd_smem<LOGN>(sm, tw_fwd + ((size_t)i << LOGN), q, 1);
+    u64 *x = J.col + (size_t)job * J.col_words + (((size_t)c * k + i) << LOGN);
+    const u64 w = R->qlinv_w[i], ws = R->qlinv_ws[i];
+    for (int n = threadIdx.x; n < N; n += blockDim.x)
+        x[n] = mul_shoup(x[n] + q - barrett(sm[PAD(n)], q, md.mu), w, ws, q);
+}
+void launch_rescale_step(const Launch &L, const DeviceTables &T, const RescaleConsts *Rd, int level, const KsJobs &J) {
+    const size_t smf = (size_t)padded_words(T.n) * 8;
+    const int nt = ntt_threads(T.n);
+    LMN_DISPATCH_LOGN(T.logn, k_rs_intt<LG><<<dim3(2, J.jobs), nt, smf, L.stream>>>(T.mods, T.tw_inv, Rd, J, T.k, level));
+    count(L);
+    LMN_DISPATCH_LOGN(T.logn, k_rs_apply<LG><<<dim3(level, 2, J.jobs), nt, smf, L.stream>>>(T.mods, T.tw_fwd, Rd, J, T.k));
+    count(L);
+}
+
+// =====================================================================================================
+// data movement between stores and the job workspace
+// =====================================================================================================
+__global__ void k_pack_out(const KsJobs J, int k, int nl, int logn, u64 *__restrict__ out) {
+    // grid: x over N/2, y = poly*nl + limb, z = job
+    const int poly = blockIdx.y / nl, limb = blockIdx.y % nl;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (1 << (logn - 1))) return;
+    const u64 *src = J.col + (size_t)blockIdx.z * J.col_words + (((size_t)poly * k + limb) << logn);
+    u64 *dst = out + (((size_t)blockIdx.z * 2 * nl + (size_t)poly * nl + limb) << logn);
+    reinterpret_cast<ulonglong2 *>(dst)[i] = reinterpret_cast<const ulonglong2 *>(src)[i];
+}
+void launch_pack_out(const Launch &L, const DeviceTables &T, const KsJobs &J, int nl, u64 *out) {
+    int half = T.n / 2, bs = half < 256 ? half : 256;
+    k_pack_out<<<dim3((half + bs - 1) / bs, 2 * nl, J.jobs), bs, 0, L.stream>>>(J, T.k, nl, T.logn, out);
+    count(L);
+}
+__global__ void k_gather_in(const u64 *__restrict__ src, uint64_t src_words, const uint32_t *__restrict__ idx, const KsJobs J,
+                            int k, int logn) {
+    // grid: x over N/2, y = poly*k + limb, z = job ; source cts are at max level (k limbs)
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (1 << (logn - 1))) return;
+    const u64 *s = src + (size_t)idx[blockIdx.z] * src_words + ((size_t)blockIdx.y << logn);
+    u64 *d = J.col + (size_t)blockIdx.z * J.col_words + ((size_t)blockIdx.y << logn);
+    reinterpret_cast<ulonglong2 *>(d)[i] = reinterpret_cast<const ulonglong2 *>(s)[i];
+}
+void launch_gather_in(const Launch &L, const DeviceTables &T, const u64 *src, uint64_t src_words, const uint32_t *idx,
+                      const KsJobs &J) {
+    int half = T.n / 2, bs = half < 256 ? half : 256;
+    k_gather_in<<<dim3((half + bs - 1) / bs, 2 * T.k, J.jobs), bs, 0, L.stream>>>(src, src_words, idx, J, T.k, T.logn);
+    count(L);
+}
+
+// ring switch tail (rlwe.SwitchCiphertextRingDegreeNTT, large -> small): INTT in the large ring, keep every
+// (N/Ns)-th coefficient, NTT in the small ring of the same prime
+template <int LOGN, int LOGS>
+__global__ void __launch_bounds__(1024) k_ring_decimate(const ModDev *mods, const ulonglong2 *tw_inv, const KsJobs J, int k, const ModDev *smod,
+                                const ulonglong2 *stw, u64 *__restrict__ out) {
+    extern __shared__ u64 sm[];
+    constexpr int N = 1 << LOGN, NS = 1 << LOGS;
+    const int c = blockIdx.x, job = blockIdx.y;
+    const ModDev md = mods[0];
+    const u64 *x = J.col + (size_t)job * J.col_words + (((size_t)c * k) << LOGN);
+    for (int n = threadIdx.x; n < N; n += blockDim.x) sm[PAD(n)] = x[n];
+    __syncthreads();
+    ntt_inv_smem<LOGN>(sm, tw_inv, md.q);
+    // decimate into the front of a second region (padded layout of the small transform)
+    u64 *sm2 = sm + padded_words(N);
+    for (int n = threadIdx.x; n < NS; n += blockDim.x)
+        sm2[PAD(n)] = mul_shoup(sm[PAD(n << (LOGN - LOGS))], md.ninv, md.ninvs, md.q);
+    __syncthreads();
+    ntt_fwd_smem<LOGS>(sm2, stw, md.q, 1);
+    u64 *o = out + (((size_t)job * 2 + c) << LOGS);
+    for (int n = threadIdx.x; n < NS; n += blockDim.x) o[n] = barrett(sm2[PAD(n)], md.q, smod->mu);
+}
+void launch_ring_decimate(const Launch &L, const DeviceTables &T, const KsJobs &J, int logns, const ModDev *small_mod,
+                          const ulonglong2 *small_tw_fwd, u64 *out) {
+    const size_t smem = ((size_t)padded_words(T.n) + padded_words(1 << logns)) * 8;
+    const int nt = ntt_threads(T.n);
+#define RD(LN, LS) k_ring_decimate<LN, LS><<<dim3(2, J.jobs), nt, smem, L.stream>>>(T.mods, T.tw_inv, J, T.k, small_mod, small_tw_fwd, out)
+    if (logns == 10) { if (T.logn == 12) RD(12, 10); else if (T.logn == 13) RD(13, 10); else if (T.logn == 14) RD(14, 10); }
+    else if (logns == 6) { if (T.logn == 8) RD(8, 6); else if (T.logn == 10) RD(10, 6); }
+    else if (logns == 8) { if (T.logn == 10) RD(10, 8); else if (T.logn == 12) RD(12, 8); }
+#undef RD
+    count(L);
+}
+
+// =====================================================================================================
+const char *kernels_init() {
+    cudaError_t e = cudaSuccess;
+    const int maxsm = 227 * 1024;
+#define SETSM(K) do { if (e == cudaSuccess) e = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, maxsm); } while (0)
+#define SET_LOGN(LG)                       \
+    SETSM(k_limb_ntt<LG>); SETSM(k_intt_c1<LG>); SETSM(k_pintt<LG>); SETSM(k_down<LG>); \
+    SETSM(k_rs_intt<LG>); SETSM(k_rs_apply<LG>);
+    SET_LOGN(6) SET_LOGN(8) SET_LOGN(10) SET_LOGN(12) SET_LOGN(13) SET_LOGN(14)
+    SETSM((k_mac<6, 1>)); SETSM((k_mac<8, 1>)); SETSM((k_mac<10, 1>)); SETSM((k_mac<12, 1>)); SETSM((k_mac<13, 1>));
+    SETSM((k_mac<13, 2>));
+    SETSM(k_encode_pass);
+    SETSM((k_ring_decimate<12, 10>)); SETSM((k_ring_decimate<13, 10>)); SETSM((k_ring_decimate<14, 10>));
+    SETSM((k_ring_decimate<8, 6>)); SETSM((k_ring_decimate<10, 6>)); SETSM((k_ring_decimate<10, 8>)); SETSM((k_ring_decimate<12, 8>));
+#undef SET_LOGN
+#undef SETSM
+    return e == cudaSuccess ? nullptr : cudaGetErrorString(e);
+}
+
+}  // namespace lmn

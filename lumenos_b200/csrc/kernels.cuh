@@ -1,0 +1,109 @@
+// Kernel argument blocks and host launchers of liblumenos_b200 (definitions in kernels.cu).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "device.cuh"
+
+namespace lmn {
+
+constexpr int MAX_LIMBS = 28;   // Q limbs + P limbs
+constexpr int MAX_P = 4;
+constexpr int MAX_DIGITS = 14;
+constexpr int ENC_C = 32;       // contiguous coefficients per Encode tile row (256 B)
+constexpr int ENC_MAX_TILE = 256;
+
+// constants of the hybrid key-switch at one level (built on the host, resident in HBM)
+struct KsConsts {
+    int nq, np, beta, k;                       // Q limbs in use, P limbs, digits, total Q limbs (evk / col stride)
+    int dig_start[MAX_DIGITS], dig_size[MAX_DIGITS];
+    u64 intt_w[MAX_LIMBS], intt_ws[MAX_LIMBS];               // N^-1 (Q_d/q_i)^-1 mod q_i (Shoup pair)
+    u64 mu_c[MAX_DIGITS][MAX_LIMBS][MAX_P];                  // (Q_d/q_a mod m_tm) * 2^64 mod m_tm   [digit][target][a]
+    u64 mu_neg[MAX_DIGITS][MAX_LIMBS];                       // -(nd-1) Q_d mod m_tm
+    u64 pin_w[MAX_P], pin_ws[MAX_P], pin_add[MAX_P];         // N^-1 (P/p_j)^-1 mod p_j ; half_j (P/p_j)^-1 mod p_j
+    u64 md_c[MAX_LIMBS][MAX_P];                              // (P/p_a mod q_i) * 2^64 mod q_i
+    u64 md_neg[MAX_LIMBS];                                   // -((np-1) P + Phalf) mod q_i
+    u64 pinv_w[MAX_LIMBS], pinv_ws[MAX_LIMBS];               // P^-1 mod q_i
+};
+// target index tix in [0, nq+np): modulus index in the global table
+__host__ __device__ inline int ks_mod_index(int tix, int nq, int k) { return tix < nq ? tix : k + (tix - nq); }
+
+struct RescaleConsts {   // DivRoundByLastModulusNTT from level l (limb l dropped)
+    u64 half;                        // (q_l - 1) / 2
+    u64 half_mod[MAX_LIMBS];         // half mod q_i
+    u64 qlinv_w[MAX_LIMBS], qlinv_ws[MAX_LIMBS];
+};
+
+struct DeviceTables {
+    int logn, n, k, np;
+    const ModDev *mods;              // [k+np (+1 small-ring modulus)]
+    const ulonglong2 *tw_fwd;        // [k+np][N]
+    const ulonglong2 *tw_inv;        // [k+np][N]
+};
+
+struct EncPassArgs {
+    const ModDev *mods;
+    const u64 *in;          // slot- or position-indexed input cts
+    const u64 *zero;        // ciphertext used for slots >= in_count (nullptr: none)
+    u64 *out;               // position-indexed output cts
+    uint32_t in_count;      // slots >= in_count read `zero`
+    int in_by_pos;          // 1: input ct of slot s is in[out_pos[s]], 0: in[s]
+    const uint16_t *scale_after;  // [logn][n]
+    const uint32_t *out_pos;      // [n]
+    const ulonglong2 *scal;       // [k][nscal]
+    uint32_t nscal, n;
+    int log_tile, s0, s1;   // tile = 2^log_tile slots, levels [s0, s1)
+    uint32_t tile_mul, stride;    // slot = tile*tile_mul + local*stride
+    uint64_t lbits;         // 4 bits per level: local index bit of level s0+i
+    int k;                  // Q limbs per poly
+    int logn;               // ring degree
+    uint64_t ct_words;      // words per ciphertext (2*k*N)
+};
+
+struct Launch {
+    cudaStream_t stream;
+    uint64_t *counter;      // kernel launch counter
+};
+
+// ---- elementwise / operator level ----
+void launch_addsub(const Launch &L, const DeviceTables &T, int level, const u64 *a, const u64 *b, u64 *o, int sub);
+void launch_mul_scalar(const Launch &L, const DeviceTables &T, int level, const u64 *a, const ulonglong2 *w_per_limb, u64 *o);
+// ptm[i][n] = (pt * T mod q_i) * 2^64 mod q_i
+void launch_prep_pt(const Launch &L, const DeviceTables &T, int level, const u64 *pt, u64 t_mod, u64 *ptm);
+// out_x[job] = in[col] * ptm_x  (x = 0,1; ptm1 may be null); in: cts with stride in_words; out: job cols with stride col_words
+void launch_mul_pt(const Launch &L, const DeviceTables &T, int level, const u64 *in, uint64_t in_words, int ncols,
+                   const u64 *ptm0, const u64 *ptm1, u64 *out0, u64 *out1, uint64_t col_words);
+void launch_limb_ntt(const Launch &L, const DeviceTables &T, int mod_idx, u64 *limb, int inverse);
+
+// ---- Encode ----
+void launch_encode_pass(const Launch &L, const EncPassArgs &A);
+
+// ---- key switch + automorphism + accumulate, for `jobs` columns laid out with fixed strides ----
+struct KsJobs {
+    u64 *col;  uint64_t col_words;   // [jobs][2][k][N]
+    u64 *y;    uint64_t y_words;     // [jobs][k][N]
+    u64 *acc;  uint64_t acc_words;   // [jobs][2][k+np][N]
+    int jobs;
+};
+// col += pi_galEl( keyswitch(col) )      (AutomorphismHoisted + Add, lattigo rlwe/inner_sum.go)
+void launch_rotate_accumulate(const Launch &L, const DeviceTables &T, const KsConsts *ksc_dev, const KsConsts &ksc_host,
+                              const KsJobs &J, const u64 *evk, uint32_t gal_el);
+// plain key switch without automorphism into (out0,out1) = (u0 + c0, u1) at level 0 (ring switch)
+// one Rescale step from level l on every job's col (in place, limb l dropped)
+void launch_rescale_step(const Launch &L, const DeviceTables &T, const RescaleConsts *rc_dev, int level,
+                         const KsJobs &J);
+// copy limbs 0..nl-1 of both polys of each job col into a packed store [jobs][2][nl][N]
+void launch_pack_out(const Launch &L, const DeviceTables &T, const KsJobs &J, int nl, u64 *out);
+// gather cts: col[j] = src[idx[j]] (idx on device)
+void launch_gather_in(const Launch &L, const DeviceTables &T, const u64 *src, uint64_t src_words, const uint32_t *idx,
+                      const KsJobs &J);
+// ring switch tail: per job, limb 0 of both polys: INTT (large), decimate by N/Ns, NTT (small) -> out [jobs][2][Ns]
+void launch_ring_decimate(const Launch &L, const DeviceTables &T, const KsJobs &J, int logns, const ModDev *small_mod,
+                          const ulonglong2 *small_tw_fwd, u64 *out);
+// key switch at level 0 without automorphism: col[0][0] += u0 ; col[1][0] = u1
+void launch_keyswitch_level0(const Launch &L, const DeviceTables &T, const KsConsts *ksc_dev, const KsConsts &ksc_host,
+                             const KsJobs &J, const u64 *evk);
+
+const char *kernels_init();  // sets dynamic shared memory attributes; returns nullptr or error string
+
+}  // namespace lmn

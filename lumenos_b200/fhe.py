@@ -1,0 +1,387 @@
+"""Host-side mirror of the reference's `fhe` package surface for the accelerated path, over the C ABI.
+
+Same names, argument meaning and error behaviour as the Go interface (ChainSafe/lumenos @ 9f33d62):
+    GenerateBGVParamsForNTT   fhe/bfv.go:121-188        ServerBFV            fhe/bfv.go:13-58
+    Encode                    fhe/code.go:8-34          NTT                  fhe/ntt.go:12-17
+    LigeroCommitter.Commit    fhe/ligero.go:95-124      LigeroProver.Prove   fhe/ligero.go:194-291
+    matrixInnerSumEval        fhe/ligero.go:299-370     RingSwitchServer     fhe/ring_switch.go:93-113
+What stays on the Go host in the reference (keys, encryption, the merlin transcript, Merkle tree, wire
+format) is passed in as data: plaintexts, Galois keys, the zero-column ciphertext and query indices.
+Ciphertexts live in device-resident stores; numpy is used only to carry host buffers into ctypes.
+"""
+import ctypes as C
+import math
+
+import numpy as np
+
+from . import _capi
+from ._capi import LumenosError, check  # noqa: F401
+
+DEFAULT = 0xFFFFFFFF
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _u64(a):
+    a = np.ascontiguousarray(a, dtype=np.uint64)
+    return a
+
+
+def GenerateBGVParamsForNTT(nttSize, logN, plaintextModulus):
+    """ref: fhe/bfv.go:121-188.  Returns the bgv.ParametersLiteral fields (prime generation is the host's)."""
+    if nttSize < 2:
+        raise ValueError("nttSize must be >= 2")
+    if logN <= 0:
+        raise ValueError("logN must be positive")
+    two_n = 2 << logN
+    if plaintextModulus % two_n != 1:
+        raise ValueError("plaintextModulus T (%d) does not satisfy T = 1 (mod 2N) (2N=%d)" % (plaintextModulus, two_n))
+    buffer_levels = 0 if plaintextModulus.bit_length() > 45 else -2
+    k = (nttSize & -nttSize).bit_length() - 1 + buffer_levels
+    return {"LogN": logN, "LogQ": [58] + [56] * (k - 1), "LogP": [55, 55], "PlaintextModulus": plaintextModulus}
+
+
+def calculateQueries(securityBits, rhoInv):
+    """ref: fhe/ligero.go:65-71"""
+    term = math.log2(1.0 + 1.0 / rhoInv)
+    if 1.0 - term <= 0:
+        return 0
+    return int(math.ceil(securityBits / (1.0 - term)))
+
+
+class BGVParameters:
+    """bgv.Parameters as the host holds them: moduli and the primitive 2N-th roots its rings use."""
+
+    def __init__(self, logN, Q, P, T, psi_q, psi_p):
+        self.logN, self.N, self.T = int(logN), 1 << int(logN), int(T)
+        self.Q, self.P = _u64(Q), _u64(P)
+        self.psi_q, self.psi_p = _u64(psi_q), _u64(psi_p)
+
+    def MaxLevel(self):
+        return len(self.Q) - 1
+
+    def GaloisElement(self, k):
+        return pow(5, k % (self.N // 2), 2 * self.N)
+
+    def GaloisElementsForInnerSum(self, batch, n):
+        """lattigo bgv.Parameters.GaloisElementsForInnerSum(1, n) (ref: fhe/ligero_test.go:53)"""
+        m = min(n * batch, self.N // 2)
+        g, s = [], batch
+        while s < m:
+            g.append(self.GaloisElement(s))
+            s <<= 1
+        if n * batch == self.N:
+            g.append(2 * self.N - 1)
+        return g
+
+
+class CiphertextStore:
+    """Device-resident []*rlwe.Ciphertext (ref: LigeroProver{Matrix, EncodedMatrix}, fhe/ligero.go:32-37)."""
+
+    def __init__(self, backend, count, level=None, small=False, wrap_ptr=None):
+        self.backend = backend
+        h = C.c_void_p()
+        L = _capi.lib()
+        if small:
+            check(L.lmn_store_create_small(backend.ctx, count, C.byref(h)))
+            self.N = 1 << backend.ring_switch_logn
+        else:
+            level = backend.params.MaxLevel() if level is None else level
+            if wrap_ptr is not None:
+                check(L.lmn_store_wrap(backend.ctx, wrap_ptr, count, level, C.byref(h)))
+            else:
+                check(L.lmn_store_create(backend.ctx, count, level, C.byref(h)))
+            self.N = backend.params.N
+        self.h = h
+        self.count = count
+        self.level = L.lmn_store_level(h)
+        self.scale = 1   # rlwe.MetaData.Scale (mod T), tracked on the host as in the reference
+
+    def __len__(self):
+        return self.count
+
+    def shape(self, count=None):
+        return (self.count if count is None else count, 2, self.level + 1, self.N)
+
+    def upload(self, cts, first=0):
+        cts = _u64(cts)
+        n = cts.size // (2 * (self.level + 1) * self.N)
+        check(_capi.lib().lmn_store_upload(self.h, first, n, _ptr(cts)))
+        return self
+
+    def upload_limb(self, ct, poly, limb, data):
+        data = _u64(data)
+        check(_capi.lib().lmn_store_upload_limb(self.h, ct, poly, limb, _ptr(data)))
+
+    def download(self, first=0, count=None):
+        count = self.count - first if count is None else count
+        out = np.empty(self.shape(count), np.uint64)
+        check(_capi.lib().lmn_store_download(self.h, first, count, _ptr(out)))
+        return out
+
+    def download_limb(self, ct, poly, limb):
+        out = np.empty(self.N, np.uint64)
+        check(_capi.lib().lmn_store_download_limb(self.h, ct, poly, limb, _ptr(out)))
+        return out
+
+    @property
+    def device_ptr(self):
+        return _capi.lib().lmn_store_device_ptr(self.h)
+
+    @property
+    def nbytes(self):
+        return _capi.lib().lmn_store_bytes(self.h)
+
+    def free(self):
+        if self.h:
+            _capi.lib().lmn_store_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class PrimeField:
+    """core.PrimeField as far as the path reads it (ref: core/field.go:29-47): N() and RootForwardUint64(i).
+    The table itself is the host's (it comes from Lattigo's ring.SubRing)."""
+
+    def __init__(self, modulus, roots_forward):
+        self.modulus = int(modulus)
+        self.roots = _u64(roots_forward)
+
+    def N(self):
+        return len(self.roots)
+
+    def Modulus(self):
+        return self.modulus
+
+    def RootForwardUint64(self, i):
+        return int(self.roots[i])
+
+
+class RingSwitchServer:
+    """ref: fhe/ring_switch.go:93-113"""
+
+    def __init__(self, backend, ringSwitchEvk, logN_small, psi_small=0):
+        check(_capi.lib().lmn_load_ring_switch_key(backend.ctx, logN_small, _ptr(_u64(ringSwitchEvk)), psi_small))
+        backend.ring_switch_logn = logN_small
+        self.backend = backend
+
+    def RingSwitchNew(self, store):
+        out = CiphertextStore(self.backend, store.count, small=True)
+        check(_capi.lib().lmn_ring_switch(self.backend.ctx, store.h, out.h))
+        out.scale = store.scale
+        return out
+
+
+class ServerBFV:
+    """ref: fhe/bfv.go:13-58 (operator boundary of the path).  One instance = one GPU."""
+
+    def __init__(self, ptField, params, device=0, scalar_centered=DEFAULT, moddown_round_nearest=DEFAULT,
+                 innersum_rowswap_last=DEFAULT, stream=None):
+        self.ptField, self.params = ptField, params
+        p = _capi.LmnParams()
+        p.log_n, p.num_q, p.num_p, p.t = params.logN, len(params.Q), len(params.P), params.T
+        p.q, p.p = params.Q.ctypes.data_as(_capi.u64p), params.P.ctypes.data_as(_capi.u64p)
+        p.psi_q, p.psi_p = params.psi_q.ctypes.data_as(_capi.u64p), params.psi_p.ctypes.data_as(_capi.u64p)
+        p.scalar_centered, p.moddown_round_nearest = scalar_centered, moddown_round_nearest
+        p.innersum_rowswap_last = innersum_rowswap_last
+        h = C.c_void_p()
+        check(_capi.lib().lmn_ctx_create(C.byref(p), device, C.byref(h)))
+        self.ctx = h
+        self.device = device
+        self.rs = None
+        self.ring_switch_logn = 0
+        self.mulCounter = 0
+        self._plans = {}
+        if stream is not None:
+            self.SetStream(stream)
+
+    # -- plumbing --
+    def SetStream(self, cuda_stream_ptr):
+        check(_capi.lib().lmn_ctx_set_stream(self.ctx, cuda_stream_ptr))
+
+    def Synchronize(self):
+        check(_capi.lib().lmn_ctx_synchronize(self.ctx))
+
+    def SetBatch(self, jobs):
+        check(_capi.lib().lmn_ctx_set_batch(self.ctx, jobs))
+
+    def LaunchCount(self):
+        return _capi.lib().lmn_ctx_launch_count(self.ctx)
+
+    def Close(self):
+        for pl in self._plans.values():
+            _capi.lib().lmn_plan_destroy(pl)
+        self._plans = {}
+        if self.ctx:
+            _capi.lib().lmn_ctx_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.Close()
+        except Exception:
+            pass
+
+    # -- reference surface --
+    def Field(self):
+        return self.ptField
+
+    def MulCounter(self):
+        return self.mulCounter
+
+    def SetRingSwitchServer(self, rs):
+        self.rs = rs
+
+    def RingSwitch(self):
+        return self.rs
+
+    def LoadGaloisKey(self, galEl, evk):
+        """rlwe.MemEvaluationKeySet entry: evk = gk.Value[d][0][c] (Q then P limbs), NTT + Montgomery"""
+        check(_capi.lib().lmn_load_galois_key(self.ctx, int(galEl), _ptr(_u64(evk))))
+
+    def NewStore(self, count, level=None):
+        return CiphertextStore(self, count, level)
+
+    def _plan(self, cols, rhoInv):
+        key = (cols, rhoInv)
+        if key not in self._plans:
+            if self.ptField.N() != cols * rhoInv:
+                raise ValueError("plaintext field degree %d does not match the codeword length %d" % (self.ptField.N(), cols * rhoInv))
+            h = C.c_void_p()
+            check(_capi.lib().lmn_plan_create(self.ctx, cols, rhoInv, _ptr(self.ptField.roots), C.byref(h)))
+            self._plans[key] = h
+        return self._plans[key]
+
+    def PlanCounts(self, cols, rhoInv):
+        a, s, m = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        check(_capi.lib().lmn_plan_counts(self._plan(cols, rhoInv), C.byref(a), C.byref(s), C.byref(m)))
+        return a.value, s.value, m.value
+
+    # operator level: operands are (store, index) pairs
+    def Add(self, op0, op1, opOut):
+        check(_capi.lib().lmn_ct_add(self.ctx, op0[0].h, op0[1], op1[0].h, op1[1], opOut[0].h, opOut[1]))
+
+    def Sub(self, op0, op1, opOut):
+        check(_capi.lib().lmn_ct_sub(self.ctx, op0[0].h, op0[1], op1[0].h, op1[1], opOut[0].h, opOut[1]))
+
+    def Mul(self, op0, scalar, opOut):
+        self.mulCounter += 1
+        check(_capi.lib().lmn_ct_mul_scalar(self.ctx, op0[0].h, op0[1], int(scalar), opOut[0].h, opOut[1]))
+
+    def MulNew(self, op0, plaintext, opOut):
+        self.mulCounter += 1
+        check(_capi.lib().lmn_ct_mul_pt(self.ctx, op0[0].h, op0[1], _ptr(_u64(plaintext)), opOut[0].h, opOut[1]))
+
+    def InnerSum(self, op, batchSize, n):
+        if batchSize != 1:
+            raise ValueError("the path uses InnerSum(ct, 1, rows) only (fhe/ligero.go:325)")
+        check(_capi.lib().lmn_ct_inner_sum(self.ctx, op[0].h, op[1], n))
+
+    def Rescale(self, op0, opOut):
+        check(_capi.lib().lmn_ct_rescale(self.ctx, op0[0].h, op0[1], opOut[0].h, opOut[1]))
+
+    def CopyNew(self, op0, opOut):
+        check(_capi.lib().lmn_ct_copy(self.ctx, op0[0].h, op0[1], opOut[0].h, opOut[1]))
+
+    def RescaleScale(self, from_level, to_level):
+        return _capi.lib().lmn_rescale_scale(self.ctx, from_level, to_level)
+
+
+def NTT(values, size, backend):
+    """ref: fhe/ntt.go:12-17 (len(values) == size).  Returns a new store holding the returned slice."""
+    if values.count != size:
+        raise ValueError("this build evaluates whole-slice transforms: len(values) must equal size")
+    out = backend.NewStore(size)
+    rho = 1
+    check(_capi.lib().lmn_ntt(backend.ctx, backend._plan(size, rho), values.h, out.h))
+    a, s, m = backend.PlanCounts(size, rho)
+    backend.mulCounter += m
+    return out
+
+
+def Encode(matrix, rows, rhoInv, backend, zeroCol):
+    """ref: fhe/code.go:8-34.  zeroCol: (store, index) of the host-produced encryption of the zero vector."""
+    cols = matrix.count
+    encoded = backend.NewStore(cols * rhoInv)
+    check(_capi.lib().lmn_encode(backend.ctx, backend._plan(cols, rhoInv), matrix.h, zeroCol[0].h, zeroCol[1], encoded.h))
+    backend.mulCounter += backend.PlanCounts(cols, rhoInv)[2]
+    return encoded
+
+
+def matrixInnerSumEval(matrix, plaintext, rows, backend):
+    """ref: fhe/ligero.go:299-370.  plaintext: [k][N] NTT-domain limbs of the bgv plaintext."""
+    lout = min(1, backend.params.MaxLevel())
+    out = backend.NewStore(matrix.count, lout)
+    check(_capi.lib().lmn_inner_product(backend.ctx, matrix.h, _ptr(_u64(plaintext)), rows, out.h))
+    out.scale = backend.RescaleScale(backend.params.MaxLevel(), lout)
+    if backend.RingSwitch() is not None:
+        out = backend.RingSwitch().RingSwitchNew(out)
+    return out
+
+
+class LigeroMetadata:
+    def __init__(self, rows, cols, rhoInv, queries):
+        self.Rows, self.Cols, self.RhoInv, self.Queries = rows, cols, rhoInv, queries
+
+
+class EncryptedProof:
+    """ref: fhe/ligero.go:185-192 (Merkle paths and root stay on the host)"""
+
+    def __init__(self, metadata, matR, matZ, queriedCols):
+        self.Metadata, self.MatR, self.MatZ, self.QueriedCols = metadata, matR, matZ, queriedCols
+
+
+class LigeroProver:
+    """ref: fhe/ligero.go:32-37, 194-291"""
+
+    def __init__(self, committer, matrix, encoded):
+        self.Committer, self.Matrix, self.EncodedMatrix = committer, matrix, encoded
+
+    def Prove(self, rPt, bPt, queryIndices, backend):
+        """rPt / bPt: plaintext limbs of backend.Encode(r) and backend.Encode(b) (ligero.go:202-221);
+        queryIndices: sampleQueryIndices(transcript, Queries, cols*rhoInv) (ligero.go:266, 638-644)."""
+        md = self.Committer
+        lib = _capi.lib()
+        lout = min(1, backend.params.MaxLevel())
+        matR = backend.NewStore(self.Matrix.count, lout)
+        matZ = backend.NewStore(self.Matrix.count, lout)
+        # InnerProduct(Matrix, r) and InnerProduct(Matrix, b): the two goroutines of ligero.go:231-242, fused
+        check(lib.lmn_inner_product2(backend.ctx, self.Matrix.h, _ptr(_u64(rPt)), _ptr(_u64(bPt)), md.Rows, matR.h, matZ.h))
+        matR.scale = matZ.scale = backend.RescaleScale(backend.params.MaxLevel(), lout)
+        if backend.RingSwitch() is not None:
+            matR = backend.RingSwitch().RingSwitchNew(matR)
+            matZ = backend.RingSwitch().RingSwitchNew(matZ)
+        # Query columns (ligero.go:262-280)
+        idx = np.ascontiguousarray(queryIndices, dtype=np.uint32)
+        if len(idx) != md.Queries:
+            raise ValueError("expected %d query indices" % md.Queries)
+        queried = backend.NewStore(len(idx), lout)
+        check(lib.lmn_query_columns(backend.ctx, self.EncodedMatrix.h, _ptr(idx), len(idx), queried.h))
+        queried.scale = backend.RescaleScale(backend.params.MaxLevel(), lout)
+        return EncryptedProof(LigeroMetadata(md.Rows, md.Cols, md.RhoInv, md.Queries), matR, matZ, queried)
+
+
+class LigeroCommitter(LigeroMetadata):
+    """ref: fhe/ligero.go:26-63, 95-124"""
+
+    def __init__(self, securityBits, rows, cols, rhoInv):
+        if rows * cols <= 0:
+            raise ValueError("size must be positive")
+        if securityBits <= 0:
+            raise ValueError("securityBits must be positive")
+        super().__init__(int(rows), int(cols), int(rhoInv), calculateQueries(securityBits, rhoInv))
+
+    def Commit(self, matrix, backend, zeroCol):
+        """Encode span of Commit (ligero.go:95-104).  The Merkle tree over the leaves (ligero.go:105-116) is
+        SURVEY 8(f) row 1 and stays with the host."""
+        if matrix.count != self.Cols:
+            raise ValueError("matrix must hold one ciphertext per column")
+        encoded = Encode(matrix, self.Rows, self.RhoInv, backend, zeroCol)
+        return LigeroProver(self, matrix, encoded)

@@ -1,0 +1,215 @@
+"""GPU parity tests (-m gpu): every output limb of the CUDA path, called through the C ABI, is compared
+bit-for-bit with the CPU oracle on the same keys, ciphertexts and plaintexts (P1), and decrypted outputs are
+compared with the reference's plaintext prover relations (P0: fhe/code_test.go:109-116, fhe/ligero_test.go:164-174,
+fhe/ligero.go:554-571)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from helpers import Scenario  # noqa: E402
+from oracle import oracle as O  # noqa: E402
+
+T = O.T_DEFAULT
+
+
+def _first_diff(a, b):
+    d = np.argwhere(a != b)
+    return "first mismatch at %s of %d mismatches (got %d, want %d)" % (d[0].tolist(), len(d), a[tuple(d[0])], b[tuple(d[0])]) if len(d) else ""
+
+
+def assert_same(got, want, what=""):
+    assert got.shape == want.shape, (got.shape, want.shape)
+    assert (got == want).all(), what + ": " + _first_diff(got, want)
+
+
+_cache = {}
+
+
+def scenario(logN, rows, cols, k):
+    key = (logN, rows, cols, k)
+    if key not in _cache:
+        _cache[key] = Scenario(logN, rows, cols, k)
+    return _cache[key]
+
+
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("logN,k", [(6, 3), (8, 3), (10, 3), (12, 3), (13, 2), (14, 3)])
+def test_limb_ntt_intt(logN, k):
+    S = scenario(logN, 1 << (logN - 1), 16, k)
+    be = S.backend()
+    st = be.NewStore(1)
+    ct = S.cts[0]
+    st.upload(ct)
+    from lumenos_b200 import _capi
+    L = _capi.lib()
+    for limb in range(k):
+        _capi.check(L.lmn_limb_ntt(be.ctx, st.h, 0, 1, limb, 1))      # INTT of poly 1
+    got = st.download()[0]
+    for limb in range(k):
+        assert_same(got[1, limb], S.P.intt(ct[1, limb], limb), "INTT limb %d" % limb)
+    for limb in range(k):
+        _capi.check(L.lmn_limb_ntt(be.ctx, st.h, 0, 1, limb, 0))
+    assert_same(st.download()[0], ct, "NTT(INTT(x))")
+    be.Close()
+
+
+@pytest.mark.parametrize("logN,k", [(6, 4), (12, 3)])
+def test_operator_level(logN, k):
+    S = scenario(logN, 1 << (logN - 1), 16, k)
+    P = S.P
+    be = S.backend()
+    st = be.NewStore(4)
+    st.upload(S.cts[:2], 0)
+    a, b = S.cts[0], S.cts[1]
+    be.Add((st, 0), (st, 1), (st, 2)); assert_same(st.download(2, 1)[0], P.add(a, b), "Add")
+    be.Sub((st, 0), (st, 1), (st, 2)); assert_same(st.download(2, 1)[0], P.sub(a, b), "Sub")
+    for w in [int(S.roots[0]), int(S.roots[4]), int(S.roots[5]), T - 1, 1, 0, 2**64 - 1]:
+        be.Mul((st, 0), w, (st, 3)); assert_same(st.download(3, 1)[0], P.mul_scalar(a, w), "Mul scalar %d" % w)
+    be.Mul((st, 0), int(S.roots[4]), (st, 0)); assert_same(st.download(0, 1)[0], P.mul_scalar(a, int(S.roots[4])), "Mul in place")
+    st.upload(a[None], 0)
+    be.MulNew((st, 0), S.rpt, (st, 2)); assert_same(st.download(2, 1)[0], P.mul_pt(a, S.rpt), "MulNew")
+    be.CopyNew((st, 1), (st, 3)); assert_same(st.download(3, 1)[0], b, "CopyNew")
+    assert be.MulCounter() == 9
+    # Rescale chain
+    cur, cur_st = a, st
+    scale = 1
+    for lvl in range(k - 1, 0, -1):
+        nxt = be.NewStore(1, lvl - 1)
+        be.Rescale((cur_st, 0), (nxt, 0))
+        want, scale = P.rescale(cur, scale)
+        assert_same(nxt.download()[0], want, "Rescale from level %d" % lvl)
+        cur, cur_st = want, nxt
+    assert scale == be.RescaleScale(k - 1, 0)
+    be.Close()
+
+
+@pytest.mark.parametrize("logN,rows,k", [(6, 32, 4), (6, 64, 4), (6, 64, 5), (8, 256, 6), (10, 512, 3),
+                                         (12, 4096, 4), (13, 8192, 3), (14, 16384, 4), (14, 8192, 3)])
+def test_inner_sum(logN, rows, k):
+    S = scenario(logN, rows, 16, k)
+    be = S.backend()
+    st = be.NewStore(1)
+    col = S.P.mul_pt(S.cts[1], S.rpt)
+    st.upload(col[None])
+    be.InnerSum((st, 0), 1, rows)
+    want = S.P.innersum(col, rows, S.gal, S.evks)
+    assert_same(st.download()[0], want, "InnerSum rows=%d" % rows)
+    be.Close()
+
+
+def test_inner_sum_missing_key_and_bad_n():
+    S = scenario(6, 32, 16, 4)
+    from lumenos_b200 import fhe
+    be = fhe.ServerBFV(fhe.PrimeField(T, S.roots), fhe.BGVParameters(6, S.P.q, S.P.p, T, S.P.psi_q, S.P.psi_p))
+    st = be.NewStore(1); st.upload(S.cts[0][None])
+    with pytest.raises(fhe.LumenosError, match="missing Galois key"):
+        be.InnerSum((st, 0), 1, 32)
+    with pytest.raises(fhe.LumenosError, match="power-of-two"):
+        be.InnerSum((st, 0), 1, 24)
+    be.Close()
+
+
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("logN,rows,cols,k", [(6, 32, 16, 6), (8, 128, 64, 8), (6, 32, 128, 3), (6, 32, 256, 3),
+                                              (6, 32, 1024, 2), (12, 2048, 8, 2)])
+def test_encode_bit_exact(logN, rows, cols, k):
+    from lumenos_b200 import fhe
+    S = scenario(logN, rows, cols, k)
+    be = S.backend()
+    matrix = be.NewStore(cols).upload(S.cts)
+    zero = be.NewStore(1).upload(S.zero[None])
+    enc = fhe.Encode(matrix, rows, 2, be, (zero, 0))
+    want = S.P.fhe_encode(S.cts, 2, S.zero, S.roots)
+    got = enc.download()
+    assert_same(got, want, "Encode %dx%d" % (rows, cols))
+    assert be.MulCounter() == O.ntt_counts()[2]
+    assert_same(matrix.download(), S.cts, "Encode must not modify the matrix")
+    # fhe.NTT on an explicit slice gives the same as Encode on [matrix | zero copies]
+    full = np.concatenate([S.cts, np.repeat(S.zero[None], cols, axis=0)])
+    inp = be.NewStore(2 * cols).upload(full)
+    out = fhe.NTT(inp, 2 * cols, be)
+    assert_same(out.download(), want, "NTT")
+    if k >= 6:  # P0: decrypt == core.Encode (fhe/code_test.go:109-116)
+        exp = np.stack([O.core_encode(S.M[i], 2, S.roots) for i in range(rows)])
+        for j in range(2 * cols):
+            assert (S.P.decrypt(S.sk, got[j])[:rows] == exp[:, j]).all(), j
+    be.Close()
+
+
+@pytest.mark.parametrize("logN,rows,cols,k,batch", [(6, 32, 16, 6, 10), (6, 64, 16, 5, 64), (8, 256, 64, 8, 64),
+                                                    (12, 4096, 8, 3, 6), (14, 16384, 4, 3, 64)])
+def test_commit_prove_bit_exact(logN, rows, cols, k, batch):
+    """TestLigeroE2E shape of flow (fhe/ligero_test.go:70-176): Commit -> Prove, every output ciphertext compared"""
+    from lumenos_b200 import fhe
+    S = scenario(logN, rows, cols, k)
+    P = S.P
+    be = S.backend()
+    be.SetBatch(batch)
+    matrix = be.NewStore(cols).upload(S.cts)
+    zero = be.NewStore(1).upload(S.zero[None])
+    committer = fhe.LigeroCommitter(128, rows, cols, 2)
+    prover = committer.Commit(matrix, be, (zero, 0))
+    rng = np.random.default_rng(7)
+    idx = rng.integers(0, 2 * cols, size=committer.Queries).astype(np.uint32)
+    idx[5] = idx[2]                                                  # duplicates are legal (ligero.go:638-644)
+    proof = prover.Prove(S.rpt, S.bpt, idx, be)
+    enc_want = P.fhe_encode(S.cts, 2, S.zero, S.roots)
+    matR, matZ, qc = proof.MatR.download(), proof.MatZ.download(), proof.QueriedCols.download()
+    for j in range(cols):
+        wr, sr = P.inner_sum_eval_column(S.cts[j], S.rpt, rows, S.gal, S.evks)
+        wz, sz = P.inner_sum_eval_column(S.cts[j], S.bpt, rows, S.gal, S.evks)
+        assert_same(matR[j], wr, "MatR[%d]" % j)
+        assert_same(matZ[j], wz, "MatZ[%d]" % j)
+        assert sr == proof.MatR.scale and sz == proof.MatZ.scale
+        # P0: slot 0 == sum_i r_i M_ij , sum_i b_i M_ij (fhe/ligero_test.go:164-174)
+        assert int(P.decrypt(S.sk, matR[j], sr)[0]) == sum((int(a) % T) * int(b) for a, b in zip(S.r, S.M[:, j])) % T
+        assert int(P.decrypt(S.sk, matZ[j], sz)[0]) == sum(int(a) * int(b) for a, b in zip(S.b, S.M[:, j])) % T
+    seen = {}
+    for i, ix in enumerate(idx[:40]):
+        if int(ix) not in seen:
+            seen[int(ix)] = P.rescale_to_level1(enc_want[ix])
+        want, sc = seen[int(ix)]
+        assert_same(qc[i], want, "QueriedCols[%d] (column %d)" % (i, ix))
+        assert sc == proof.QueriedCols.scale
+    assert_same(prover.EncodedMatrix.download(), enc_want, "EncodedMatrix")
+    be.Close()
+
+
+def test_ring_switch_bit_exact():
+    from lumenos_b200 import fhe
+    logN, logNs, rows, cols, k = 8, 6, 128, 16, 4
+    S = scenario(logN, rows, cols, k)
+    P = S.P
+    Ps = O.Params(logNs, q=P.q[:1], p=P.p)
+    sks = Ps.keygen_sk(9)
+    evk = P.keygen_ringswitch(S.sk, sks, logNs, 11)
+    be = S.backend()
+    be.SetRingSwitchServer(fhe.RingSwitchServer(be, evk, logNs))
+    matrix = be.NewStore(cols).upload(S.cts)
+    out = fhe.matrixInnerSumEval(matrix, S.rpt, rows, be)
+    got = out.download()
+    assert got.shape == (cols, 2, 1, 1 << logNs)
+    for j in range(cols):
+        lvl1, _ = P.inner_sum_eval_column(S.cts[j], S.rpt, rows, S.gal, S.evks)
+        assert_same(got[j], P.ringswitch(lvl1, evk, logNs), "ring switch column %d" % j)
+    be.Close()
+
+
+def test_store_roundtrip_and_errors():
+    from lumenos_b200 import fhe
+    S = scenario(6, 32, 16, 4)
+    be = S.backend()
+    st = be.NewStore(3)
+    st.upload(S.cts[:3])
+    assert_same(st.download(), S.cts[:3], "bulk roundtrip")
+    st.upload_limb(2, 1, 3, S.cts[0][0, 1])
+    assert_same(st.download_limb(2, 1, 3), S.cts[0][0, 1], "limb roundtrip")
+    with pytest.raises(fhe.LumenosError):
+        st.upload(S.cts[:4])
+    with pytest.raises(fhe.LumenosError):
+        be.NewStore(1, level=7)
+    lvl1 = be.NewStore(1, 1)
+    with pytest.raises(fhe.LumenosError, match="share one level"):
+        be.Add((st, 0), (st, 1), (lvl1, 0))
+    be.Close()

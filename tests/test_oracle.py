@@ -1,0 +1,127 @@
+"""CPU tests of the oracle against the reference's own known answers and its plaintext twin (P0 ladder)."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+
+KAT = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "kat.json")))
+T = KAT["t"]
+
+
+@pytest.mark.parametrize("shape", ["2048x1024", "4096x2048"])
+def test_witness_generator_kat(shape):
+    rows, cols = map(int, shape.split("x"))
+    M = O.witness_matrix(rows, cols)
+    assert int(np.sum(M.astype(object))) % T == KAT["witness_p1"][shape]
+
+
+def test_witness_generator_kat_big():
+    # 8192x4096 (256 MiB of u64): the stream is row-major, so a prefix check of the 16384x4096 matrix covers both
+    M = O.witness_matrix(8192, 4096)
+    assert int(np.sum(M.astype(object))) % T == KAT["witness_p1"]["8192x4096"]
+
+
+@pytest.mark.parametrize("n", [2048, 4096, 8192])
+def test_fhe_ntt_op_counts(n):
+    roots = O.field_roots_forward(n)
+    P = O.Params(4, k=1)
+    O.lib().orc_fhe_ntt(P.h, np.zeros((n, 2, 1, 16), np.uint64), n, n, roots, n)
+    assert list(O.ntt_counts()) == KAT["ntt_op_counts"][str(n)]
+
+
+def test_param_heuristic():
+    # ref: fhe/bfv.go:141-158 and server logs "ModQ chain length 10/11/12"
+    for cols, k in KAT["q_chain_len"].items():
+        assert O.lib().orc_num_q_primes_for_ntt(int(cols), T) == k
+    P = O.Params(12, cols=1024)
+    assert P.k == 10 and P.np == 2
+    assert [int(x).bit_length() for x in P.p] in ([56, 55], [55, 56], [56, 56], [55, 55])
+    for q in list(P.q) + list(P.p):
+        assert int(q) % (2 * P.N) == 1
+
+
+def test_ntt_roundtrip_and_negacyclic():
+    P = O.Params(8, k=3)
+    rng = np.random.default_rng(0)
+    for mi in range(P.k + P.np):
+        q = int(P.q[mi]) if mi < P.k else int(P.p[mi - P.k])
+        a = rng.integers(0, q, size=P.N, dtype=np.uint64)
+        assert (P.intt(P.ntt(a, mi), mi) == a).all()
+        # X * a(X) mod X^N+1 in the NTT domain is a pointwise product with NTT(X)
+        x = np.zeros(P.N, np.uint64); x[1] = 1
+        prod = (P.ntt(a, mi).astype(object) * P.ntt(x, mi).astype(object)) % q
+        shifted = np.empty(P.N, np.uint64); shifted[1:] = a[:-1]; shifted[0] = (q - int(a[-1])) % q
+        assert (P.intt(prod.astype(np.uint64), mi) == shifted).all()
+
+
+@pytest.mark.parametrize("logN,rows,cols,k", [(6, 32, 16, 6), (8, 128, 64, 8), (10, 512, 128, 9)])
+def test_encode_matches_plaintext_twin(logN, rows, cols, k):
+    """TestEncode (fhe/code_test.go:80-116): decrypt(fhe.Encode(cts))[i][j] == core.Encode(matrix[i])[j]"""
+    P = O.Params(logN, k=k)
+    sk = P.keygen_sk(2); pk = P.keygen_pk(sk, 3)
+    M = O.witness_matrix(rows, cols)
+    cts = np.stack([P.encrypt(pk, P.encode(M[:, j]), 100 + j) for j in range(cols)])
+    roots = O.field_roots_forward(2 * cols)
+    enc = P.fhe_encode(cts, 2, P.encrypt(pk, None, 4), roots)
+    exp = np.stack([O.core_encode(M[i], 2, roots) for i in range(rows)])
+    for j in range(2 * cols):
+        assert (P.decrypt(sk, enc[j])[:rows] == exp[:, j]).all(), j
+
+
+@pytest.mark.parametrize("logN,rows,k", [(6, 32, 4), (6, 64, 4), (6, 64, 5), (8, 256, 6)])
+def test_inner_product_matches_plaintext_prover(logN, rows, k):
+    """TestLigeroE2E (fhe/ligero_test.go:164-174): slot 0 of matrixInnerSumEval == sum_i r_i M_ij (rows < N and rows == N)"""
+    P = O.Params(logN, k=k)
+    sk = P.keygen_sk(2); pk = P.keygen_pk(sk, 3)
+    cols = 3
+    M = O.witness_matrix(rows, cols)
+    gal = P.galois_elements_for_innersum(rows)
+    evks = [P.keygen_galois(sk, g, 5) for g in gal]
+    rng = np.random.default_rng(1)
+    r = rng.integers(0, 2**63, size=rows, dtype=np.uint64) * np.uint64(2) + np.uint64(1)
+    rpt = P.encode(r)
+    for j in range(cols):
+        ct = P.encrypt(pk, P.encode(M[:, j]), 100 + j)
+        out, scale = P.inner_sum_eval_column(ct, rpt, rows, gal, evks)
+        assert out.shape == (2, 2, P.N)
+        exp = sum((int(a) % T) * int(b) % T for a, b in zip(r, M[:, j])) % T
+        assert int(P.decrypt(sk, out, scale)[0]) == exp
+
+
+def test_verify_relations_on_queried_columns():
+    """Proof.Verify (fhe/ligero.go:554-571): <queried column, r> == Encode(MatR)[idx] on rescaled encoded columns"""
+    logN, rows, cols, k = 6, 32, 16, 6
+    P = O.Params(logN, k=k)
+    sk = P.keygen_sk(2); pk = P.keygen_pk(sk, 3)
+    M = O.witness_matrix(rows, cols)
+    cts = np.stack([P.encrypt(pk, P.encode(M[:, j]), 100 + j) for j in range(cols)])
+    roots = O.field_roots_forward(2 * cols)
+    enc = P.fhe_encode(cts, 2, P.encrypt(pk, None, 4), roots)
+    rng = np.random.default_rng(3)
+    r = rng.integers(0, T, size=rows, dtype=np.uint64)
+    matR = np.array([sum(int(a) * int(b) for a, b in zip(r, M[:, j])) % T for j in range(cols)], dtype=np.uint64)
+    encR = O.core_encode(matR, 2, roots)
+    for idx in [0, 5, 17, 31, 5]:
+        lvl1, scale = P.rescale_to_level1(enc[idx])
+        col = P.decrypt(sk, lvl1, scale)[:rows]
+        assert sum(int(a) * int(b) for a, b in zip(col, r)) % T == int(encR[idx])
+
+
+def test_ring_switch_decrypts_under_small_key():
+    """TestRingSwitch analogue (fhe/ring_switch_test.go:13-78) with a real degree change: coefficients at
+    multiples of N/N' of the plaintext polynomial survive the switch."""
+    logN, logNs, k = 8, 6, 4
+    P = O.Params(logN, k=k)
+    Ps = O.Params(logNs, q=P.q[:1], p=P.p)     # small ring, same first prime
+    sk = P.keygen_sk(2); pk = P.keygen_pk(sk, 3)
+    sks = Ps.keygen_sk(9)
+    evk = P.keygen_ringswitch(sk, sks, logNs, 11)
+    ct = P.encrypt(pk, None, 5)
+    lvl1, _ = P.rescale_to_level1(ct)
+    out = P.ringswitch(lvl1, evk, logNs)
+    assert out.shape == (2, 1, Ps.N)
+    # an encryption of zero stays an encryption of zero (small noise) under the small key
+    assert Ps.noise_bits(sks, out) < 45

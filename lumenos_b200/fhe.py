@@ -11,6 +11,7 @@ Ciphertexts live in device-resident stores; numpy is used only to carry host buf
 """
 import ctypes as C
 import math
+import weakref
 
 import numpy as np
 
@@ -95,6 +96,7 @@ class CiphertextStore:
                 check(L.lmn_store_create(backend.ctx, count, level, C.byref(h)))
             self.N = backend.params.N
         self.h = h
+        backend._stores.add(self)
         self.count = count
         self.level = L.lmn_store_level(h)
         self.scale = 1   # rlwe.MetaData.Scale (mod T), tracked on the host as in the reference
@@ -135,9 +137,10 @@ class CiphertextStore:
         return _capi.lib().lmn_store_bytes(self.h)
 
     def free(self):
-        if self.h:
+        # a store must be released before its context (ServerBFV.Close releases the survivors itself)
+        if self.h and self.backend.ctx:
             _capi.lib().lmn_store_destroy(self.h)
-            self.h = None
+        self.h = None
 
     def __del__(self):
         try:
@@ -199,6 +202,7 @@ class ServerBFV:
         self.ring_switch_logn = 0
         self.mulCounter = 0
         self._plans = {}
+        self._stores = weakref.WeakSet()
         if stream is not None:
             self.SetStream(stream)
 
@@ -219,6 +223,8 @@ class ServerBFV:
         for pl in self._plans.values():
             _capi.lib().lmn_plan_destroy(pl)
         self._plans = {}
+        for st in list(getattr(self, "_stores", [])):
+            st.free()
         if self.ctx:
             _capi.lib().lmn_ctx_destroy(self.ctx)
             self.ctx = None

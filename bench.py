@@ -1,0 +1,421 @@
+#!/usr/bin/env python
+"""Benchmark of the lumenos server-side hot path on B200: Encode eval + Prove eval (both inner products + query columns)
+at a reference matrix shape (BASELINE.json: 16384x4096 LogN=14 is the headline; fits one GPU).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--config A|B|C|D] [--impl b200|reference]
+
+A "step" = one pass of the hot path over one synthetic encrypted matrix: fhe.Encode (fhe/code.go:8-34) then
+Prove's InnerProduct(Matrix, r) || InnerProduct(Matrix, b) and Query columns (fhe/ligero.go:194-280).
+`value` = seconds per step with inputs resident in HBM (metric is time-like: lower is better); `e2e` = the same
+through the C ABI with HOST buffers (pinned): H2D of the matrix and D2H of MatR/MatZ/queried columns inside the
+timed region.  N > 1: strong scaling -- columns shard by rank for the inner products and the query rescale, the
+Encode lanes shard by coefficient slice; the only exchange is the all-to-all that turns the queried
+columns' coefficient slices into whole ciphertexts.
+Synthetic data: uniformly random canonical residues for ciphertexts, keys and plaintexts (all kernels are
+data-independent in time); parity with real encryptions is the job of tests/, not of this file.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CONFIGS = {  # rows, cols, logN  (scripts/benchmark_server.sh:34-39, README.md:59-61)
+    "A": (2048, 1024, 12), "B": (4096, 2048, 12), "C": (8192, 4096, 13), "D": (16384, 4096, 14),
+}
+PUBLISHED_S = {"A": 14.77, "B": 36.80, "C": 179.93, "D": 397.85}  # Encode + Prove eval, m7i.8xlarge 32 vCPU
+RHO_INV, SECURITY_BITS = 2, 128
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region"""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=lambda: [self.lines.append(l) for l in self.proc.stdout], daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], None, set()
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx = float(f[1])
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------------------------
+def cpu_reference_sample(cfg, threads, enc_lanes=2048, ip_cols=None, q_cols=None):
+    """Times the CPU oracle (a C port of the reference's Go/Lattigo path) on a bounded sample of the workload and
+    extrapolates linearly to the full shape.  Returns (seconds_full_workload, description, parts)."""
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import oracle as O
+    rows, cols, logN = CONFIGS[cfg]
+    k = O.lib().orc_num_q_primes_for_ntt(cols, O.T_DEFAULT)
+    P = O.Params(logN, k=k)
+    N, n = P.N, cols * RHO_INV
+    rng = np.random.default_rng(5)
+    ip_cols = ip_cols or threads
+    q_cols = q_cols or threads
+    # Encode: the reference runs it on ONE goroutine (fhe/code.go, fhe/ntt.go have no worker pool)
+    roots = O.field_roots_forward(n)
+    limb_of_lane = (np.arange(enc_lanes) * k // enc_lanes).astype(np.int32)
+    qs = P.q[limb_of_lane]
+    ml = (rng.integers(0, 2**62, size=(cols, enc_lanes), dtype=np.uint64) % qs).astype(np.uint64)
+    zl = (rng.integers(0, 2**62, size=enc_lanes, dtype=np.uint64) % qs).astype(np.uint64)
+    t0 = time.perf_counter()
+    P.fhe_encode_lanes(ml, RHO_INV, zl, limb_of_lane, roots)
+    enc_s = (time.perf_counter() - t0) * (2 * k * N / enc_lanes)
+    # inner product: column-parallel worker pool like matrixInnerSumEval (fhe/ligero.go:308-345)
+    def rand_ct():
+        ct = np.empty((2, k, N), np.uint64)
+        for i in range(k):
+            ct[:, i, :] = rng.integers(0, int(P.q[i]), size=(2, N), dtype=np.uint64)
+        return ct
+    gal = P.galois_elements_for_innersum(rows)
+    sk = P.keygen_sk(1)
+    evks = [P.keygen_galois(sk, g, 2) for g in gal]
+    pt = rand_ct()[0]
+    cts = [rand_ct() for _ in range(ip_cols)]
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(threads) as ex:
+        list(ex.map(lambda ct: P.inner_sum_eval_column(ct, pt, rows, gal, evks), cts))
+    ip_s = (time.perf_counter() - t0) * (2 * cols / ip_cols)
+    # query columns: single goroutine in the reference (fhe/ligero.go:268-274); timed column-parallel here and
+    # reported as the faster of the two readings would flatter the CPU, so keep it sequential-equivalent
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(threads) as ex:
+        list(ex.map(P.rescale_to_level1, cts[:q_cols]))
+    q_par = (time.perf_counter() - t0) * (fheq(cfg) / q_cols)
+    parts = {"encode_s_1core": round(enc_s, 2), "inner_product_s": round(ip_s, 2), "query_s_parallel": round(q_par, 2)}
+    desc = ("C port of the reference path (oracle/), %s %dx%d LogN=%d k=%d: Encode on %d of %d lanes single-threaded (as the reference), "
+            "%d of %d column-vectors of matrixInnerSumEval and %d of %d query rescales on %d threads; each part scaled linearly to the full shape"
+            % (cfg, rows, cols, logN, k, enc_lanes, 2 * k * N, ip_cols, 2 * cols, q_cols, fheq(cfg), threads))
+    return enc_s + ip_s + q_par, desc, parts
+
+
+def fheq(cfg):
+    from lumenos_b200 import fhe
+    return fhe.calculateQueries(SECURITY_BITS, RHO_INV)
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    vals, desc, parts = [], "", {}
+    for i in range(args.warmup + args.steps):
+        v, desc, parts = cpu_reference_sample(args.config, threads, enc_lanes=1024, ip_cols=threads, q_cols=threads)
+        if i >= args.warmup:
+            vals.append(v)
+    rows, cols, logN = CONFIGS[args.config]
+    value = sum(vals) / len(vals)
+    print(json.dumps({
+        "impl": "reference", "metric": "ligero_server_prove_eval_s", "value": value, "unit": "s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": value * 1e3, "higher_is_better": False, "scaling": "strong",
+        "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": "%s: %dx%d LogN=%d encode + prove eval (inner products r,b + %d query columns)" % (args.config, rows, cols, logN, fheq(args.config))},
+        "cpu_baseline": {"value": value, "unit": "s", "cores": threads, "kind": "port", "sample": desc, "parts": parts},
+        "e2e": {"value": value, "unit": "s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "reference = Go + un-vendored Lattigo; no Go toolchain here, so the CPU arm is the C port (oracle/); published m7i.8xlarge number: %.2f s" % PUBLISHED_S[args.config],
+    }))
+
+
+# ------------------------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--config", default="D", choices=list(CONFIGS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+
+    import torch
+    import torch.distributed as dist
+    from lumenos_b200 import _capi, fhe, hostutil as H
+
+    rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+    G = world
+    if G != args.gpus:
+        log("warning: --gpus %d but WORLD_SIZE %d" % (args.gpus, G))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if G > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    rows, cols, logN = CONFIGS[args.config]
+    N, n = 1 << logN, cols * RHO_INV
+    T = H.T_DEFAULT
+    k = H.num_q_primes_for_ntt(cols, T)
+    if cols % G or N % G or (N // G) < 32:
+        raise SystemExit("config does not shard over %d GPUs" % G)
+    t_setup = time.perf_counter()
+    q, p = H.generate_moduli(logN, k)
+    params = fhe.BGVParameters(logN, q, p, T, [H.psi_of(m, logN) for m in q], [H.psi_of(m, logN) for m in p])
+    field = fhe.PrimeField(T, H.field_roots_forward(n, T))
+    stream = torch.cuda.current_stream(dev)
+    be = fhe.ServerBFV(field, params, device=local, stream=stream.cuda_stream)
+    be.SetBatch(args.batch)
+    lib = _capi.lib()
+    rng = np.random.default_rng(1234 + rank)
+    mods = list(q) + list(p)
+    beta = (k + len(p) - 1) // len(p)
+
+    # Galois keys: random canonical residues in the evk layout [beta][2][k+np][N]
+    for g in params.GaloisElementsForInnerSum(1, rows):
+        evk = np.empty((beta, 2, k + len(p), N), np.uint64)
+        for i, m in enumerate(mods):
+            evk[:, :, i, :] = rng.integers(0, m, size=(beta, 2, N), dtype=np.uint64)
+        be.LoadGaloisKey(g, evk)
+    del evk
+
+    def rand_cts(count, coeffs):
+        t = torch.empty((count, 2, k, coeffs), dtype=torch.int64, device=dev)
+        for i in range(k):
+            t[:, :, i, :].random_(0, int(q[i]))
+        return t
+
+    cols_loc, Ns = cols // G, N // G
+    log_ns = logN - (G.bit_length() - 1)
+    committer = fhe.LigeroCommitter(SECURITY_BITS, rows, cols, RHO_INV)
+    nq_total = committer.Queries
+    qrng = np.random.default_rng(99)
+    qidx = (qrng.integers(0, 2**62, size=nq_total) % n).astype(np.uint32)
+    qidx[7] = qidx[3]
+    my_q = list(range(rank, nq_total, G))
+    lout = 1
+
+    mat_cols_t = rand_cts(cols_loc, N)                  # column shard: inner products
+    mat_cols = fhe.CiphertextStore(be, cols_loc, k - 1, wrap_ptr=mat_cols_t.data_ptr())
+    if G == 1:
+        mat_enc_t, mat_enc = mat_cols_t, mat_cols       # same layout on one GPU
+    else:
+        mat_enc_t = rand_cts(cols, Ns)                  # coefficient slice of every column: Encode
+    zero_t = rand_cts(1, Ns if G > 1 else N)
+    enc_t = torch.empty((n, 2, k, Ns if G > 1 else N), dtype=torch.int64, device=dev)
+    enc_store = fhe.CiphertextStore(be, n, k - 1, wrap_ptr=enc_t.data_ptr()) if G == 1 else None
+    zero_store = fhe.CiphertextStore(be, 1, k - 1, wrap_ptr=zero_t.data_ptr()) if G == 1 else None
+    matR = be.NewStore(cols_loc, lout)
+    matZ = be.NewStore(cols_loc, lout)
+    queried = be.NewStore(max(1, len(my_q)), lout)
+    rpt = np.stack([rng.integers(0, m, size=N, dtype=np.uint64) for m in q])
+    bpt = np.stack([rng.integers(0, m, size=N, dtype=np.uint64) for m in q])
+    plan = be._plan(cols, RHO_INV)
+    my_idx = np.ascontiguousarray(qidx[my_q], dtype=np.uint32)
+    arange_idx = np.arange(len(my_q), dtype=np.uint32)
+    log("[rank %d] setup %.1fs: %s %dx%d LogN=%d k=%d, %d GPU(s), device mem %.1f GiB" %
+        (rank, time.perf_counter() - t_setup, args.config, rows, cols, logN, k, G, torch.cuda.memory_allocated(dev) / 2**30))
+
+    vp = C.c_void_p
+
+    def step():
+        # ---- Commit: Encode span (fhe/ligero.go:96-100) ----
+        if G == 1:
+            _capi.check(lib.lmn_encode(be.ctx, plan, mat_enc.h, zero_store.h, 0, enc_store.h))
+        else:
+            _capi.check(lib.lmn_encode_lanes(be.ctx, plan, vp(mat_enc_t.data_ptr()), vp(zero_t.data_ptr()), vp(enc_t.data_ptr()), log_ns))
+        # ---- Prove: inner products (ligero.go:231-242) ----
+        _capi.check(lib.lmn_inner_product2(be.ctx, mat_cols.h, rpt.ctypes.data_as(vp), bpt.ctypes.data_as(vp), rows, matR.h, matZ.h))
+        # ---- Prove: query columns (ligero.go:262-280) ----
+        if G == 1:
+            _capi.check(lib.lmn_query_columns(be.ctx, enc_store.h, my_idx.ctypes.data_as(vp), len(my_idx), queried.h))
+        else:
+            # coefficient slices of the queried columns -> whole ciphertexts on the rank that rescales them
+            send = torch.cat([enc_t[torch.as_tensor(qidx[d::G].astype(np.int64), device=dev)] for d in range(G)])
+            send_splits = [len(qidx[d::G]) for d in range(G)]
+            recv = torch.empty((G * len(my_q), 2, k, Ns), dtype=torch.int64, device=dev)
+            dist.all_to_all_single(recv, send, [len(my_q)] * G, send_splits)
+            full = recv.view(G, len(my_q), 2, k, Ns).permute(1, 2, 3, 0, 4).contiguous()
+            st = fhe.CiphertextStore(be, len(my_q), k - 1, wrap_ptr=full.data_ptr())
+            _capi.check(lib.lmn_query_columns(be.ctx, st.h, arange_idx.ctypes.data_as(vp), len(my_q), queried.h))
+            torch.cuda.current_stream(dev).synchronize()
+            st.free()
+
+    def barrier():
+        if G > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if G > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(args.warmup):
+        step()
+    # device-resident timing; the dominant kernel (k_mac) and the HBM-bound Encode kernel are bracketed with event pairs
+    KID = {lib.lmn_kernel_name(i).decode(): i for i in range(lib.lmn_kernel_count())}
+    _capi.check(lib.lmn_profile_enable(be.ctx, (1 << KID["k_mac"]) | (1 << KID["k_encode_pass"])))
+    for i in range(lib.lmn_kernel_count()):
+        lib.lmn_profile_read(be.ctx, i, None, None, 1)
+    launches0 = be.LaunchCount()
+    sampler = ClockSampler(local)
+    sampler.start()
+    total_ms = timed(step, args.steps)
+    clocks = sampler.stop()
+    gpu_launches = be.LaunchCount() - launches0
+    ms_per_step = total_ms / args.steps
+
+    def prof(name):
+        ms, cnt = C.c_double(), C.c_uint64()
+        _capi.check(lib.lmn_profile_read(be.ctx, KID[name], C.byref(ms), C.byref(cnt), 1))
+        return ms.value, cnt.value
+    mac_ms, mac_n = prof("k_mac")
+    enc_ms, enc_n = prof("k_encode_pass")
+    _capi.check(lib.lmn_profile_enable(be.ctx, 0))
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak, hbm_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback (B200_PROFILING.md)")
+    np_ = len(p)
+    jobs = min(args.batch, 2 * cols_loc)
+    limb_b = N * 8
+    # k_mac algorithmic bytes per launch: per job read y (k limbs) + c1 (k limbs), write 2(k+np) accumulator limbs; evk once per launch
+    mac_bytes = jobs * (2 * k + 2 * (k + np_)) * limb_b + beta * 2 * (k + np_) * limb_b
+    mac_avg_s = mac_ms / max(1, mac_n) * 1e-3
+    roofline = {"kernel": "k_mac (ModUp + NTT + gadget MAC; integer-bound, reported against HBM as the contract asks)", "bound": "hbm",
+                "achieved": mac_bytes / mac_avg_s / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": mac_bytes / mac_avg_s / 1e9 / hbm_peak,
+                "traffic": None, "peak_source": hbm_src, "avg_launch_ms": mac_avg_s * 1e3, "launches": mac_n,
+                "share_of_step": mac_ms / total_ms}
+    # integer roofline of the same kernel: NTT butterflies per launch / measured register-resident butterfly ceiling
+    pk = C.c_double()
+    _capi.check(lib.lmn_bench_int_peak(be.ctx, C.byref(pk)))
+    ntts = sum((k + np_) - min(np_, k - d * np_) for d in range(beta))   # (digit, target) pairs that need ModUp + NTT
+    mac_bfly = jobs * ntts * (N // 2) * logN
+    roofline_int = {"kernel": "k_mac", "bound": "int", "achieved": mac_bfly / mac_avg_s / 1e9, "peak": pk.value / 1e9, "unit": "Gbutterfly/s",
+                    "frac": mac_bfly / mac_avg_s / pk.value, "peak_source": "k_peak_bfly micro-kernel on this GPU, same run",
+                    "note": "counts only NTT butterflies (ModUp, MAC and reductions are extra integer work in the same kernel)"}
+    ctw = 2 * k * (Ns if G > 1 else N) * 8
+    enc_bytes = ((cols + 1 + n) + (2 * n if n > 256 else 0)) * ctw   # pass 1 (+ pass 2, in place) per step
+    enc_s = enc_ms / args.steps * 1e-3
+    roofline_encode = {"kernel": "k_encode_pass (both passes of one Encode)", "bound": "hbm", "achieved": enc_bytes / enc_s / 1e9, "peak": hbm_peak,
+                       "unit": "GB/s", "frac": enc_bytes / enc_s / 1e9 / hbm_peak, "traffic": None, "ms_per_step": enc_s * 1e3,
+                       "algorithmic_min_bytes": (cols + 1 + n) * ctw, "share_of_step": enc_ms / total_ms}
+
+    # kernel-class breakdown of one extra (untimed) step
+    _capi.check(lib.lmn_profile_enable(be.ctx, 0xFFFFFFFF))
+    step()
+    breakdown = {}
+    for name, i in KID.items():
+        ms, cnt = C.c_double(), C.c_uint64()
+        _capi.check(lib.lmn_profile_read(be.ctx, i, C.byref(ms), C.byref(cnt), 1))
+        if cnt.value:
+            breakdown[name] = {"ms": round(ms.value, 3), "launches": cnt.value}
+    _capi.check(lib.lmn_profile_enable(be.ctx, 0))
+
+    # ---- e2e: host buffers through the C ABI, H2D + D2H inside the timed region ----
+    e2e = None
+    if not args.no_e2e:
+        def halloc(nbytes):
+            ptr = vp()
+            _capi.check(lib.lmn_host_alloc(nbytes, C.byref(ptr)))
+            return ptr
+        h_mat = halloc(mat_cols.nbytes)
+        _capi.check(lib.lmn_store_download(mat_cols.h, 0, cols_loc, h_mat))
+        h_enc = None
+        if G > 1:
+            h_enc = halloc(mat_enc_t.numel() * 8)
+            torch.cuda.synchronize(dev)
+            C.memmove(h_enc, mat_enc_t.cpu().numpy().ctypes.data, mat_enc_t.numel() * 8)
+        h_r, h_z, h_q = halloc(matR.nbytes), halloc(matZ.nbytes), halloc(queried.nbytes)
+        h2d = mat_cols.nbytes + (mat_enc_t.numel() * 8 if G > 1 else 0) + 2 * k * N * 8
+        d2h = matR.nbytes + matZ.nbytes + queried.nbytes
+
+        def e2e_step():
+            _capi.check(lib.lmn_store_upload(mat_cols.h, 0, cols_loc, h_mat))
+            if G > 1:
+                src = (C.c_char * (mat_enc_t.numel() * 8)).from_address(h_enc.value)
+                mat_enc_t.view(torch.uint8).copy_(torch.frombuffer(src, dtype=torch.uint8), non_blocking=True)
+            step()
+            _capi.check(lib.lmn_store_download(matR.h, 0, cols_loc, h_r))
+            _capi.check(lib.lmn_store_download(matZ.h, 0, cols_loc, h_z))
+            _capi.check(lib.lmn_store_download(queried.h, 0, max(1, len(my_q)), h_q))
+        e2e_step()
+        e2e_steps = max(1, min(args.steps, 3))
+        e2e_ms = timed(e2e_step, e2e_steps) / e2e_steps
+        e2e = {"value": e2e_ms / 1e3, "unit": "s", "h2d_bytes_per_step": int(h2d) * G, "d2h_bytes_per_step": int(d2h) * G, "steps": e2e_steps,
+               "path": "lmn_store_upload (pinned host -> HBM) + lmn_encode + lmn_inner_product2 + lmn_query_columns + lmn_store_download"}
+        for hptr in (h_mat, h_enc, h_r, h_z, h_q):
+            if hptr:
+                lib.lmn_host_free(hptr)
+
+    cpu = None
+    if rank == 0 and G == 1 and not args.no_cpu:
+        threads = os.cpu_count() or 1
+        v, desc, parts = cpu_reference_sample(args.config, threads)
+        cpu = {"value": v, "unit": "s", "cores": threads, "kind": "port", "sample": desc, "parts": parts,
+               "published_reference_s": PUBLISHED_S[args.config], "published_hardware": "m7i.8xlarge 32 vCPU (README.md:55-72), different hardware"}
+
+    if rank == 0:
+        out = {
+            "metric": "ligero_server_prove_eval_s", "value": ms_per_step / 1e3, "unit": "s", "n_gpus": G, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": {"workload": "%s: %dx%d LogN=%d k=%d encode + prove eval (inner products r,b + %d query columns)" % (args.config, rows, cols, logN, k, nq_total),
+                       "l2": "inputs (%.1f GiB matrix per GPU) far exceed the 126 MB L2; no flush needed" % (mat_cols.nbytes / 2**30),
+                       "sharding": "1 GPU" if G == 1 else "columns/%d for inner products + query rescale, coefficient slices/%d for Encode, all-to-all of queried slices" % (G, G),
+                       "batch_jobs": args.batch},
+            "e2e": e2e, "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "roofline_int": roofline_int,
+            "roofline_encode": roofline_encode, "kernel_breakdown_one_step": breakdown, "cpu_baseline": cpu,
+            "published_reference_s": PUBLISHED_S[args.config],
+        }
+        print(json.dumps(out))
+    be.Close()
+    if G > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -112,6 +112,13 @@ int lmn_encode(lmn_ctx *ctx, const lmn_plan *plan, const lmn_store *matrix, cons
  * out[i] = i-th ciphertext of the returned slice. in and out must be distinct stores. */
 int lmn_ntt(lmn_ctx *ctx, const lmn_plan *plan, const lmn_store *in, lmn_store *out);
 
+/* multi-GPU form of lmn_encode: every lane (poly, limb, coefficient) is an independent transform,
+ * so a rank may hold a coefficient slice of every ciphertext.  Buffers are raw device pointers laid out
+ * [ciphertext][poly 0..1][limb 0..k-1][2^log_coeffs coefficients]; matrix has plan-cols entries, zero one entry,
+ * encoded cols*rho_inv entries. */
+int lmn_encode_lanes(lmn_ctx *ctx, const lmn_plan *plan, const void *matrix_dev, const void *zero_dev, void *encoded_dev,
+                     uint32_t log_coeffs);
+
 /* host-only self-check of the plan compiler (no device): evaluates the compiled plan of size n on a plaintext
  * vector over Z_t in place, which must reproduce core.NTT (core/ntt.go:3-6) -- the equality the reference's own
  * TestEncode asserts (fhe/code_test.go:100-116).  counts3 (optional) receives {adds, subs, muls}. */
@@ -157,6 +164,15 @@ int lmn_ct_rescale(lmn_ctx *ctx, const lmn_store *a, uint32_t ai, lmn_store *o, 
 int lmn_ct_copy(lmn_ctx *ctx, const lmn_store *a, uint32_t ai, lmn_store *o, uint32_t oi);                                 /* Ciphertext.CopyNew, code.go:12 */
 /* ring.SubRing NTT / INTT of one limb of one polynomial, in place (test hook for the limb kernels) */
 int lmn_limb_ntt(lmn_ctx *ctx, lmn_store *a, uint32_t ai, uint32_t poly, uint32_t limb, int inverse);
+
+/* ---------------- measurement hooks (bench.py) ---------------- */
+/* per-kernel-class device timing with CUDA event pairs on the launch stream; mask bit i = class i */
+int lmn_profile_enable(lmn_ctx *ctx, uint32_t mask);
+int lmn_profile_read(lmn_ctx *ctx, int kernel_id, double *ms, uint64_t *launches, int reset);
+int lmn_kernel_count(void);
+const char *lmn_kernel_name(int kernel_id);
+/* measured ceiling of the NTT butterfly instruction mix on the integer pipes (register-resident, all SMs) */
+int lmn_bench_int_peak(lmn_ctx *ctx, double *butterflies_per_s);
 
 #ifdef __cplusplus
 }

@@ -48,6 +48,12 @@ SIGNATURES = {
     "lmn_plan_host_check": (C.c_int, [C.c_uint32, vp, C.c_uint64, vp, vp]),
     "lmn_encode": (C.c_int, [vp, vp, vp, vp, C.c_uint32, vp]),
     "lmn_ntt": (C.c_int, [vp, vp, vp, vp]),
+    "lmn_encode_lanes": (C.c_int, [vp, vp, vp, vp, vp, C.c_uint32]),
+    "lmn_profile_enable": (C.c_int, [vp, C.c_uint32]),
+    "lmn_profile_read": (C.c_int, [vp, C.c_int, C.POINTER(C.c_double), u64p, C.c_int]),
+    "lmn_kernel_count": (C.c_int, []),
+    "lmn_kernel_name": (C.c_char_p, [C.c_int]),
+    "lmn_bench_int_peak": (C.c_int, [vp, C.POINTER(C.c_double)]),
     "lmn_load_galois_key": (C.c_int, [vp, C.c_uint64, vp]),
     "lmn_load_ring_switch_key": (C.c_int, [vp, C.c_uint32, vp, C.c_uint64]),
     "lmn_inner_product": (C.c_int, [vp, vp, vp, C.c_uint32, vp]),

@@ -48,11 +48,12 @@ struct lmn_ctx {
     ulonglong2 *ws_scalar = nullptr;
     uint32_t ws_jobs = 0;
     uint64_t launches = 0;
+    Profiler prof;
     std::mutex mu;
 
     u64 mod(int i) const { return i < k ? q[i] : p[i - k]; }
     size_t ct_words(int level) const { return 2 * (size_t)(level + 1) * n; }
-    Launch L() { return Launch{stream, &launches}; }
+    Launch L() { return Launch{stream, &launches, &prof}; }
 };
 
 struct lmn_store {
@@ -265,6 +266,8 @@ void lmn_ctx_destroy(lmn_ctx *c) {
     cudaFree(c->d_mods); cudaFree(c->d_twf); cudaFree(c->d_twi); cudaFree(c->ws_pt); cudaFree(c->ws_scalar);
     cudaFree(c->ws_col); cudaFree(c->ws_y); cudaFree(c->ws_acc); cudaFree(c->ws_idx);
     cudaFree(c->d_rs_evk); cudaFree(c->d_small_mod); cudaFree(c->d_small_tw);
+    for (int i = 0; i < KID_COUNT; i++) for (auto &sp : c->prof.spans[i]) { cudaEventDestroy(sp.first); cudaEventDestroy(sp.second); }
+    for (auto e : c->prof.pool) cudaEventDestroy(e);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
@@ -436,11 +439,12 @@ int lmn_plan_host_check(uint32_t n, const uint64_t *roots, uint64_t t, uint64_t 
 }
 
 // ---------------- Encode ----------------
-static int run_plan(lmn_ctx *c, const lmn_plan *p, const u64 *in, uint32_t in_count, const u64 *zero, u64 *out) {
+static int run_plan(lmn_ctx *c, const lmn_plan *p, const u64 *in, uint32_t in_count, const u64 *zero, u64 *out, int lane_logn = -1) {
     const EncodePlan &pl = p->pl;
+    if (lane_logn < 0) lane_logn = c->logn;
     EncPassArgs A; memset(&A, 0, sizeof(A));
     A.mods = c->d_mods; A.scale_after = p->d_scale_after; A.out_pos = p->d_out_pos; A.scal = p->d_scal;
-    A.nscal = (uint32_t)pl.scalars.size(); A.n = pl.n; A.k = c->k; A.logn = c->logn; A.ct_words = c->ct_words(c->k - 1);
+    A.nscal = (uint32_t)pl.scalars.size(); A.n = pl.n; A.k = c->k; A.logn = lane_logn; A.ct_words = 2 * (uint64_t)c->k << lane_logn;
     A.out = out;
     Launch L = c->L();
     if (pl.split == 0) {
@@ -483,6 +487,52 @@ int lmn_ntt(lmn_ctx *c, const lmn_plan *p, const lmn_store *in, lmn_store *out) 
     std::lock_guard<std::mutex> g(c->mu);
     cudaSetDevice(c->device);
     return run_plan(c, p, in->d, in->count, nullptr, out->d);
+}
+
+int lmn_encode_lanes(lmn_ctx *c, const lmn_plan *p, const void *matrix_dev, const void *zero_dev, void *encoded_dev, uint32_t log_coeffs) {
+    if (!c || !p || !matrix_dev || !zero_dev || !encoded_dev) return fail(LMN_ERR_INVALID, "null argument");
+    if (p->ctx != c) return fail(LMN_ERR_INVALID, "plan belongs to a different context");
+    if (log_coeffs < 5 || (int)log_coeffs > c->logn) return fail(LMN_ERR_INVALID, "a coefficient slice holds between 32 and N coefficients per limb");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    return run_plan(c, p, (const u64 *)matrix_dev, p->cols, (const u64 *)zero_dev, (u64 *)encoded_dev, (int)log_coeffs);
+}
+
+// ---------------- profiling ----------------
+int lmn_profile_enable(lmn_ctx *c, uint32_t mask) {
+    if (!c) return fail(LMN_ERR_INVALID, "null context");
+    std::lock_guard<std::mutex> g(c->mu);
+    c->prof.mask = mask;
+    return 0;
+}
+int lmn_profile_read(lmn_ctx *c, int kernel_id, double *ms, uint64_t *launches, int reset) {
+    if (!c || kernel_id < 0 || kernel_id >= KID_COUNT) return fail(LMN_ERR_INVALID, "bad kernel id");
+    std::lock_guard<std::mutex> g(c->mu);
+    CK(cudaStreamSynchronize(c->stream));
+    double total = 0;
+    for (auto &sp : c->prof.spans[kernel_id]) {
+        float t = 0; CK(cudaEventElapsedTime(&t, sp.first, sp.second));
+        total += t;
+    }
+    if (ms) *ms = total;
+    if (launches) *launches = c->prof.launches[kernel_id];
+    if (reset) {
+        for (auto &sp : c->prof.spans[kernel_id]) { c->prof.pool.push_back(sp.first); c->prof.pool.push_back(sp.second); }
+        c->prof.spans[kernel_id].clear();
+        c->prof.launches[kernel_id] = 0;
+    }
+    return 0;
+}
+int lmn_kernel_count(void) { return KID_COUNT; }
+const char *lmn_kernel_name(int id) { return kernel_name(id); }
+int lmn_bench_int_peak(lmn_ctx *c, double *butterflies_per_s) {
+    if (!c || !butterflies_per_s) return fail(LMN_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    int sms = 0; CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
+    *butterflies_per_s = measure_peak_butterflies(c->stream, c->d_mods, sms);
+    CK(cudaGetLastError());
+    return 0;
 }
 
 // ---------------- keys ----------------

@@ -22,7 +22,27 @@ namespace lmn {
     }
 
 static inline int ntt_threads(int m) { int t = m / 8; return t < 32 ? 32 : (t > 1024 ? 1024 : t); }
-static inline void count(const Launch &L) { if (L.counter) (*L.counter)++; }
+const char *kernel_name(int id) {
+    static const char *names[KID_COUNT] = {"k_encode_pass", "k_mul_pt", "k_intt_c1", "k_vfix", "k_mac", "k_pintt", "k_vpfix",
+                                           "k_down", "k_rs_intt", "k_rs_apply", "k_pack_out", "k_gather_in", "k_ring_decimate", "other"};
+    return id >= 0 && id < KID_COUNT ? names[id] : "?";
+}
+cudaEvent_t Profiler::get() {
+    if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+    cudaEvent_t e; cudaEventCreate(&e); return e;
+}
+LaunchScope::LaunchScope(const Launch &l, int kid) : L(l), id(kid) {
+    if (L.counter) (*L.counter)++;
+    if (L.prof) {
+        L.prof->launches[id]++;
+        if (L.prof->mask & (1u << id)) {
+            cudaEvent_t e0 = L.prof->get(); e1 = L.prof->get();
+            cudaEventRecord(e0, L.stream);
+            L.prof->spans[id].emplace_back(e0, e1);
+        }
+    }
+}
+LaunchScope::~LaunchScope() { if (e1) cudaEventRecord(e1, L.stream); }
 
 // =====================================================================================================
 // elementwise kernels
@@ -43,10 +63,10 @@ __global__ void k_addsub(const ModDev *mods, int nlimbs, int logn, const u64 *__
     reinterpret_cast<ulonglong2 *>(o + off)[i] = r;
 }
 void launch_addsub(const Launch &L, const DeviceTables &T, int level, const u64 *a, const u64 *b, u64 *o, int sub) {
+    LaunchScope scope(L, KID_OTHER);
     int nl = level + 1, half = T.n / 2, bs = half < 256 ? half : 256;
     dim3 g((half + bs - 1) / bs, 2 * nl);
     k_addsub<<<g, bs, 0, L.stream>>>(T.mods, nl, T.logn, a, b, o, sub);
-    count(L);
 }
 
 __global__ void k_mul_scalar(const ModDev *mods, int nlimbs, int logn, const u64 *__restrict__ a,
@@ -63,10 +83,10 @@ __global__ void k_mul_scalar(const ModDev *mods, int nlimbs, int logn, const u64
     reinterpret_cast<ulonglong2 *>(o + off)[i] = x;
 }
 void launch_mul_scalar(const Launch &L, const DeviceTables &T, int level, const u64 *a, const ulonglong2 *w, u64 *o) {
+    LaunchScope scope(L, KID_OTHER);
     int nl = level + 1, half = T.n / 2, bs = half < 256 ? half : 256;
     dim3 g((half + bs - 1) / bs, 2 * nl);
     k_mul_scalar<<<g, bs, 0, L.stream>>>(T.mods, nl, T.logn, a, w, o);
-    count(L);
 }
 
 // ptm = MForm(pt * (T mod q_i))  : folds the factor T of bgv tensorStandard (degree-0 operand) and the Montgomery
@@ -94,10 +114,10 @@ __global__ void k_prep_pt(const ModDev *mods, int logn, const u64 *__restrict__ 
     ptm[off] = m;
 }
 void launch_prep_pt(const Launch &L, const DeviceTables &T, int level, const u64 *pt, u64 t_mod, u64 *ptm) {
+    LaunchScope scope(L, KID_OTHER);
     int bs = T.n < 256 ? T.n : 256;
     dim3 g((T.n + bs - 1) / bs, level + 1);
     k_prep_pt<<<g, bs, 0, L.stream>>>(T.mods, T.logn, pt, t_mod, ptm);
-    count(L);
 }
 
 // ct x pt for one or two plaintexts, reading the matrix ciphertext once
@@ -124,12 +144,12 @@ __global__ void k_mul_pt(const ModDev *mods, int nlimbs, int logn, const u64 *__
 }
 void launch_mul_pt(const Launch &L, const DeviceTables &T, int level, const u64 *in, uint64_t in_words, int ncols,
                    const u64 *ptm0, const u64 *ptm1, u64 *out0, u64 *out1, uint64_t col_words) {
+    LaunchScope scope(L, KID_MULPT);
     int nl = level + 1, half = T.n / 2, bs = half < 256 ? half : 256;
     dim3 g((half + bs - 1) / bs, 2 * nl, ncols);
     // the job col keeps the context-wide limb stride T.k when it is a workspace col, or nl when it is a store entry
     int kstride = (int)(col_words / 2 >> T.logn);
     k_mul_pt<<<g, bs, 0, L.stream>>>(T.mods, nl, T.logn, in, in_words, ptm0, ptm1, out0, out1, col_words, kstride);
-    count(L);
 }
 
 // =====================================================================================================
@@ -152,10 +172,10 @@ __global__ void __launch_bounds__(1024) k_limb_ntt(const ModDev *mods, const ulo
     }
 }
 void launch_limb_ntt(const Launch &L, const DeviceTables &T, int mod_idx, u64 *limb, int inverse) {
+    LaunchScope scope(L, KID_OTHER);
     size_t smem = (size_t)padded_words(T.n) * 8;
     LMN_DISPATCH_LOGN(T.logn, k_limb_ntt<LG><<<1, ntt_threads(T.n), smem, L.stream>>>(
                                   T.mods, inverse ? T.tw_inv : T.tw_fwd, mod_idx, limb, inverse));
-    count(L);
 }
 
 // =====================================================================================================
@@ -207,12 +227,12 @@ __global__ void __launch_bounds__(256) k_encode_pass(const EncPassArgs A) {
     }
 }
 void launch_encode_pass(const Launch &L, const EncPassArgs &A) {
+    LaunchScope scope(L, KID_ENCODE);
     const uint64_t chunks = A.ct_words / ENC_C;
     const uint32_t tiles = A.n >> A.log_tile;
     dim3 g((unsigned)chunks, tiles);
     size_t smem = ((size_t)ENC_C << A.log_tile) * 8;
     k_encode_pass<<<g, 256, smem, L.stream>>>(A);
-    count(L);
 }
 
 // =====================================================================================================
@@ -426,15 +446,16 @@ void launch_rotate_accumulate(const Launch &L, const DeviceTables &T, const KsCo
     const int N = T.n, nq = Ch.nq, np = Ch.np, jobs = J.jobs;
     const size_t sm_full = (size_t)padded_words(N) * 8;
     const int nt_full = ntt_threads(N);
-    LMN_DISPATCH_LOGN(T.logn, k_intt_c1<LG><<<dim3(nq, jobs), nt_full, sm_full, L.stream>>>(T.mods, T.tw_inv, Cd, J, Ch.k));
-    count(L);
+    { LaunchScope scope(L, KID_INTT_C1);
+    LMN_DISPATCH_LOGN(T.logn, k_intt_c1<LG><<<dim3(nq, jobs), nt_full, sm_full, L.stream>>>(T.mods, T.tw_inv, Cd, J, Ch.k)); }
     bool multi = false;
     for (int d = 0; d < Ch.beta; d++) multi |= Ch.dig_size[d] > 1;
     if (multi) {
         int bs = N < 256 ? N : 256;
+        LaunchScope scope(L, KID_VFIX);
         k_vfix<<<dim3((N + bs - 1) / bs, Ch.beta, jobs), bs, 0, L.stream>>>(T.mods, Cd, J, T.logn);
-        count(L);
-    }
+        }
+    { LaunchScope scope(L, KID_MAC);
     if (T.logn <= 13) {
         const size_t smm = ((size_t)padded_words(N) + 2 * (size_t)N) * 8;
         LMN_DISPATCH_LOGN(T.logn, k_mac<(LG <= 13 ? LG : 13), 1><<<dim3(nq + np, jobs), nt_full, smm, L.stream>>>(
@@ -443,18 +464,17 @@ void launch_rotate_accumulate(const Launch &L, const DeviceTables &T, const KsCo
         const int M = N / 2;
         const size_t smm = ((size_t)padded_words(M) + 2 * (size_t)M) * 8;
         k_mac<13, 2><<<dim3((nq + np) * 2, jobs), ntt_threads(M), smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk);
-    }
-    count(L);
-    LMN_DISPATCH_LOGN(T.logn, k_pintt<LG><<<dim3(np, 2, jobs), nt_full, sm_full, L.stream>>>(T.mods, T.tw_inv, Cd, J));
-    count(L);
+    } }
+    { LaunchScope scope(L, KID_PINTT);
+    LMN_DISPATCH_LOGN(T.logn, k_pintt<LG><<<dim3(np, 2, jobs), nt_full, sm_full, L.stream>>>(T.mods, T.tw_inv, Cd, J)); }
     if (np > 1) {
         int bs = N < 256 ? N : 256;
+        LaunchScope scope(L, KID_VPFIX);
         k_vpfix<<<dim3((N + bs - 1) / bs, 2, jobs), bs, 0, L.stream>>>(T.mods, Cd, J, T.logn);
-        count(L);
-    }
+        }
+    { LaunchScope scope(L, KID_DOWN);
     LMN_DISPATCH_LOGN(T.logn, k_down<LG><<<dim3(nq, 2, jobs), nt_full, sm_full, L.stream>>>(T.mods, T.tw_fwd, Cd, J, gal_el,
-                                                                                        gal_el == 0 ? 1 : 0));
-    count(L);
+                                                                                        gal_el == 0 ? 1 : 0)); }
 }
 
 void launch_keyswitch_level0(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch,
@@ -501,10 +521,10 @@ __global__ void __launch_bounds__(1024) k_rs_apply(const ModDev *mods, const ulo
 void launch_rescale_step(const Launch &L, const DeviceTables &T, const RescaleConsts *Rd, int level, const KsJobs &J) {
     const size_t smf = (size_t)padded_words(T.n) * 8;
     const int nt = ntt_threads(T.n);
-    LMN_DISPATCH_LOGN(T.logn, k_rs_intt<LG><<<dim3(2, J.jobs), nt, smf, L.stream>>>(T.mods, T.tw_inv, Rd, J, T.k, level));
-    count(L);
-    LMN_DISPATCH_LOGN(T.logn, k_rs_apply<LG><<<dim3(level, 2, J.jobs), nt, smf, L.stream>>>(T.mods, T.tw_fwd, Rd, J, T.k));
-    count(L);
+    { LaunchScope scope(L, KID_RS_INTT);
+    LMN_DISPATCH_LOGN(T.logn, k_rs_intt<LG><<<dim3(2, J.jobs), nt, smf, L.stream>>>(T.mods, T.tw_inv, Rd, J, T.k, level)); }
+    { LaunchScope scope(L, KID_RS_APPLY);
+    LMN_DISPATCH_LOGN(T.logn, k_rs_apply<LG><<<dim3(level, 2, J.jobs), nt, smf, L.stream>>>(T.mods, T.tw_fwd, Rd, J, T.k)); }
 }
 
 // =====================================================================================================
@@ -520,9 +540,9 @@ __global__ void k_pack_out(const KsJobs J, int k, int nl, int logn, u64 *__restr
     reinterpret_cast<ulonglong2 *>(dst)[i] = reinterpret_cast<const ulonglong2 *>(src)[i];
 }
 void launch_pack_out(const Launch &L, const DeviceTables &T, const KsJobs &J, int nl, u64 *out) {
+    LaunchScope scope(L, KID_PACK);
     int half = T.n / 2, bs = half < 256 ? half : 256;
     k_pack_out<<<dim3((half + bs - 1) / bs, 2 * nl, J.jobs), bs, 0, L.stream>>>(J, T.k, nl, T.logn, out);
-    count(L);
 }
 __global__ void k_gather_in(const u64 *__restrict__ src, uint64_t src_words, const uint32_t *__restrict__ idx, const KsJobs J,
                             int k, int logn) {
@@ -535,9 +555,9 @@ __global__ void k_gather_in(const u64 *__restrict__ src, uint64_t src_words, con
 }
 void launch_gather_in(const Launch &L, const DeviceTables &T, const u64 *src, uint64_t src_words, const uint32_t *idx,
                       const KsJobs &J) {
+    LaunchScope scope(L, KID_GATHER);
     int half = T.n / 2, bs = half < 256 ? half : 256;
     k_gather_in<<<dim3((half + bs - 1) / bs, 2 * T.k, J.jobs), bs, 0, L.stream>>>(src, src_words, idx, J, T.k, T.logn);
-    count(L);
 }
 
 // ring switch tail (rlwe.SwitchCiphertextRingDegreeNTT, large -> small): INTT in the large ring, keep every
@@ -564,6 +584,7 @@ __global__ void __launch_bounds__(1024) k_ring_decimate(const ModDev *mods, cons
 }
 void launch_ring_decimate(const Launch &L, const DeviceTables &T, const KsJobs &J, int logns, const ModDev *small_mod,
                           const ulonglong2 *small_tw_fwd, u64 *out) {
+    LaunchScope scope(L, KID_DECIMATE);
     const size_t smem = ((size_t)padded_words(T.n) + padded_words(1 << logns)) * 8;
     const int nt = ntt_threads(T.n);
 #define RD(LN, LS) k_ring_decimate<LN, LS><<<dim3(2, J.jobs), nt, smem, L.stream>>>(T.mods, T.tw_inv, J, T.k, small_mod, small_tw_fwd, out)
@@ -571,7 +592,48 @@ void launch_ring_decimate(const Launch &L, const DeviceTables &T, const KsJobs &
     else if (logns == 6) { if (T.logn == 8) RD(8, 6); else if (T.logn == 10) RD(10, 6); }
     else if (logns == 8) { if (T.logn == 10) RD(10, 8); else if (T.logn == 12) RD(12, 8); }
 #undef RD
-    count(L);
+}
+
+// =====================================================================================================
+// integer-pipe ceiling: the radix-8 butterfly network of ntt_fwd_smem on register-resident data (no loads, no
+// barriers), all SMs busy.  Denominator of the integer roofline of the NTT-bound kernels.
+__global__ void __launch_bounds__(256) k_peak_bfly(const ModDev *mods, int rounds, u64 *sink) {
+    const u64 q = mods[0].q, q2 = 2 * q;
+    u64 a[8];
+#pragma unroll
+    for (int r = 0; r < 8; r++) a[r] = (u64)(threadIdx.x * 8 + r + blockIdx.x) % q;
+    ulonglong2 w[7];
+#pragma unroll
+    for (int r = 0; r < 7; r++) { w[r].x = (mods[0].ninv + r * 977) % q; w[r].y = mods[0].ninvs + r; }
+    for (int it = 0; it < rounds; it++) {
+#pragma unroll
+        for (int r = 0; r < 4; r++) bfly_ct(a[r], a[r + 4], w[0], q, q2);
+        bfly_ct(a[0], a[2], w[1], q, q2); bfly_ct(a[1], a[3], w[1], q, q2);
+        bfly_ct(a[4], a[6], w[2], q, q2); bfly_ct(a[5], a[7], w[2], q, q2);
+#pragma unroll
+        for (int r = 0; r < 4; r++) bfly_ct(a[2 * r], a[2 * r + 1], w[3 + r], q, q2);
+#pragma unroll
+        for (int r = 0; r < 8; r++) a[r] = csub(a[r] >> 6, q);   // keep values bounded (cheap, ALU pipe)
+    }
+    u64 x = 0;
+#pragma unroll
+    for (int r = 0; r < 8; r++) x ^= a[r];
+    if (x == 0x1234567) sink[0] = x;
+}
+double measure_peak_butterflies(cudaStream_t stream, const ModDev *mods, int sm_count) {
+    u64 *sink = nullptr;
+    if (cudaMalloc(&sink, 8) != cudaSuccess) return 0.0;
+    const int rounds = 4096, blocks = sm_count * 8, threads = 256;
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    k_peak_bfly<<<blocks, threads, 0, stream>>>(mods, 64, sink);   // warm-up
+    cudaEventRecord(e0, stream);
+    k_peak_bfly<<<blocks, threads, 0, stream>>>(mods, rounds, sink);
+    cudaEventRecord(e1, stream);
+    cudaEventSynchronize(e1);
+    float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(sink);
+    if (ms <= 0) return 0.0;
+    return (double)blocks * threads * rounds * 12.0 / (ms * 1e-3);
 }
 
 // =====================================================================================================

@@ -1,6 +1,8 @@
 // Kernel argument blocks and host launchers of liblumenos_b200 (definitions in kernels.cu).
 #pragma once
 #include <cstdint>
+#include <utility>
+#include <vector>
 #include <cuda_runtime.h>
 
 #include "device.cuh"
@@ -56,14 +58,36 @@ struct EncPassArgs {
     uint32_t tile_mul, stride;    // slot = tile*tile_mul + local*stride
     uint64_t lbits;         // 4 bits per level: local index bit of level s0+i
     int k;                  // Q limbs per poly
-    int logn;               // ring degree
+    int logn;               // log2 of the coefficients per limb in these buffers (ring degree, or a slice of it)
     uint64_t ct_words;      // words per ciphertext (2*k*N)
+};
+
+// kernel classes (profiling / launch accounting)
+enum KernelId { KID_ENCODE = 0, KID_MULPT, KID_INTT_C1, KID_VFIX, KID_MAC, KID_PINTT, KID_VPFIX, KID_DOWN, KID_RS_INTT,
+                KID_RS_APPLY, KID_PACK, KID_GATHER, KID_DECIMATE, KID_OTHER, KID_COUNT };
+const char *kernel_name(int id);
+
+// optional per-class device timing: CUDA event pairs recorded on the launch stream around each launch
+struct Profiler {
+    uint32_t mask = 0;                                    // bit i: time kernels of class i
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> spans[KID_COUNT];
+    std::vector<cudaEvent_t> pool;
+    uint64_t launches[KID_COUNT] = {0};
+    cudaEvent_t get();
 };
 
 struct Launch {
     cudaStream_t stream;
     uint64_t *counter;      // kernel launch counter
+    Profiler *prof;
 };
+struct LaunchScope {        // RAII: counts the launch and brackets it with events when its class is being profiled
+    const Launch &L; int id; cudaEvent_t e1 = nullptr;
+    LaunchScope(const Launch &l, int kid);
+    ~LaunchScope();
+};
+// peak rate of the NTT butterfly instruction mix on the integer pipes, register-resident (no memory traffic)
+double measure_peak_butterflies(cudaStream_t stream, const ModDev *mods, int sm_count);
 
 // ---- elementwise / operator level ----
 void launch_addsub(const Launch &L, const DeviceTables &T, int level, const u64 *a, const u64 *b, u64 *o, int sub);

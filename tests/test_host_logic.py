@@ -102,3 +102,16 @@ def test_context_creation_without_gpu_reports_error(lib):
     params = fhe.BGVParameters(6, P.q, P.p, T, P.psi_q, P.psi_p)
     with pytest.raises(fhe.LumenosError):
         fhe.ServerBFV(fhe.PrimeField(T, O.field_roots_forward(16)), params)
+
+
+def test_hostutil_matches_oracle():
+    """the Python stand-in for the Go host's Lattigo-derived material agrees with the oracle's restatement"""
+    from lumenos_b200 import hostutil as H
+    for logN, k in [(6, 3), (12, 10), (14, 12)]:
+        P = O.Params(logN, k=k)
+        q, p = H.generate_moduli(logN, k)
+        assert q == [int(x) for x in P.q] and p == [int(x) for x in P.p]
+        assert [H.psi_of(m, logN) for m in q[:2] + p] == [int(x) for x in list(P.psi_q[:2]) + list(P.psi_p)]
+    for n in [16, 2048]:
+        assert (H.field_roots_forward(n) == O.field_roots_forward(n)).all()
+    assert H.num_q_primes_for_ntt(4096) == 12

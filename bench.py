@@ -167,6 +167,7 @@ def main():
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cols-override", type=int, default=0, help="profiling only: shrink the matrix to this many columns, keeping the named config's k, N and rows")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)
@@ -186,9 +187,11 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     rows, cols, logN = CONFIGS[args.config]
-    N, n = 1 << logN, cols * RHO_INV
     T = H.T_DEFAULT
     k = H.num_q_primes_for_ntt(cols, T)
+    if args.cols_override:
+        cols = args.cols_override
+    N, n = 1 << logN, cols * RHO_INV
     if cols % G or N % G or (N // G) < 32:
         raise SystemExit("config does not shard over %d GPUs" % G)
     t_setup = time.perf_counter()
@@ -403,7 +406,7 @@ def main():
         out = {
             "metric": "ligero_server_prove_eval_s", "value": ms_per_step / 1e3, "unit": "s", "n_gpus": G, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-            "config": {"workload": "%s: %dx%d LogN=%d k=%d encode + prove eval (inner products r,b + %d query columns)" % (args.config, rows, cols, logN, k, nq_total),
+            "config": {"workload": "%s%s: %dx%d LogN=%d k=%d encode + prove eval (inner products r,b + %d query columns)" % (args.config, " (PROFILING SUBSET of columns)" if args.cols_override else "", rows, cols, logN, k, nq_total),
                        "l2": "inputs (%.1f GiB matrix per GPU) far exceed the 126 MB L2; no flush needed" % (mat_cols.nbytes / 2**30),
                        "sharding": "1 GPU" if G == 1 else "columns/%d for inner products + query rescale, coefficient slices/%d for Encode, all-to-all of queried slices" % (G, G),
                        "batch_jobs": args.batch},

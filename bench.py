@@ -174,7 +174,7 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from lumenos_b200 import _capi, fhe, hostutil as H
+    from lumenos_b200 import _capi, fhe, hostutil as H, sharding
 
     rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
     G = world
@@ -227,7 +227,7 @@ def main():
     qrng = np.random.default_rng(99)
     qidx = (qrng.integers(0, 2**62, size=nq_total) % n).astype(np.uint32)
     qidx[7] = qidx[3]
-    my_q = list(range(rank, nq_total, G))
+    my_q = sharding.queries_of(nq_total, rank, G)
     lout = 1
 
     mat_cols_t = rand_cts(cols_loc, N)                  # column shard: inner products
@@ -266,11 +266,7 @@ def main():
             _capi.check(lib.lmn_query_columns(be.ctx, enc_store.h, my_idx.ctypes.data_as(vp), len(my_idx), queried.h))
         else:
             # coefficient slices of the queried columns -> whole ciphertexts on the rank that rescales them
-            send = torch.cat([enc_t[torch.as_tensor(qidx[d::G].astype(np.int64), device=dev)] for d in range(G)])
-            send_splits = [len(qidx[d::G]) for d in range(G)]
-            recv = torch.empty((G * len(my_q), 2, k, Ns), dtype=torch.int64, device=dev)
-            dist.all_to_all_single(recv, send, [len(my_q)] * G, send_splits)
-            full = recv.view(G, len(my_q), 2, k, Ns).permute(1, 2, 3, 0, 4).contiguous()
+            full = sharding.exchange_queried(enc_t, qidx, rank, G)
             st = fhe.CiphertextStore(be, len(my_q), k - 1, wrap_ptr=full.data_ptr())
             _capi.check(lib.lmn_query_columns(be.ctx, st.h, arange_idx.ctypes.data_as(vp), len(my_q), queried.h))
             torch.cuda.current_stream(dev).synchronize()

@@ -1,0 +1,72 @@
+"""2-GPU equivalence (-m gpu, skipped with fewer than 2 devices): the sharded path (coefficient-sliced Encode,
+column-sharded inner products, all-to-all of queried slices) produces byte-identical outputs to the 1-GPU path."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+WORKER = r'''
+import os, sys
+sys.path.insert(0, %r); sys.path.insert(0, os.path.join(%r, "tests"))
+import ctypes as C
+import numpy as np, torch, torch.distributed as dist
+from helpers import Scenario
+from lumenos_b200 import fhe, sharding, _capi
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local); dev = torch.device("cuda", local)
+dist.init_process_group("nccl", device_id=dev)
+S = Scenario(logN=8, rows=256, cols=16, k=5)
+P, lib = S.P, _capi.lib()
+be = S.backend(device=local, stream=torch.cuda.current_stream(dev).cuda_stream)
+want_enc = P.fhe_encode(S.cts, 2, S.zero, S.roots)
+# Encode on coefficient slices
+lo, hi = sharding.coefficient_range(P.N, rank, world)
+m_sl = torch.from_numpy(S.cts[..., lo:hi].astype(np.int64)).contiguous().to(dev)
+z_sl = torch.from_numpy(S.zero[None][..., lo:hi].astype(np.int64)).contiguous().to(dev)
+e_sl = torch.empty((2 * S.cols, 2, P.k, hi - lo), dtype=torch.int64, device=dev)
+vp = C.c_void_p
+_capi.check(lib.lmn_encode_lanes(be.ctx, be._plan(S.cols, 2), vp(m_sl.data_ptr()), vp(z_sl.data_ptr()), vp(e_sl.data_ptr()), (hi - lo).bit_length() - 1))
+be.Synchronize()
+assert np.array_equal(e_sl.cpu().numpy().astype(np.uint64), want_enc[..., lo:hi]), "sliced Encode differs"
+# query columns via the all-to-all
+qidx = np.random.default_rng(3).integers(0, 2 * S.cols, size=21); qidx[4] = qidx[1]
+full = sharding.exchange_queried(e_sl, qidx, rank, world)
+mine = sharding.queries_of(len(qidx), rank, world)
+st = fhe.CiphertextStore(be, len(mine), P.k - 1, wrap_ptr=full.data_ptr())
+out = be.NewStore(len(mine), 1)
+idx = np.arange(len(mine), dtype=np.uint32)
+_capi.check(lib.lmn_query_columns(be.ctx, st.h, idx.ctypes.data_as(vp), len(mine), out.h))
+got = out.download()
+for j, qi in enumerate(mine):
+    assert np.array_equal(got[j], P.rescale_to_level1(want_enc[qidx[qi]])[0]), "queried column %%d differs" %% qi
+# inner products on the column shard
+a, b = sharding.column_range(S.cols, rank, world)
+mat = be.NewStore(b - a).upload(S.cts[a:b])
+mr, mz = be.NewStore(b - a, 1), be.NewStore(b - a, 1)
+_capi.check(lib.lmn_inner_product2(be.ctx, mat.h, S.rpt.ctypes.data_as(vp), S.bpt.ctypes.data_as(vp), S.rows, mr.h, mz.h))
+gr, gz = mr.download(), mz.download()
+for j in range(a, b):
+    assert np.array_equal(gr[j - a], P.inner_sum_eval_column(S.cts[j], S.rpt, S.rows, S.gal, S.evks)[0])
+    assert np.array_equal(gz[j - a], P.inner_sum_eval_column(S.cts[j], S.bpt, S.rows, S.gal, S.evks)[0])
+be.Close()
+dist.barrier()
+print("rank", rank, "ok")
+dist.destroy_process_group()
+'''
+
+
+def test_two_gpu_equivalence(tmp_path):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER % (ROOT, ROOT))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29655", str(script)],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count("ok") == 2

@@ -364,11 +364,7 @@ def main():
             return ptr
         h_mat = halloc(mat_cols.nbytes)
         _capi.check(lib.lmn_store_download(mat_cols.h, 0, cols_loc, h_mat))
-        h_enc = None
-        if G > 1:
-            h_enc = halloc(mat_enc_t.numel() * 8)
-            torch.cuda.synchronize(dev)
-            C.memmove(h_enc, mat_enc_t.cpu().numpy().ctypes.data, mat_enc_t.numel() * 8)
+        h_enc_t = mat_enc_t.cpu().pin_memory() if G > 1 else None   # pinned host copy of this rank's Encode slice
         h_r, h_z, h_q = halloc(matR.nbytes), halloc(matZ.nbytes), halloc(queried.nbytes)
         h2d = mat_cols.nbytes + (mat_enc_t.numel() * 8 if G > 1 else 0) + 2 * k * N * 8
         d2h = matR.nbytes + matZ.nbytes + queried.nbytes
@@ -376,8 +372,7 @@ def main():
         def e2e_step():
             _capi.check(lib.lmn_store_upload(mat_cols.h, 0, cols_loc, h_mat))
             if G > 1:
-                src = (C.c_char * (mat_enc_t.numel() * 8)).from_address(h_enc.value)
-                mat_enc_t.view(torch.uint8).copy_(torch.frombuffer(src, dtype=torch.uint8), non_blocking=True)
+                mat_enc_t.copy_(h_enc_t, non_blocking=True)
             step()
             _capi.check(lib.lmn_store_download(matR.h, 0, cols_loc, h_r))
             _capi.check(lib.lmn_store_download(matZ.h, 0, cols_loc, h_z))
@@ -387,7 +382,7 @@ def main():
         e2e_ms = timed(e2e_step, e2e_steps) / e2e_steps
         e2e = {"value": e2e_ms / 1e3, "unit": "s", "h2d_bytes_per_step": int(h2d) * G, "d2h_bytes_per_step": int(d2h) * G, "steps": e2e_steps,
                "path": "lmn_store_upload (pinned host -> HBM) + lmn_encode + lmn_inner_product2 + lmn_query_columns + lmn_store_download"}
-        for hptr in (h_mat, h_enc, h_r, h_z, h_q):
+        for hptr in (h_mat, h_r, h_z, h_q):
             if hptr:
                 lib.lmn_host_free(hptr)
 

@@ -345,6 +345,8 @@ def main():
                        "algorithmic_min_bytes": (cols + 1 + n) * ctw, "share_of_step": enc_ms / total_ms}
 
     # kernel-class breakdown of one extra (untimed) step
+    for i in range(lib.lmn_kernel_count()):
+        lib.lmn_profile_read(be.ctx, i, None, None, 1)
     _capi.check(lib.lmn_profile_enable(be.ctx, 0xFFFFFFFF))
     step()
     breakdown = {}

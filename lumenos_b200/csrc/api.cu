@@ -35,7 +35,9 @@ struct lmn_ctx {
     DeviceTables T{};
     std::map<int, std::pair<KsConsts, KsConsts *>> ks;      // per level
     std::map<int, RescaleConsts *> rs;                      // per level
-    std::map<u64, u64 *> galois;                            // galEl -> device evk
+    std::map<u64, u64 *> galois;                            // galEl -> device evk (rows pre-scaled, see key_scale)
+    int key_scale[MAX_DIGITS][MAX_LIMBS];                   // s(d, gm): evk rows of non-own (d, gm) carry the factor 2^s
+    u64 *d_key_fm = nullptr;                                // [beta][k+np] 2^s in Montgomery form (0 = own row)
     // ring switch
     int logn_small = 0;
     u64 *d_rs_evk = nullptr;
@@ -43,7 +45,7 @@ struct lmn_ctx {
     ulonglong2 *d_small_tw = nullptr;
     // workspace
     uint32_t batch = 64;
-    u64 *ws_col = nullptr, *ws_y = nullptr, *ws_acc = nullptr, *ws_pt = nullptr;
+    u64 *ws_col = nullptr, *ws_y = nullptr, *ws_acc = nullptr, *ws_mu = nullptr, *ws_pt = nullptr;
     uint32_t *ws_idx = nullptr; size_t ws_idx_cap = 0;
     ulonglong2 *ws_scalar = nullptr;
     uint32_t ws_jobs = 0;
@@ -94,6 +96,34 @@ static void build_twiddles(u64 q, u64 psi, int logn, std::vector<ulonglong2> &fw
     }
 }
 
+// s(d, gm) for every max-level digit d and every modulus gm outside it: the smallest e in [0, 16] for which all
+// 2^e (Q_d/q_a) mod m are below 2^31 in signed form gives s = 64 - e (fast 64x32-bit base conversion); otherwise s = 64
+// (generic 64x64-bit path).  Single-prime digits need no Montgomery step: s = 0.
+static void build_key_scale(lmn_ctx *c) {
+    const int k = c->k, np = c->np, KP = k + np, beta = (k + np - 1) / np;
+    memset(c->key_scale, 0, sizeof(c->key_scale));
+    for (int d = 0; d < beta; d++) {
+        const int s0 = d * np, nd = std::min(np, k - s0);
+        for (int gm = 0; gm < KP; gm++) {
+            if (gm >= s0 && gm < s0 + nd) continue;
+            if (nd < 2) { c->key_scale[d][gm] = 0; continue; }
+            const u64 m = c->mod(gm);
+            int best = 64;
+            for (int e = 0; e <= 16 && best == 64; e++) {
+                bool ok = true;
+                for (int a = 0; a < nd && ok; a++) {
+                    u64 pr = h_powmod(2, (u64)e, m);
+                    for (int b = 0; b < nd; b++) if (b != a) pr = h_mulmod(pr, c->q[s0 + b] % m, m);
+                    u64 mag = pr <= m / 2 ? pr : m - pr;
+                    ok = mag < (1ull << 31);
+                }
+                if (ok) best = 64 - e;
+            }
+            c->key_scale[d][gm] = best;
+        }
+    }
+}
+
 static void build_ks_consts(const lmn_ctx *c, int level, KsConsts &K) {
     memset(&K, 0, sizeof(K));
     const int nq = level + 1, np = c->np, k = c->k;
@@ -112,11 +142,39 @@ static void build_ks_consts(const lmn_ctx *c, int level, KsConsts &K) {
             K.intt_w[i] = w; K.intt_ws[i] = h_shoup(w, qi);
         }
         for (int tix = 0; tix < nq + np; tix++) {
-            u64 m = c->mod(ks_mod_index(tix, nq, k));
-            for (int a = 0; a < K.dig_size[d]; a++) K.mu_c[d][tix][a] = h_mform(digit_prod(d, K.dig_start[d] + a, m), m);
-            u64 qd = digit_prod(d, -1, m);
-            u64 v = h_mulmod((u64)(K.dig_size[d] - 1) % m, qd, m);
-            K.mu_neg[d][tix] = v ? m - v : 0;
+            const int gm = ks_mod_index(tix, nq, k);
+            if (gm >= K.dig_start[d] && gm < K.dig_start[d] + K.dig_size[d]) continue;   // own limb
+            const u64 m = c->mod(gm);
+            const int nd = K.dig_size[d], s = c->key_scale[d][gm];
+            // r must equal value * 2^-s (mod m) because the key rows of (d, gm) carry 2^s
+            const u64 ginv = h_invmod(h_powmod(2, (u64)s, m), m);
+            K.mu_g_w[d][tix] = ginv; K.mu_g_ws[d][tix] = h_shoup(ginv, m);
+            if (nd < 2) continue;
+            const u64 scale = h_powmod(2, (u64)(64 - s), m);                 // c_a = 2^(64-s) Q_d/q_a mod m
+            const bool same_as_max = nd == std::min(np, k - d * np);
+            u64 cfull[MAX_P]; bool small = same_as_max;
+            u128 maxneg = 0;
+            for (int a = 0; a < nd; a++) {
+                cfull[a] = h_mulmod(digit_prod(d, K.dig_start[d] + a, m), scale, m);
+                u64 mag = cfull[a] <= m / 2 ? cfull[a] : m - cfull[a];
+                if (mag >= (1ull << 31)) small = false;
+            }
+            const u64 kconst = [&] { u64 v = h_mulmod(h_mulmod((u64)(nd - 1) % m, digit_prod(d, -1, m), m), scale, m); return v ? m - v : 0; }();
+            if (small) {
+                K.mu_fast[d][tix] = 1;
+                for (int a = 0; a < nd; a++) {
+                    bool neg = cfull[a] > m / 2;
+                    u64 mag = neg ? m - cfull[a] : cfull[a];
+                    K.mu_mag[d][tix][a] = (uint32_t)mag;
+                    if (neg) { K.mu_sgn[d][tix] |= 1u << a; maxneg += (u128)((u64)nd * c->q[K.dig_start[d] + a]) * mag; }
+                }
+                u128 kk = (u128)kconst + (u128)(maxneg / m + 1) * m;
+                K.mu_k_lo[d][tix] = (u64)kk; K.mu_k_hi[d][tix] = (u64)(kk >> 64);
+            } else {
+                K.mu_fast[d][tix] = 0;
+                for (int a = 0; a < nd; a++) K.mu_c[d][tix][a] = cfull[a];
+                K.mu_k_lo[d][tix] = kconst; K.mu_k_hi[d][tix] = 0;
+            }
         }
     }
     auto p_prod = [&](int skip, u64 m) {
@@ -176,19 +234,21 @@ static int get_rs(lmn_ctx *c, int level, const RescaleConsts **dev) {
 
 static int ensure_workspace(lmn_ctx *c, uint32_t jobs) {
     if (c->ws_jobs >= jobs) return 0;
-    if (c->ws_col) { cudaFree(c->ws_col); cudaFree(c->ws_y); cudaFree(c->ws_acc); c->ws_col = c->ws_y = c->ws_acc = nullptr; c->ws_jobs = 0; }
+    if (c->ws_col) { cudaFree(c->ws_col); cudaFree(c->ws_y); cudaFree(c->ws_acc); cudaFree(c->ws_mu); c->ws_col = c->ws_y = c->ws_acc = c->ws_mu = nullptr; c->ws_jobs = 0; }
     size_t N = c->n, k = c->k, KP = c->k + c->np;
     CK(cudaMalloc(&c->ws_col, jobs * 2 * k * N * 8));
     CK(cudaMalloc(&c->ws_y, jobs * k * N * 8));
     CK(cudaMalloc(&c->ws_acc, jobs * 2 * KP * N * 8));
+    CK(cudaMalloc(&c->ws_mu, jobs * (size_t)((c->k + c->np - 1) / c->np) * KP * N * 8));
     c->ws_jobs = jobs;
     return 0;
 }
 static KsJobs jobs_view(lmn_ctx *c, uint32_t first, uint32_t jobs) {
     size_t N = c->n, k = c->k, KP = c->k + c->np;
     KsJobs J;
-    J.col_words = 2 * k * N; J.y_words = k * N; J.acc_words = 2 * KP * N;
+    J.col_words = 2 * k * N; J.y_words = k * N; J.acc_words = 2 * KP * N; J.mu_words = (size_t)((c->k + c->np - 1) / c->np) * KP * N;
     J.col = c->ws_col + first * J.col_words; J.y = c->ws_y + first * J.y_words; J.acc = c->ws_acc + first * J.acc_words;
+    J.mu = c->ws_mu + first * J.mu_words;
     J.jobs = (int)jobs;
     return J;
 }
@@ -252,6 +312,22 @@ int lmn_ctx_create(const lmn_params *P, int device, lmn_ctx **out) {
     if (e != cudaSuccess) { int rc = fail(LMN_ERR_CUDA, std::string("context setup: ") + cudaGetErrorString(e)); lmn_ctx_destroy(c); return rc; }
     c->stream = c->own_stream;
     c->T = DeviceTables{c->logn, c->n, c->k, c->np, c->d_mods, c->d_twf, c->d_twi};
+    build_key_scale(c);
+    {
+        const int beta = (c->k + c->np - 1) / c->np;
+        std::vector<u64> fm((size_t)beta * KP, 0);
+        for (int d = 0; d < beta; d++)
+            for (int gm = 0; gm < KP; gm++) {
+                const int s0 = d * c->np, nd = std::min(c->np, c->k - s0);
+                if (gm >= s0 && gm < s0 + nd) continue;
+                if (c->key_scale[d][gm] == 0) continue;
+                const u64 m = c->mod(gm);
+                fm[(size_t)d * KP + gm] = h_mform(h_powmod(2, (u64)c->key_scale[d][gm], m), m);
+            }
+        e = cudaMalloc(&c->d_key_fm, fm.size() * 8);
+        if (e == cudaSuccess) e = cudaMemcpy(c->d_key_fm, fm.data(), fm.size() * 8, cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) { int rc = fail(LMN_ERR_CUDA, std::string("context setup: ") + cudaGetErrorString(e)); lmn_ctx_destroy(c); return rc; }
+    }
     *out = c;
     return 0;
 }
@@ -265,7 +341,7 @@ void lmn_ctx_destroy(lmn_ctx *c) {
     for (auto &kv : c->galois) cudaFree(kv.second);
     cudaFree(c->d_mods); cudaFree(c->d_twf); cudaFree(c->d_twi); cudaFree(c->ws_pt); cudaFree(c->ws_scalar);
     cudaFree(c->ws_col); cudaFree(c->ws_y); cudaFree(c->ws_acc); cudaFree(c->ws_idx);
-    cudaFree(c->d_rs_evk); cudaFree(c->d_small_mod); cudaFree(c->d_small_tw);
+    cudaFree(c->d_rs_evk); cudaFree(c->d_small_mod); cudaFree(c->d_small_tw); cudaFree(c->d_key_fm); cudaFree(c->ws_mu);
     for (int i = 0; i < KID_COUNT; i++) for (auto &sp : c->prof.spans[i]) { cudaEventDestroy(sp.first); cudaEventDestroy(sp.second); }
     for (auto e : c->prof.pool) cudaEventDestroy(e);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -548,6 +624,7 @@ int lmn_load_galois_key(lmn_ctx *c, uint64_t gal_el, const uint64_t *evk) {
     auto it = c->galois.find(gal_el);
     if (it != c->galois.end()) d = it->second; else CK(cudaMalloc(&d, bytes));
     CK(cudaMemcpyAsync(d, evk, bytes, cudaMemcpyHostToDevice, c->stream));
+    launch_scale_rows(c->L(), c->T, d, c->d_key_fm, beta);   // fold 2^s into the rows the base-converted digits multiply
     CK(cudaStreamSynchronize(c->stream));
     c->galois[gal_el] = d;
     return 0;
@@ -563,6 +640,8 @@ int lmn_load_ring_switch_key(lmn_ctx *c, uint32_t logns, const uint64_t *evk, ui
     size_t bytes = (size_t)beta * 2 * (c->k + c->np) * c->n * 8;
     if (!c->d_rs_evk) CK(cudaMalloc(&c->d_rs_evk, bytes));
     CK(cudaMemcpy(c->d_rs_evk, evk, bytes, cudaMemcpyHostToDevice));
+    launch_scale_rows(c->L(), c->T, c->d_rs_evk, c->d_key_fm, beta);
+    CK(cudaStreamSynchronize(c->stream));
     u64 q0 = c->q[0];
     if (!psi_small) {
         // psi_small = psi^(N/N'): read psi back from the forward table (entry bitrev(1) = N/2 holds psi)

@@ -23,7 +23,7 @@ namespace lmn {
 
 static inline int ntt_threads(int m) { int t = m / 8; return t < 32 ? 32 : (t > 1024 ? 1024 : t); }
 const char *kernel_name(int id) {
-    static const char *names[KID_COUNT] = {"k_encode_pass", "k_mul_pt", "k_intt_c1", "k_vfix", "k_mac", "k_pintt", "k_vpfix",
+    static const char *names[KID_COUNT] = {"k_encode_pass", "k_mul_pt", "k_intt_c1", "k_modup", "k_mac", "k_pintt", "k_vpfix",
                                            "k_down", "k_rs_intt", "k_rs_apply", "k_pack_out", "k_gather_in", "k_ring_decimate", "other"};
     return id >= 0 && id < KID_COUNT ? names[id] : "?";
 }
@@ -152,6 +152,24 @@ void launch_mul_pt(const Launch &L, const DeviceTables &T, int level, const u64 
     k_mul_pt<<<g, bs, 0, L.stream>>>(T.mods, nl, T.logn, in, in_words, ptm0, ptm1, out0, out1, col_words, kstride);
 }
 
+// key rows (digit d, component c, modulus gm) times a per-(d, gm) constant given in Montgomery form (0 = leave the row)
+__global__ void k_scale_rows(u64 *__restrict__ evk, const ModDev *mods, const u64 *__restrict__ fm, int KP, int logn) {
+    const int row = blockIdx.y, gm = row % KP, d = row / (2 * KP);
+    const u64 f = fm[d * KP + gm];
+    if (!f) return;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (1 << logn)) return;
+    const ModDev md = mods[gm];
+    u64 *x = evk + ((size_t)row << logn);
+    x[i] = mont_mul(x[i], f, md.q, md.qinv);
+}
+void launch_scale_rows(const Launch &L, const DeviceTables &T, u64 *evk, const u64 *fm_dev, int beta) {
+    LaunchScope scope(L, KID_OTHER);
+    int bs = T.n < 256 ? T.n : 256;
+    const int KP = T.k + T.np;
+    k_scale_rows<<<dim3((T.n + bs - 1) / bs, beta * 2 * KP), bs, 0, L.stream>>>(evk, T.mods, fm_dev, KP, T.logn);
+}
+
 // =====================================================================================================
 // single-limb NTT / INTT (test hook; the production kernels fuse these transforms with their neighbours)
 // =====================================================================================================
@@ -254,22 +272,95 @@ __global__ void __launch_bounds__(1024) k_intt_c1(const ModDev *mods, const ulon
     for (int n = threadIdx.x; n < N; n += blockDim.x) dst[n] = mul_shoup(sm[PAD(n)], w, ws, md.q);
 }
 
-// (2) fold the float64 overflow estimate v of reconstructRNS into the first residue of each multi-prime digit:
-//     y_s0 += (nd - 1 - v) q_s0,  v = floor(sum_a float64(y_a)/float64(q_a))   (same operation order as Go)
-__global__ void k_vfix(const ModDev *mods, const KsConsts *C, const KsJobs J, int logn) {
+// (2) base conversion of every digit to every other modulus, once per coefficient (lattigo DecomposeAndSplit:
+//     reconstructRNS + multSum).  The float64 overflow estimate v = floor(sum_a float64(y_a)/float64(q_a)) (same operation
+//     order as Go) is folded into the first residue: z_0 = y_0 + (nd-1-v) q_0, so that the value is sum_a z_a (Q_d/q_a)
+//     - (nd-1) Q_d with no data-dependent term.  S = 2: the first Cooley-Tukey level of the length-N transform is applied
+//     here (X + wY, X - wY), so that k_mac can run two independent half-length transforms.
+template <int S>
+__global__ void __launch_bounds__(256) k_modup(const ModDev *mods, const ulonglong2 *tw_fwd, const KsConsts *C, const KsJobs J,
+                                                int logn, int beta_max) {
     const int d = blockIdx.y, job = blockIdx.z;
     const int nd = C->dig_size[d], s0 = C->dig_start[d];
-    if (nd < 2) return;
+    const int nq = C->nq, k = C->k, KP = k + C->np;
+    const int M = (1 << logn) / S;
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
-    if (n >= (1 << logn)) return;
-    u64 *y = J.y + (size_t)job * J.y_words;
-    double vf = 0.0;
-    for (int a = 0; a < nd; a++) {
-        const u64 ya = y[((size_t)(s0 + a) << logn) + n];
-        vf = __dadd_rn(vf, __ddiv_rn(__ull2double_rn(ya), __ull2double_rn(mods[s0 + a].q)));
+    if (n >= M) return;
+    const u64 *y = J.y + (size_t)job * J.y_words;
+    u64 *mu = J.mu + (size_t)job * J.mu_words + (((size_t)d * KP) << logn);
+    u64 z[S][MAX_P];
+#pragma unroll
+    for (int r = 0; r < S; r++) {
+        double vf = 0.0;
+#pragma unroll
+        for (int a = 0; a < MAX_P; a++) {
+            if (a < nd) {
+                z[r][a] = y[((size_t)(s0 + a) << logn) + n + r * M];
+                vf = __dadd_rn(vf, __ddiv_rn(__ull2double_rn(z[r][a]), __ull2double_rn(mods[s0 + a].q)));
+            } else z[r][a] = 0;
+        }
+        if (nd >= 2) z[r][0] += (u64)(nd - 1 - (int)__double2ull_rz(vf)) * mods[s0].q;
     }
-    const u64 v = __double2ull_rz(vf);
-    y[((size_t)s0 << logn) + n] += (u64)(nd - 1 - (int)v) * mods[s0].q;
+    for (int tix = 0; tix < nq + C->np; tix++) {
+        if (tix < nq && tix >= s0 && tix < s0 + nd) continue;   // own limbs are copied from the NTT-domain input
+        const int gm = ks_mod_index(tix, nq, k);
+        const u64 p = mods[gm].q, pinv = mods[gm].qinv, p2 = 2 * p;
+        u64 vals[S];
+        if (nd == 1) {
+            // single-prime digit: centred lift (DecomposeAndSplit, decompLvl < 0), then the key-row scale 2^(e-64)
+            const u64 qd = mods[s0].q, hq = qd >> 1, gw = C->mu_g_w[d][tix], gws = C->mu_g_ws[d][tix], pmu = mods[gm].mu;
+#pragma unroll
+            for (int r = 0; r < S; r++) {
+                const u64 c = z[r][0];
+                const bool neg = c >= hq;
+                const u64 rr = barrett(neg ? qd - c : c, p, pmu);
+                vals[r] = mul_shoup_lazy(neg ? (rr ? p - rr : 0) : rr, gw, gws, p);
+            }
+        } else if (C->mu_fast[d][tix]) {
+            const uint32_t sgn = C->mu_sgn[d][tix];
+            uint32_t mag[MAX_P];
+#pragma unroll
+            for (int a = 0; a < MAX_P; a++) mag[a] = a < nd ? C->mu_mag[d][tix][a] : 0;
+            const u64 klo = C->mu_k_lo[d][tix], khi = C->mu_k_hi[d][tix];
+#pragma unroll
+            for (int r = 0; r < S; r++) {
+                u64 lo = klo, hi = khi;
+#pragma unroll
+                for (int a = 0; a < MAX_P; a++) {
+                    if (a < nd) {
+                        // 64 x 32 -> 96-bit product with two 32x32 multiplies
+                        const u64 p0 = (u64)(uint32_t)z[r][a] * mag[a];
+                        const u64 p1 = (u64)(uint32_t)(z[r][a] >> 32) * mag[a];
+                        const u64 plo = p0 + (p1 << 32);
+                        const u64 phi = (p1 >> 32) + (plo < p0);
+                        if ((sgn >> a) & 1) { const u64 t = lo; lo -= plo; hi -= phi + (t < plo); }
+                        else { lo += plo; hi += phi + (lo < plo); }
+                    }
+                }
+                vals[r] = mont_reduce_lazy(lo, hi, p, pinv);
+            }
+        } else {
+            u64 cm[MAX_P];
+#pragma unroll
+            for (int a = 0; a < MAX_P; a++) cm[a] = a < nd ? C->mu_c[d][tix][a] : 0;
+            const u64 klo = C->mu_k_lo[d][tix], khi = C->mu_k_hi[d][tix];
+#pragma unroll
+            for (int r = 0; r < S; r++) {
+                u64 lo = klo, hi = khi;
+#pragma unroll
+                for (int a = 0; a < MAX_P; a++)
+                    if (a < nd) mac128(lo, hi, z[r][a], cm[a]);
+                vals[r] = csub(mont_reduce_lazy(lo, hi, p, pinv), p2);
+            }
+        }
+        u64 *o = mu + ((size_t)gm << logn);
+        if (S == 2) {
+            const ulonglong2 w1 = tw_fwd[((size_t)gm << logn) + 1];
+            const u64 t = mul_shoup_lazy(vals[1], w1.x, w1.y, p);
+            o[n] = vals[0] + t;
+            o[n + M] = vals[0] - t + p2;
+        } else o[n] = vals[0];
+    }
 }
 
 // (3) for one target modulus (and one half of the output when the ring is larger than the block transform):
@@ -287,9 +378,8 @@ __global__ void __launch_bounds__(1024) k_mac(const ModDev *mods, const ulonglon
     const int nq = C->nq, k = C->k, KP = k + C->np;
     const int gm = ks_mod_index(tix, nq, k);
     const ModDev md = mods[gm];
-    const u64 p = md.q, p2 = 2 * md.q;
+    const u64 p = md.q;
     const ulonglong2 *tw = tw_fwd + ((size_t)gm << LOGN);
-    const u64 *y = J.y + (size_t)job * J.y_words;
     const u64 *c1 = J.col + (size_t)job * J.col_words + ((size_t)k << LOGN);  // poly 1 (NTT domain)
     for (int n = threadIdx.x; n < M; n += blockDim.x) { acc0[n] = 0; acc1[n] = 0; }
 
@@ -309,46 +399,9 @@ __global__ void __launch_bounds__(1024) k_mac(const ModDev *mods, const ulonglon
             continue;
         }
         __syncthreads();  // previous digit's readers of `data` are done
-        if (nd == 1) {
-            // single-prime digit: centred lift (DecomposeAndSplit, decompLvl < 0)
-            const u64 qd = mods[s0].q, hq = qd >> 1;
-            const u64 *ys = y + ((size_t)s0 << LOGN);
-            const ulonglong2 w1 = tw[1];
-            for (int n = threadIdx.x; n < M; n += blockDim.x) {
-                u64 vals[S];
-#pragma unroll
-                for (int r = 0; r < S; r++) {
-                    const u64 c = ys[n + r * M];
-                    const bool neg = c >= hq;
-                    const u64 rr = barrett(neg ? qd - c : c, p, md.mu);
-                    vals[r] = neg ? (rr ? p - rr : 0) : rr;
-                }
-                if (S == 2) {
-                    const u64 t = mul_shoup_lazy(vals[1], w1.x, w1.y, p);
-                    data[PAD(n)] = h == 0 ? vals[0] + t : vals[0] - t + p2;
-                } else data[PAD(n)] = vals[0];
-            }
-        } else {
-            u64 cm[MAX_P];
-#pragma unroll
-            for (int a = 0; a < MAX_P; a++) cm[a] = a < nd ? C->mu_c[d][tix][a] : 0;
-            const u64 neg = C->mu_neg[d][tix];
-            const ulonglong2 w1 = tw[1];
-            for (int n = threadIdx.x; n < M; n += blockDim.x) {
-                u64 vals[S];
-#pragma unroll
-                for (int r = 0; r < S; r++) {
-                    u64 lo = 0, hi = neg;
-#pragma unroll
-                    for (int a = 0; a < MAX_P; a++)
-                        if (a < nd) mac128(lo, hi, y[((size_t)(s0 + a) << LOGN) + n + r * M], cm[a]);
-                    vals[r] = csub(mont_reduce_lazy(lo, hi, p, md.qinv), p2);
-                }
-                if (S == 2) {
-                    const u64 t = mul_shoup_lazy(vals[1], w1.x, w1.y, p);
-                    data[PAD(n)] = h == 0 ? vals[0] + t : vals[0] - t + p2;
-                } else data[PAD(n)] = vals[0];
-            }
+        {
+            const u64 *src = J.mu + (size_t)job * J.mu_words + ((((size_t)d * KP) + gm) << LOGN) + (size_t)h * M;
+            for (int n = threadIdx.x; n < M; n += blockDim.x) data[PAD(n)] = src[n];
         }
         __syncthreads();
         ntt_fwd_smem<LOGM>(data, tw, p, S + h);
@@ -448,13 +501,14 @@ void launch_rotate_accumulate(const Launch &L, const DeviceTables &T, const KsCo
     const int nt_full = ntt_threads(N);
     { LaunchScope scope(L, KID_INTT_C1);
     LMN_DISPATCH_LOGN(T.logn, k_intt_c1<LG><<<dim3(nq, jobs), nt_full, sm_full, L.stream>>>(T.mods, T.tw_inv, Cd, J, Ch.k)); }
-    bool multi = false;
-    for (int d = 0; d < Ch.beta; d++) multi |= Ch.dig_size[d] > 1;
-    if (multi) {
-        int bs = N < 256 ? N : 256;
+    {
         LaunchScope scope(L, KID_VFIX);
-        k_vfix<<<dim3((N + bs - 1) / bs, Ch.beta, jobs), bs, 0, L.stream>>>(T.mods, Cd, J, T.logn);
-        }
+        const int M = T.logn >= 14 ? N / 2 : N;
+        const int bs = M < 256 ? M : 256;
+        const int beta_max = (Ch.k + np - 1) / np;
+        if (T.logn >= 14) k_modup<2><<<dim3((M + bs - 1) / bs, Ch.beta, jobs), bs, 0, L.stream>>>(T.mods, T.tw_fwd, Cd, J, T.logn, beta_max);
+        else k_modup<1><<<dim3((M + bs - 1) / bs, Ch.beta, jobs), bs, 0, L.stream>>>(T.mods, T.tw_fwd, Cd, J, T.logn, beta_max);
+    }
     { LaunchScope scope(L, KID_MAC);
     if (T.logn <= 13) {
         const size_t smm = ((size_t)padded_words(N) + 2 * (size_t)N) * 8;

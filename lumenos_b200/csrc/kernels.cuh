@@ -20,8 +20,16 @@ struct KsConsts {
     int nq, np, beta, k;                       // Q limbs in use, P limbs, digits, total Q limbs (evk / col stride)
     int dig_start[MAX_DIGITS], dig_size[MAX_DIGITS];
     u64 intt_w[MAX_LIMBS], intt_ws[MAX_LIMBS];               // N^-1 (Q_d/q_i)^-1 mod q_i (Shoup pair)
-    u64 mu_c[MAX_DIGITS][MAX_LIMBS][MAX_P];                  // (Q_d/q_a mod m_tm) * 2^64 mod m_tm   [digit][target][a]
-    u64 mu_neg[MAX_DIGITS][MAX_LIMBS];                       // -(nd-1) Q_d mod m_tm
+    // base conversion digit d -> target tix:  V = K + sum_a z_a * c_a  (a 128-bit integer), r = V * 2^-64 mod m (Montgomery
+    // step), which equals 2^(e-64) * ModUp value.  The factor 2^(64-e) is folded into the evaluation-key rows of (d, tix) when
+    // the key is loaded.  For Lattigo's primes (2^b +- j*2N + 1) the constants 2^e (Q_d/q_a) mod m are tiny in signed form
+    // (|c| < 2^31): "fast" pairs use 64x32-bit products.
+    int mu_fast[MAX_DIGITS][MAX_LIMBS];                      // 1: small signed constants
+    uint32_t mu_mag[MAX_DIGITS][MAX_LIMBS][MAX_P];           // |c_a|          (fast)
+    uint32_t mu_sgn[MAX_DIGITS][MAX_LIMBS];                  // bit a: c_a < 0 (fast)
+    u64 mu_c[MAX_DIGITS][MAX_LIMBS][MAX_P];                  // Q_d/q_a mod m  (generic, e = 0)
+    u64 mu_k_lo[MAX_DIGITS][MAX_LIMBS], mu_k_hi[MAX_DIGITS][MAX_LIMBS];   // K = -2^e (nd-1) Q_d mod m, plus a multiple of m covering the negative terms
+    u64 mu_g_w[MAX_DIGITS][MAX_LIMBS], mu_g_ws[MAX_DIGITS][MAX_LIMBS];    // 2^(e-64) mod m (Shoup pair): single-prime digits
     u64 pin_w[MAX_P], pin_ws[MAX_P], pin_add[MAX_P];         // N^-1 (P/p_j)^-1 mod p_j ; half_j (P/p_j)^-1 mod p_j
     u64 md_c[MAX_LIMBS][MAX_P];                              // (P/p_a mod q_i) * 2^64 mod q_i
     u64 md_neg[MAX_LIMBS];                                   // -((np-1) P + Phalf) mod q_i
@@ -97,6 +105,8 @@ void launch_prep_pt(const Launch &L, const DeviceTables &T, int level, const u64
 // out_x[job] = in[col] * ptm_x  (x = 0,1; ptm1 may be null); in: cts with stride in_words; out: job cols with stride col_words
 void launch_mul_pt(const Launch &L, const DeviceTables &T, int level, const u64 *in, uint64_t in_words, int ncols,
                    const u64 *ptm0, const u64 *ptm1, u64 *out0, u64 *out1, uint64_t col_words);
+// evk rows (d, c, gm) *= fm[d][gm] (Montgomery-form factors, 0 = skip); beta digits
+void launch_scale_rows(const Launch &L, const DeviceTables &T, u64 *evk, const u64 *fm_dev, int beta);
 void launch_limb_ntt(const Launch &L, const DeviceTables &T, int mod_idx, u64 *limb, int inverse);
 
 // ---- Encode ----
@@ -107,6 +117,7 @@ struct KsJobs {
     u64 *col;  uint64_t col_words;   // [jobs][2][k][N]
     u64 *y;    uint64_t y_words;     // [jobs][k][N]
     u64 *acc;  uint64_t acc_words;   // [jobs][2][k+np][N]
+    u64 *mu;   uint64_t mu_words;    // [jobs][beta_max][k+np][N] base-converted digits (first NTT level applied when N = 16384)
     int jobs;
 };
 // col += pi_galEl( keyswitch(col) )      (AutomorphismHoisted + Add, lattigo rlwe/inner_sum.go)

@@ -1,0 +1,143 @@
+// C++ twin of the reference's TestEncode / TestLigeroE2E (fhe/code_test.go:14-123, fhe/ligero_test.go:70-176) written against
+// the C++ host mirror (include/lumenos_b200.hpp).  The CPU oracle plays Lattigo: it makes the keys, encrypts the witness,
+// and provides the expected ciphertexts / decryptions.  Exit code 0 = all checks passed.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "lumenos_b200.hpp"
+#include "lumenos_oracle.h"
+
+using namespace lumenos;
+typedef uint64_t u64;
+
+#define REQUIRE(cond, ...) do { if (!(cond)) { std::fprintf(stderr, "FAIL %s:%d: ", __FILE__, __LINE__); std::fprintf(stderr, __VA_ARGS__); std::fprintf(stderr, "\n"); return 1; } } while (0)
+
+static const u64 Modulus = 144115188075593729ull;  // fhe/ligero_test.go:16
+
+int main(int argc, char **argv) {
+    const int logN = argc > 1 ? std::atoi(argv[1]) : 8, rows = argc > 2 ? std::atoi(argv[2]) : 256, cols = argc > 3 ? std::atoi(argv[3]) : 16,
+              k = argc > 4 ? std::atoi(argv[4]) : 6, rhoInv = 2;
+    orc_switches sw; orc_default_switches(&sw);
+    orc_params *P = orc_params_generate(logN, k, Modulus, &sw);
+    REQUIRE(P, "oracle parameters");
+    const int N = orc_params_N(P), np = orc_params_np(P), n = cols * rhoInv;
+    const size_t ctw = 2 * (size_t)k * N;
+
+    // ---- host side (Lattigo's job in the reference): keys, witness, encryption ----
+    std::vector<int8_t> sk(N);
+    orc_keygen_sk(P, 11, sk.data());
+    std::vector<u64> pk(ctw);
+    orc_keygen_pk(P, sk.data(), 12, pk.data());
+    std::vector<u64> M((size_t)rows * cols);
+    orc_witness_matrix(rows, cols, Modulus, M.data());
+    std::vector<u64> cts(ctw * cols), zero(ctw), col(rows), pt((size_t)k * N);
+    for (int j = 0; j < cols; j++) {
+        for (int i = 0; i < rows; i++) col[i] = M[(size_t)i * cols + j];
+        orc_encode_pt(P, col.data(), rows, k - 1, pt.data());
+        orc_encrypt_pk(P, pk.data(), pt.data(), 100 + j, cts.data() + ctw * j);
+    }
+    orc_encrypt_pk(P, pk.data(), nullptr, 13, zero.data());
+    u64 galEls[64];
+    const int ngal = orc_galois_elements_for_innersum(P, rows, galEls);
+    const int beta = orc_beta(P);
+    std::vector<std::vector<u64>> evks(ngal, std::vector<u64>((size_t)beta * 2 * (k + np) * N));
+    std::vector<const u64 *> evkp(ngal);
+    for (int i = 0; i < ngal; i++) { orc_keygen_galois(P, sk.data(), galEls[i], 14, evks[i].data()); evkp[i] = evks[i].data(); }
+    fhe::PrimeField field; field.modulus = Modulus; field.roots.resize(n);
+    REQUIRE(orc_field_roots_forward(Modulus, n, sw.primroot_start, field.roots.data()) == 0, "field tables");
+    std::vector<u64> r(rows), b(rows), rpt((size_t)k * N), bpt((size_t)k * N);
+    u64 seed = 0x9e3779b97f4a7c15ull;
+    for (int i = 0; i < rows; i++) { seed = seed * 6364136223846793005ull + 1442695040888963407ull; r[i] = seed; }   // unreduced, like SampleUints
+    u64 zc = 1; for (int i = 0; i < cols; i++) zc = (u64)((unsigned __int128)zc * 3 % Modulus);                       // z = 3, z^cols
+    u64 pw = 1; for (int i = 0; i < rows; i++) { b[i] = pw; pw = (u64)((unsigned __int128)pw * zc % Modulus); }
+    orc_encode_pt(P, r.data(), rows, k - 1, rpt.data());
+    orc_encode_pt(P, b.data(), rows, k - 1, bpt.data());
+
+    // ---- the path under test, through the C++ mirror ----
+    fhe::Parameters params;
+    params.LogN = logN; params.T = Modulus;
+    params.Q.resize(k); params.P.resize(np); params.PsiQ.resize(k); params.PsiP.resize(np);
+    orc_params_moduli(P, params.Q.data(), params.P.data());
+    orc_params_psi(P, params.PsiQ.data(), params.PsiP.data());
+    try {
+        fhe::ServerBFV server(field, params, 0);
+        for (int i = 0; i < ngal; i++) server.LoadGaloisKey(galEls[i], evks[i].data());
+        fhe::CiphertextStore matrix(server, cols), zeroCol(server, 1);
+        matrix.Upload(cts.data(), 0, cols);
+        zeroCol.Upload(zero.data(), 0, 1);
+        fhe::LigeroCommitter ligero(128, rows, cols, rhoInv);
+        REQUIRE(ligero.Queries == 309, "queries = %d", ligero.Queries);
+        fhe::LigeroProver comm = ligero.Commit(matrix, server, {&zeroCol, 0});
+        std::vector<uint32_t> idx(ligero.Queries);
+        for (int i = 0; i < ligero.Queries; i++) { seed = seed * 6364136223846793005ull + 1442695040888963407ull; idx[i] = (uint32_t)((seed >> 33) % n); }
+        idx[9] = idx[4];
+        fhe::EncryptedProof proof = comm.Prove(rpt.data(), bpt.data(), idx, server);
+
+        // TestEncode: decrypt(Encode) == core.Encode, and bit-exact against the oracle's fhe.Encode
+        std::vector<u64> enc_want(ctw * n), enc_got = comm.EncodedMatrix->Download();
+        orc_fhe_encode(P, cts.data(), cols, rhoInv, zero.data(), field.roots.data(), enc_want.data());
+        REQUIRE(enc_got == enc_want, "EncodedMatrix differs from the oracle");
+        u64 adds, subs, muls; orc_fhe_ntt_counts(&adds, &subs, &muls);
+        REQUIRE((u64)server.MulCounter() == muls, "MulCounter %d vs %llu", server.MulCounter(), (unsigned long long)muls);
+        std::vector<u64> row(cols), encRow(n), dec(N);
+        std::vector<std::vector<u64>> encPlain(rows, std::vector<u64>(n));
+        for (int i = 0; i < rows; i++) {
+            for (int j = 0; j < cols; j++) row[j] = M[(size_t)i * cols + j];
+            orc_core_encode(row.data(), cols, rhoInv, Modulus, field.roots.data(), encPlain[i].data());
+        }
+        for (int j = 0; j < n; j++) {
+            orc_decrypt_decode(P, sk.data(), enc_got.data() + ctw * j, k - 1, 1, dec.data());
+            for (int i = 0; i < rows; i++) REQUIRE(dec[i] == encPlain[i][j], "Matrices differ at [%d][%d]", i, j);
+        }
+        // TestLigeroE2E: MatR / MatZ slot 0 == LigeroProveReference inner products; ciphertexts bit-exact vs oracle
+        const size_t l1w = 2 * 2 * (size_t)N;
+        std::vector<u64> matR = proof.MatR->Download(), matZ = proof.MatZ->Download(), want(l1w);
+        for (int j = 0; j < cols; j++) {
+            u64 sc = orc_inner_sum_eval_column(P, cts.data() + ctw * j, rpt.data(), rows, galEls, evkp.data(), ngal, want.data());
+            REQUIRE(sc == proof.MatR->Scale, "scale metadata");
+            REQUIRE(std::memcmp(want.data(), matR.data() + l1w * j, l1w * 8) == 0, "MatR[%d] differs from the oracle", j);
+            orc_inner_sum_eval_column(P, cts.data() + ctw * j, bpt.data(), rows, galEls, evkp.data(), ngal, want.data());
+            REQUIRE(std::memcmp(want.data(), matZ.data() + l1w * j, l1w * 8) == 0, "MatZ[%d] differs from the oracle", j);
+            unsigned __int128 accR = 0, accZ = 0;
+            for (int i = 0; i < rows; i++) {
+                accR = (accR + (unsigned __int128)(r[i] % Modulus) * M[(size_t)i * cols + j]) % Modulus;
+                accZ = (accZ + (unsigned __int128)b[i] * M[(size_t)i * cols + j]) % Modulus;
+            }
+            orc_decrypt_decode(P, sk.data(), matR.data() + l1w * j, 1, sc, dec.data());
+            REQUIRE(dec[0] == (u64)accR, "MatR[%d] decrypts to %llu, want %llu", j, (unsigned long long)dec[0], (unsigned long long)(u64)accR);
+            orc_decrypt_decode(P, sk.data(), matZ.data() + l1w * j, 1, sc, dec.data());
+            REQUIRE(dec[0] == (u64)accZ, "MatZ[%d] decrypts wrong", j);
+        }
+        // queried columns: bit-exact, and Verify's well-formedness relation <col, r> == Encode(MatR)[idx] (fhe/ligero.go:554-563)
+        std::vector<u64> qc = proof.QueriedCols->Download(), matRplain(cols), encR(n);
+        for (int j = 0; j < cols; j++) {
+            unsigned __int128 acc = 0;
+            for (int i = 0; i < rows; i++) acc = (acc + (unsigned __int128)(r[i] % Modulus) * M[(size_t)i * cols + j]) % Modulus;
+            matRplain[j] = (u64)acc;
+        }
+        orc_core_encode(matRplain.data(), cols, rhoInv, Modulus, field.roots.data(), encR.data());
+        for (int q = 0; q < 24; q++) {
+            u64 sc = orc_rescale_to_level1(P, enc_want.data() + ctw * idx[q], want.data());
+            REQUIRE(std::memcmp(want.data(), qc.data() + l1w * q, l1w * 8) == 0, "QueriedCols[%d] differs from the oracle", q);
+            orc_decrypt_decode(P, sk.data(), qc.data() + l1w * q, 1, sc, dec.data());
+            unsigned __int128 acc = 0;
+            for (int i = 0; i < rows; i++) acc = (acc + (unsigned __int128)dec[i] * (r[i] % Modulus)) % Modulus;
+            REQUIRE((u64)acc == encR[idx[q]], "well-formedness R check failed for column %u", idx[q]);
+        }
+        // error behaviour: missing key / bad shapes raise, they do not abort
+        fhe::ServerBFV bare(field, params, 0);
+        fhe::CiphertextStore one(bare, 1);
+        one.Upload(cts.data(), 0, 1);
+        bool threw = false;
+        try { bare.InnerSum({&one, 0}, 1, rows); } catch (const Error &e) { threw = e.code == LMN_ERR_NOKEY; }
+        REQUIRE(threw, "InnerSum without keys must fail with LMN_ERR_NOKEY");
+    } catch (const std::exception &e) {
+        std::fprintf(stderr, "FAIL: exception: %s\n", e.what());
+        return 1;
+    }
+    orc_params_free(P);
+    std::printf("ok: C++ mirror Commit/Prove bit-exact vs oracle and plaintext-correct (logN=%d %dx%d k=%d)\n", logN, rows, cols, k);
+    return 0;
+}

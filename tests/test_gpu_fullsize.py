@@ -1,0 +1,131 @@
+"""Full-size parity (-m gpu): the CUDA path at BASELINE.json's shapes (ring degree, chain length and matrix size of
+configs B and D) on uniformly random canonical residues, checked
+  * bit-for-bit against the oracle on random samples (lanes of Encode, columns of the inner products, query columns),
+  * through size-independent properties: Encode is linear per lane, results do not depend on the batch size, and a
+    second run reproduces the first."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from oracle import oracle as O  # noqa: E402
+
+T = O.T_DEFAULT
+
+
+def _backend(P, roots):
+    from lumenos_b200 import fhe
+    params = fhe.BGVParameters(P.logN, P.q, P.p, P.t, P.psi_q, P.psi_p)
+    return fhe.ServerBFV(fhe.PrimeField(P.t, roots), params)
+
+
+def _rand_cts(torch, dev, q, count, N, seed):
+    g = torch.Generator(device=dev).manual_seed(seed)
+    t = torch.empty((count, 2, len(q), N), dtype=torch.int64, device=dev)
+    for i, m in enumerate(q):
+        t[:, :, i, :] = torch.randint(0, int(m), (count, 2, N), generator=g, dtype=torch.int64, device=dev)
+    return t
+
+
+@pytest.mark.parametrize("logN,cols,k", [(12, 2048, 11), (14, 4096, 12)])
+def test_encode_full_size_sampled_lanes_and_linearity(logN, cols, k):
+    import torch
+    from lumenos_b200 import _capi, fhe
+    dev = torch.device("cuda", 0)
+    P = O.Params(logN, k=k)
+    N, n = P.N, 2 * cols
+    roots = O.field_roots_forward(n)
+    be = _backend(P, roots)
+    lib = _capi.lib()
+    A = _rand_cts(torch, dev, P.q, cols, N, 1)
+    Z = _rand_cts(torch, dev, P.q, 1, N, 2)
+    EA = torch.empty((n, 2, k, N), dtype=torch.int64, device=dev)
+    sA, sZ = fhe.CiphertextStore(be, cols, k - 1, wrap_ptr=A.data_ptr()), fhe.CiphertextStore(be, 1, k - 1, wrap_ptr=Z.data_ptr())
+    sEA = fhe.CiphertextStore(be, n, k - 1, wrap_ptr=EA.data_ptr())
+    plan = be._plan(cols, 2)
+    _capi.check(lib.lmn_encode(be.ctx, plan, sA.h, sZ.h, 0, sEA.h))
+    be.Synchronize()
+    # ---- bit-exact against the oracle on random lanes ----
+    rng = np.random.default_rng(7)
+    nl = 1024
+    lanes = np.sort(rng.choice(2 * k * N, size=nl, replace=False))
+    limb_of_lane = ((lanes // N) % k).astype(np.int32)
+    lt = torch.as_tensor(lanes, device=dev)
+    ml = A.view(cols, -1)[:, lt].cpu().numpy().astype(np.uint64)
+    zl = Z.view(1, -1)[0, lt].cpu().numpy().astype(np.uint64)
+    got = EA.view(n, -1)[:, lt].cpu().numpy().astype(np.uint64)
+    want = P.fhe_encode_lanes(ml, 2, zl, limb_of_lane, roots)
+    assert np.array_equal(got, want), "Encode differs from the oracle on sampled lanes (%d mismatches)" % int((got != want).sum())
+    # ---- a second run reproduces the first ----
+    first = EA.view(n, -1)[:, lt].clone()
+    _capi.check(lib.lmn_encode(be.ctx, plan, sA.h, sZ.h, 0, sEA.h))
+    be.Synchronize()
+    assert torch.equal(first, EA.view(n, -1)[:, lt])
+    # ---- linearity per lane (config B size only: three encoded matrices must fit) ----
+    if logN == 12:
+        qv = torch.as_tensor(P.q.astype(np.int64), device=dev).view(1, 1, k, 1)
+        B = _rand_cts(torch, dev, P.q, cols, N, 3)
+        Z2 = _rand_cts(torch, dev, P.q, 1, N, 4)
+        EB, ES = torch.empty_like(EA), torch.empty_like(EA)
+        S, ZS = (A + B) % qv, (Z + Z2) % qv
+        st = lambda t, c: fhe.CiphertextStore(be, c, k - 1, wrap_ptr=t.data_ptr())  # noqa: E731
+        sB, sZ2, sS, sZS, sEB, sES = st(B, cols), st(Z2, 1), st(S, cols), st(ZS, 1), st(EB, n), st(ES, n)
+        _capi.check(lib.lmn_encode(be.ctx, plan, sB.h, sZ2.h, 0, sEB.h))
+        _capi.check(lib.lmn_encode(be.ctx, plan, sS.h, sZS.h, 0, sES.h))
+        be.Synchronize()
+        assert torch.equal((EA + EB) % qv, ES), "Encode(A) + Encode(B) != Encode(A + B)"
+    be.Close()
+
+
+@pytest.mark.parametrize("logN,rows,k", [(12, 4096, 11), (14, 16384, 12)])
+def test_prove_full_ring_sampled_columns(logN, rows, k):
+    """inner products + query rescale at the full ring size and chain length of configs B / D (columns are independent,
+    so 48 columns exercise exactly the per-column work of the full matrix)"""
+    import torch
+    from lumenos_b200 import _capi, fhe
+    dev = torch.device("cuda", 0)
+    P = O.Params(logN, k=k)
+    N, cols = P.N, 48
+    roots = O.field_roots_forward(2 * cols)
+    be = _backend(P, roots)
+    lib = _capi.lib()
+    rng = np.random.default_rng(11)
+    mods = list(P.q) + list(P.p)
+    gal = P.galois_elements_for_innersum(rows)
+    evks = []
+    for g in gal:
+        e = np.empty((P.beta, 2, k + P.np, N), np.uint64)
+        for i, m in enumerate(mods):
+            e[:, :, i, :] = rng.integers(0, int(m), size=(P.beta, 2, N), dtype=np.uint64)
+        evks.append(e)
+        be.LoadGaloisKey(g, e)
+    M = _rand_cts(torch, dev, P.q, cols, N, 5)
+    E = _rand_cts(torch, dev, P.q, 2 * cols, N, 6)           # stands for an encoded matrix
+    sM, sE = fhe.CiphertextStore(be, cols, k - 1, wrap_ptr=M.data_ptr()), fhe.CiphertextStore(be, 2 * cols, k - 1, wrap_ptr=E.data_ptr())
+    rpt = np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in P.q])
+    bpt = np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in P.q])
+    vp = C.c_void_p
+    outs = {}
+    for batch in (64, 10):
+        be.SetBatch(batch)
+        mr, mz = be.NewStore(cols, 1), be.NewStore(cols, 1)
+        _capi.check(lib.lmn_inner_product2(be.ctx, sM.h, rpt.ctypes.data_as(vp), bpt.ctypes.data_as(vp), rows, mr.h, mz.h))
+        outs[batch] = (mr.download(), mz.download())
+    assert np.array_equal(outs[64][0], outs[10][0]) and np.array_equal(outs[64][1], outs[10][1]), "result depends on the batch size"
+    Mh = M.cpu().numpy().astype(np.uint64)
+    for j in (0, 17, 47):
+        wr, _ = P.inner_sum_eval_column(Mh[j], rpt, rows, gal, evks)
+        wz, _ = P.inner_sum_eval_column(Mh[j], bpt, rows, gal, evks)
+        assert np.array_equal(outs[64][0][j], wr), "MatR[%d] differs from the oracle" % j
+        assert np.array_equal(outs[64][1][j], wz), "MatZ[%d] differs from the oracle" % j
+    idx = np.array([5, 90, 5, 33], dtype=np.uint32)
+    q = be.NewStore(len(idx), 1)
+    _capi.check(lib.lmn_query_columns(be.ctx, sE.h, idx.ctypes.data_as(vp), len(idx), q.h))
+    got = q.download()
+    Eh = E[torch.as_tensor(idx.astype(np.int64), device=dev)].cpu().numpy().astype(np.uint64)
+    for i in range(len(idx)):
+        assert np.array_equal(got[i], P.rescale_to_level1(Eh[i])[0]), "queried column %d differs from the oracle" % idx[i]
+    assert np.array_equal(got[0], got[2])
+    be.Close()

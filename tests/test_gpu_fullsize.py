@@ -17,8 +17,10 @@ T = O.T_DEFAULT
 
 def _backend(P, roots):
     from lumenos_b200 import fhe
+    import torch
     params = fhe.BGVParameters(P.logN, P.q, P.p, P.t, P.psi_q, P.psi_p)
-    return fhe.ServerBFV(fhe.PrimeField(P.t, roots), params)
+    # the stores wrap torch tensors, so the library runs on torch's current stream (one ordering for both)
+    return fhe.ServerBFV(fhe.PrimeField(P.t, roots), params, stream=torch.cuda.current_stream().cuda_stream)
 
 
 def _rand_cts(torch, dev, q, count, N, seed):
@@ -60,6 +62,7 @@ def test_encode_full_size_sampled_lanes_and_linearity(logN, cols, k):
     assert np.array_equal(got, want), "Encode differs from the oracle on sampled lanes (%d mismatches)" % int((got != want).sum())
     # ---- a second run reproduces the first ----
     first = EA.view(n, -1)[:, lt].clone()
+    torch.cuda.synchronize()   # the clone runs on torch's stream, the library on its own: order them
     _capi.check(lib.lmn_encode(be.ctx, plan, sA.h, sZ.h, 0, sEA.h))
     be.Synchronize()
     assert torch.equal(first, EA.view(n, -1)[:, lt])

@@ -82,7 +82,7 @@ static bool supported_logn(int l) { return l == 6 || l == 8 || l == 10 || l == 1
 static void build_mod(ModDev &m, u64 q, int n) {
     memset(&m, 0, sizeof(m));
     m.q = q; m.qinv = h_qinv64(q); m.mu = (u64)((((u128)1) << 64) / q);
-    m.ninv = h_invmod((u64)n % q, q); m.ninvs = h_shoup(m.ninv, q);
+    m.ninv = h_invmod((u64)n % q, q); m.ninvs = h_shoup(m.ninv, q); m.q3 = 3 * q;
 }
 static void build_twiddles(u64 q, u64 psi, int logn, std::vector<ulonglong2> &fwd, std::vector<ulonglong2> &inv) {
     int n = 1 << logn;
@@ -274,7 +274,10 @@ int lmn_ctx_create(const lmn_params *P, int device, lmn_ctx **out) {
     for (uint32_t i = 0; i < P->num_q + P->num_p; i++) {
         u64 m = i < P->num_q ? P->q[i] : P->p[i - P->num_q];
         u64 psi = i < P->num_q ? P->psi_q[i] : P->psi_p[i - P->num_q];
-        if (m >= (1ull << 59) || m < (1ull << 20) || m % two_n != 1) return fail(LMN_ERR_INVALID, "modulus must be an NTT-friendly prime below 2^59");
+        // lazy transforms: values grow by 3q per forward level on top of an 8q entry bound (ntt_r16.cuh) and must stay below 2^64
+        const u64 lazy_cap = ~0ull / (3 * (u64)P->log_n + 8);
+        if (m >= (1ull << 59) || m > lazy_cap || m < (1ull << 20) || m % two_n != 1)
+            return fail(LMN_ERR_INVALID, "modulus must be an NTT-friendly prime below min(2^59, 2^64 / (3 log N + 8))");
         if (h_powmod(psi, two_n / 2, m) != m - 1) return fail(LMN_ERR_INVALID, "psi is not a primitive 2N-th root of unity");
     }
     if (P->t % two_n != 1) return fail(LMN_ERR_INVALID, "plaintext modulus must be 1 mod 2N");  // ref: fhe/bfv.go:136-140

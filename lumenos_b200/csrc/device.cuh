@@ -19,7 +19,8 @@ struct ModDev {
     u64 mu;     // floor(2^64 / q)  (single-word Barrett for x < 2^64)
     u64 ninv;   // N^-1 mod q
     u64 ninvs;  // Shoup companion of ninv
-    u64 pad[3];
+    u64 q3;     // 3q (lazy forward butterfly with the 3-product quotient estimate, ntt_r16.cuh)
+    u64 pad[2];
 };
 
 __device__ __forceinline__ u64 csub(u64 x, u64 q) { return x >= q ? x - q : x; }

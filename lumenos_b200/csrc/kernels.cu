@@ -550,8 +550,8 @@ __global__ void __launch_bounds__(R16_THREADS, 2) k_mac_r16(const ModDev *mods, 
 //      stay in registers for all digits, shared memory holds only the block's twiddles (32 KB, loaded once per CTA) and
 //      two 17 KB transposition buffers, so three CTAs fit per SM and the transform issues no global loads.  Per digit a
 //      thread loads 8 residues (issued before the previous digit's MAC) and 8 key-row vectors (issued two passes early).
-template <int S>
-__global__ void __launch_bounds__(RA_THREADS, 2) k_mac_ra(const ModDev *mods, const ulonglong2 *tw_fwd, const KsConsts *C,
+template <int S, int OCC, int PF>
+__global__ void __launch_bounds__(RA_THREADS, OCC) k_mac_ra(const ModDev *mods, const ulonglong2 *tw_fwd, const KsConsts *C,
                                                            const KsJobs J, const u64 *__restrict__ evk) {
     extern __shared__ u64 sm[];
     constexpr int M = RA_M;
@@ -593,25 +593,37 @@ __global__ void __launch_bounds__(RA_THREADS, 2) k_mac_ra(const ModDev *mods, co
     for (int d = 0; d < beta; d++) {
         const ulonglong2 *e0 = reinterpret_cast<const ulonglong2 *>(evk + ((((size_t)d * 2 + 0) * KP + gm) << LOGN) + blk + 8 * u);
         const ulonglong2 *e1 = reinterpret_cast<const ulonglong2 *>(evk + ((((size_t)d * 2 + 1) * KP + gm) << LOGN) + blk + 8 * u);
+        // key rows: component 0 is requested before the transform, component 1 before its third pass; both are plain loads
+        // pinned in front of the next barrier (ld_pin2), a full pass or more ahead of the MAC that consumes them
         ulonglong2 k0[4], k1[4];
-        auto load_keys = [&]() {
 #pragma unroll
-            for (int r = 0; r < 4; r++) { k0[r] = __ldg(e0 + r); k1[r] = __ldg(e1 + r); }
+        for (int r = 0; r < 4; r++) k0[r] = ld_pin2(e0 + r);
+        auto load_k1 = [&]() {
+#pragma unroll
+            for (int r = 0; r < 4; r++) k1[r] = ld_pin2(e1 + r);
         };
-        if (d != own) { ntt2048_fwd(a, flip ? buf1 : buf0, stw, fm, load_keys); flip ^= 1; }
-        else load_keys();
+        if (d != own) {
+            if (PF & 2) ntt2048_fwd(a, flip ? buf1 : buf0, stw, fm, load_k1);
+            else { ntt2048_fwd(a, flip ? buf1 : buf0, stw, fm, []() {}); load_k1(); }
+            flip ^= 1;
+        } else load_k1();
         u64 nx[8];
-        if (d + 1 < beta) load_digit(d + 1, nx);
+        if ((PF & 1) && d + 1 < beta) load_digit(d + 1, nx);
 #pragma unroll
         for (int r = 0; r < 4; r++) {
             acc0[2 * r] += mont_mul_lazy(a[2 * r], k0[r].x, p, md.qinv);
-            acc1[2 * r] += mont_mul_lazy(a[2 * r], k1[r].x, p, md.qinv);
             acc0[2 * r + 1] += mont_mul_lazy(a[2 * r + 1], k0[r].y, p, md.qinv);
+        }
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            acc1[2 * r] += mont_mul_lazy(a[2 * r], k1[r].x, p, md.qinv);
             acc1[2 * r + 1] += mont_mul_lazy(a[2 * r + 1], k1[r].y, p, md.qinv);
         }
         if (d + 1 < beta) {
+            if (PF & 1) {
 #pragma unroll
-            for (int r = 0; r < 8; r++) a[r] = nx[r];
+                for (int r = 0; r < 8; r++) a[r] = nx[r];
+            } else load_digit(d + 1, a);
         }
     }
     ulonglong2 *o0 = reinterpret_cast<ulonglong2 *>(J.acc + (size_t)job * J.acc_words + ((size_t)gm << LOGN) + blk + 8 * u);
@@ -726,9 +738,14 @@ void launch_rotate_accumulate(const Launch &L, const DeviceTables &T, const KsCo
     if (SB && !use_r16) {
         const size_t smm = (2 * (size_t)RA_M + 2 * (size_t)RA_WORDS) * 8;
         const dim3 g((nq + np) * SB, jobs);
-        if (SB == 8) k_mac_ra<8><<<g, RA_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk);
-        else if (SB == 4) k_mac_ra<4><<<g, RA_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk);
-        else k_mac_ra<2><<<g, RA_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk);
+        static const int var = getenv("LMN_MAC_VAR") ? atoi(getenv("LMN_MAC_VAR")) : 0;   // experiment switch: occupancy x prefetch
+#define MACRA(SS) do { \
+            if (var == 1) k_mac_ra<SS, 3, 3><<<g, RA_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk); \
+            else if (var == 2) k_mac_ra<SS, 3, 2><<<g, RA_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk); \
+            else if (var == 3) k_mac_ra<SS, 3, 0><<<g, RA_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk); \
+            else k_mac_ra<SS, 2, 3><<<g, RA_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk); } while (0)
+        if (SB == 8) MACRA(8); else if (SB == 4) MACRA(4); else MACRA(2);
+#undef MACRA
     } else if (SB) {
         const int S16 = SB;
         const size_t smm = ((size_t)R16_WORDS + 2 * (size_t)R16_M + 2 * R16_STW) * 8;
@@ -931,7 +948,9 @@ const char *kernels_init() {
     SET_LOGN(6) SET_LOGN(8) SET_LOGN(10) SET_LOGN(12) SET_LOGN(13) SET_LOGN(14)
     SETSM((k_mac<6, 1>)); SETSM((k_mac<8, 1>)); SETSM((k_mac<10, 1>)); SETSM((k_mac<12, 1>)); SETSM((k_mac<13, 1>));
     SETSM((k_mac<13, 2>));
-SETSM(k_mac_ra<2>); SETSM(k_mac_ra<4>); SETSM(k_mac_ra<8>);
+#define SETRA(SS) SETSM((k_mac_ra<SS, 2, 3>)); SETSM((k_mac_ra<SS, 3, 3>)); SETSM((k_mac_ra<SS, 3, 2>)); SETSM((k_mac_ra<SS, 3, 0>));
+    SETRA(2) SETRA(4) SETRA(8)
+#undef SETRA
 #define SETMAC(SS) SETSM((k_mac_r16<SS, 0>)); SETSM((k_mac_r16<SS, 1>)); SETSM((k_mac_r16<SS, 2>)); SETSM((k_mac_r16<SS, 3>));
     SETMAC(1) SETMAC(2) SETMAC(4)
 #undef SETMAC

@@ -26,17 +26,19 @@ constexpr int R16_LOGM = 12;
 constexpr int R16_M = 1 << R16_LOGM;
 constexpr int R16_WORDS = R16_M + (R16_M >> 4);   // padded block
 
-// Loads that must be ISSUED where they are written (prefetch into registers one stage ahead of their use): ptxas sinks
-// ordinary ld.global.nc towards the first use to shorten live ranges, which puts an L2 round trip in front of every
-// butterfly level when only 4 warps per scheduler are resident.  Volatile loads keep their place relative to barriers.
+// Loads that must be ISSUED where they are written (prefetch into registers one or two stages ahead of their use):
+// ptxas sinks ld.global.nc towards the first use to shorten live ranges - even across bar.sync - which puts an L2 round
+// trip in front of the consumer when only 4 warps per scheduler are resident.  A plain (coherent) ld.global may not move
+// across the CTA barrier that follows it, so it stays in the stage where it is written.  (ld.volatile also stays put, but
+// is issued as LDG.STRONG.SYS and measured 10 % slower end to end.)
 __device__ __forceinline__ ulonglong2 ld_pin2(const ulonglong2 *p) {
     ulonglong2 v;
-    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
+    asm volatile("ld.global.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
     return v;
 }
 __device__ __forceinline__ u64 ld_pin(const u64 *p) {
     u64 v;
-    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
+    asm volatile("ld.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
 
@@ -231,7 +233,7 @@ __device__ __forceinline__ void ntt2048_fwd(u64 (&a)[8], u64 *s, const ulonglong
     { const unsigned i = u >> 2, j = u & 3;
 #pragma unroll
       for (int r = 0; r < 8; r++) a[r] = s[PAD(i * 32 + j + 4 * r)];
-      before_pass_c();   // the caller's prefetches for its epilogue (two passes ahead of their use)
+      before_pass_c();   // the caller's prefetches for its epilogue
       r8_fwd_f(a, [&](int t, int b) { return stw[((64 + i) << t) + b]; }, m);              // levels 6-8
 #pragma unroll
       for (int r = 0; r < 8; r++) s[PAD(i * 32 + j + 4 * r)] = a[r]; }

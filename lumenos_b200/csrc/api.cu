@@ -45,7 +45,7 @@ struct lmn_ctx {
     ulonglong2 *d_small_tw = nullptr;
     // workspace
     uint32_t batch = 64;
-    u64 *ws_col = nullptr, *ws_y = nullptr, *ws_acc = nullptr, *ws_mu = nullptr, *ws_pt = nullptr;
+    u64 *ws_col = nullptr, *ws_col2 = nullptr, *ws_y = nullptr, *ws_acc = nullptr, *ws_mu = nullptr, *ws_pt = nullptr;
     uint32_t *ws_idx = nullptr; size_t ws_idx_cap = 0;
     ulonglong2 *ws_scalar = nullptr;
     uint32_t ws_jobs = 0;
@@ -234,9 +234,10 @@ static int get_rs(lmn_ctx *c, int level, const RescaleConsts **dev) {
 
 static int ensure_workspace(lmn_ctx *c, uint32_t jobs) {
     if (c->ws_jobs >= jobs) return 0;
-    if (c->ws_col) { cudaFree(c->ws_col); cudaFree(c->ws_y); cudaFree(c->ws_acc); cudaFree(c->ws_mu); c->ws_col = c->ws_y = c->ws_acc = c->ws_mu = nullptr; c->ws_jobs = 0; }
+    if (c->ws_col) { cudaFree(c->ws_col); cudaFree(c->ws_col2); cudaFree(c->ws_y); cudaFree(c->ws_acc); cudaFree(c->ws_mu); c->ws_col = c->ws_col2 = c->ws_y = c->ws_acc = c->ws_mu = nullptr; c->ws_jobs = 0; }
     size_t N = c->n, k = c->k, KP = c->k + c->np;
     CK(cudaMalloc(&c->ws_col, jobs * 2 * k * N * 8));
+    CK(cudaMalloc(&c->ws_col2, jobs * 2 * k * N * 8));   // the block pipeline rotates out of place
     CK(cudaMalloc(&c->ws_y, jobs * k * N * 8));
     CK(cudaMalloc(&c->ws_acc, jobs * 2 * KP * N * 8));
     CK(cudaMalloc(&c->ws_mu, jobs * (size_t)((c->k + c->np - 1) / c->np) * KP * N * 8));
@@ -247,7 +248,7 @@ static KsJobs jobs_view(lmn_ctx *c, uint32_t first, uint32_t jobs) {
     size_t N = c->n, k = c->k, KP = c->k + c->np;
     KsJobs J;
     J.col_words = 2 * k * N; J.y_words = k * N; J.acc_words = 2 * KP * N; J.mu_words = (size_t)((c->k + c->np - 1) / c->np) * KP * N;
-    J.col = c->ws_col + first * J.col_words; J.y = c->ws_y + first * J.y_words; J.acc = c->ws_acc + first * J.acc_words;
+    J.col = c->ws_col + first * J.col_words; J.col2 = c->ws_col2 + first * J.col_words; J.y = c->ws_y + first * J.y_words; J.acc = c->ws_acc + first * J.acc_words;
     J.mu = c->ws_mu + first * J.mu_words;
     J.jobs = (int)jobs;
     return J;
@@ -343,7 +344,7 @@ void lmn_ctx_destroy(lmn_ctx *c) {
     for (auto &kv : c->rs) cudaFree(kv.second);
     for (auto &kv : c->galois) cudaFree(kv.second);
     cudaFree(c->d_mods); cudaFree(c->d_twf); cudaFree(c->d_twi); cudaFree(c->ws_pt); cudaFree(c->ws_scalar);
-    cudaFree(c->ws_col); cudaFree(c->ws_y); cudaFree(c->ws_acc); cudaFree(c->ws_idx);
+    cudaFree(c->ws_col); cudaFree(c->ws_col2); cudaFree(c->ws_y); cudaFree(c->ws_acc); cudaFree(c->ws_idx);
     cudaFree(c->d_rs_evk); cudaFree(c->d_small_mod); cudaFree(c->d_small_tw); cudaFree(c->d_key_fm); cudaFree(c->ws_mu);
     for (int i = 0; i < KID_COUNT; i++) for (auto &sp : c->prof.spans[i]) { cudaEventDestroy(sp.first); cudaEventDestroy(sp.second); }
     for (auto e : c->prof.pool) cudaEventDestroy(e);
@@ -664,7 +665,7 @@ int lmn_load_ring_switch_key(lmn_ctx *c, uint32_t logns, const uint64_t *evk, ui
 }
 
 // ---------------- InnerSum on the job workspace ----------------
-static int innersum_jobs(lmn_ctx *c, int level, const KsJobs &J, uint32_t n) {
+static int innersum_jobs(lmn_ctx *c, int level, KsJobs &J, uint32_t n) {
     const uint32_t N = (uint32_t)c->n;
     if (n == 0 || (n & (n - 1)) || n > N) return fail(LMN_ERR_UNSUPPORTED, "InnerSum is implemented for power-of-two n <= N");
     const KsConsts *Kh, *Kd;
@@ -677,7 +678,9 @@ static int innersum_jobs(lmn_ctx *c, int level, const KsJobs &J, uint32_t n) {
     if (full && c->rowswap_last) gals.push_back(2 * (u64)N - 1);
     for (u64 g : gals) if (!c->galois.count(g)) return fail(LMN_ERR_NOKEY, "missing Galois key for element " + std::to_string(g));
     Launch L = c->L();
+    const ptrdiff_t off = J.col - c->ws_col;
     for (u64 g : gals) launch_rotate_accumulate(L, c->T, Kd, *Kh, J, c->galois[g], (uint32_t)g);
+    if (J.col != c->ws_col + off) std::swap(c->ws_col, c->ws_col2);   // the view ended in the second buffer: make it the current one
     CK(cudaGetLastError());
     return 0;
 }

@@ -26,8 +26,8 @@ namespace lmn {
 
 static inline int ntt_threads(int m) { int t = m / 8; return t < 32 ? 32 : (t > 1024 ? 1024 : t); }
 const char *kernel_name(int id) {
-    static const char *names[KID_COUNT] = {"k_encode_pass", "k_mul_pt", "k_intt_c1", "k_modup", "k_mac", "k_pintt", "k_vpfix",
-                                           "k_down", "k_rs_intt", "k_rs_apply", "k_pack_out", "k_gather_in", "k_ring_decimate", "other"};
+    static const char *names[KID_COUNT] = {"k_encode_pass", "k_mul_pt", "k_intt_c1", "k_modup", "k_mac", "k_pintt", "k_down_pre",
+                                           "k_down", "k_rs_intt", "k_rs_pre", "k_rs_apply", "k_pack_out", "k_gather_in", "k_ring_decimate", "other"};
     return id >= 0 && id < KID_COUNT ? names[id] : "?";
 }
 cudaEvent_t Profiler::get() {
@@ -712,8 +712,36 @@ __global__ void __launch_bounds__(1024) k_down(const ModDev *mods, const ulonglo
     }
 }
 
+const char *kernels_blk_init();
+static bool use_blk_pipeline(int logn) {
+    static const bool off = getenv("LMN_BLK") && !strcmp(getenv("LMN_BLK"), "0");   // A/B switch: whole-limb kernels
+    return !off && blk_blocks(logn) > 0;
+}
+static void launch_mac_ra(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch, const KsJobs &J, const u64 *evk);
+
+// block pipeline (kernels_blk.cu): six launches per rotation, out of place col -> col2
+static void rotate_accumulate_blk(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch, KsJobs &J,
+                                  const u64 *evk, uint32_t gal_el) {
+    const int nq = Ch.nq, np = Ch.np, k = T.k, KP = T.k + T.np;
+    BlkSlots A;
+    A.src = J.col; A.src_job_words = J.col_words; A.dst = J.y; A.dst_job_words = J.y_words; A.nslots = nq;
+    for (int i = 0; i < nq; i++) { A.mod[i] = i; A.src_limb[i] = (uint32_t)(k + i); A.dst_limb[i] = (uint32_t)i; }
+    launch_blk_intt(L, T, A, J.jobs, KID_INTT_C1);
+    launch_modup_blk(L, T, Cd, Ch, J);
+    launch_mac_ra(L, T, Cd, Ch, J, evk);
+    BlkSlots B;
+    B.src = J.acc; B.src_job_words = J.acc_words; B.dst = J.acc; B.dst_job_words = J.acc_words; B.nslots = 2 * np;
+    for (int c = 0; c < 2; c++)
+        for (int j = 0; j < np; j++) { const int s = c * np + j; B.mod[s] = k + j; B.src_limb[s] = B.dst_limb[s] = (uint32_t)(c * KP + k + j); }
+    launch_blk_intt(L, T, B, J.jobs, KID_PINTT);
+    launch_down_pre(L, T, Cd, Ch, J);
+    launch_down_blk(L, T, Cd, Ch, J, gal_el, gal_el == 0 ? 1 : 0);
+    u64 *t = J.col; J.col = J.col2; J.col2 = t;
+}
+
 void launch_rotate_accumulate(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch,
-                              const KsJobs &J, const u64 *evk, uint32_t gal_el) {
+                              KsJobs &J, const u64 *evk, uint32_t gal_el) {
+    if (use_blk_pipeline(T.logn)) return rotate_accumulate_blk(L, T, Cd, Ch, J, evk, gal_el);
     const int N = T.n, nq = Ch.nq, np = Ch.np, jobs = J.jobs;
     const size_t sm_full = (size_t)padded_words(N) * 8;
     const int nt_full = ntt_threads(N);
@@ -734,19 +762,9 @@ void launch_rotate_accumulate(const Launch &L, const DeviceTables &T, const KsCo
         else if (Sm == 2) k_modup<2><<<g, bs, 0, L.stream>>>(T.mods, T.tw_fwd, Cd, J, T.logn, beta_max);
         else k_modup<1><<<g, bs, 0, L.stream>>>(T.mods, T.tw_fwd, Cd, J, T.logn, beta_max);
     }
-    { LaunchScope scope(L, KID_MAC);
-    if (SB && !use_r16) {
-        const size_t smm = (2 * (size_t)RA_M + 2 * (size_t)RA_WORDS) * 8;
-        const dim3 g((nq + np) * SB, jobs);
-        static const int var = getenv("LMN_MAC_VAR") ? atoi(getenv("LMN_MAC_VAR")) : 0;   // experiment switch: occupancy x prefetch
-#define MACRA(SS) do { \
-            if (var == 1) k_mac_ra<SS, 3, 3><<<g, RA_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk); \
-            else if (var == 2) k_mac_ra<SS, 3, 2><<<g, RA_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk); \
-            else if (var == 3) k_mac_ra<SS, 3, 0><<<g, RA_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk); \
-            else k_mac_ra<SS, 2, 3><<<g, RA_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk); } while (0)
-        if (SB == 8) MACRA(8); else if (SB == 4) MACRA(4); else MACRA(2);
-#undef MACRA
-    } else if (SB) {
+    if (SB && !use_r16) launch_mac_ra(L, T, Cd, Ch, J, evk);
+    else { LaunchScope scope(L, KID_MAC);
+    if (SB) {
         const int S16 = SB;
         const size_t smm = ((size_t)R16_WORDS + 2 * (size_t)R16_M + 2 * R16_STW) * 8;
         const dim3 g((nq + np) * S16, jobs);
@@ -778,8 +796,23 @@ void launch_rotate_accumulate(const Launch &L, const DeviceTables &T, const KsCo
                                                                                         gal_el == 0 ? 1 : 0)); }
 }
 
+static void launch_mac_ra(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch, const KsJobs &J, const u64 *evk) {
+    LaunchScope scope(L, KID_MAC);
+    const int SB = T.n >> RA_LOGM;
+    const size_t smm = (2 * (size_t)RA_M + 2 * (size_t)RA_WORDS) * 8;
+    const dim3 g((Ch.nq + Ch.np) * SB, J.jobs);
+    static const int var = getenv("LMN_MAC_VAR") ? atoi(getenv("LMN_MAC_VAR")) : 0;   // experiment switch: occupancy x prefetch
+#define MACRA(SS) do { \
+        if (var == 1) k_mac_ra<SS, 3, 3><<<g, RA_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk); \
+        else if (var == 2) k_mac_ra<SS, 3, 2><<<g, RA_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk); \
+        else if (var == 3) k_mac_ra<SS, 3, 0><<<g, RA_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk); \
+        else k_mac_ra<SS, 2, 3><<<g, RA_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk); } while (0)
+    if (SB == 8) MACRA(8); else if (SB == 4) MACRA(4); else MACRA(2);
+#undef MACRA
+}
+
 void launch_keyswitch_level0(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch,
-                             const KsJobs &J, const u64 *evk) {
+                             KsJobs &J, const u64 *evk) {
     launch_rotate_accumulate(L, T, Cd, Ch, J, evk, 0 /* mode 1: replace, no automorphism */);
 }
 
@@ -820,6 +853,15 @@ __global__ void __launch_bounds__(1024) k_rs_apply(const ModDev *mods, const ulo
         x[n] = mul_shoup(x[n] + q - barrett(sm[PAD(n)], q, md.mu), w, ws, q);
 }
 void launch_rescale_step(const Launch &L, const DeviceTables &T, const RescaleConsts *Rd, int level, const KsJobs &J) {
+    if (use_blk_pipeline(T.logn)) {
+        BlkSlots A;
+        A.src = J.col; A.src_job_words = J.col_words; A.dst = J.acc; A.dst_job_words = J.acc_words; A.nslots = 2;
+        for (int c = 0; c < 2; c++) { A.mod[c] = level; A.src_limb[c] = (uint32_t)(c * T.k + level); A.dst_limb[c] = (uint32_t)c; }
+        launch_blk_intt(L, T, A, J.jobs, KID_RS_INTT);
+        launch_rs_pre(L, T, Rd, level, J);
+        launch_rs_blk(L, T, Rd, level, J);
+        return;
+    }
     const size_t smf = (size_t)padded_words(T.n) * 8;
     const int nt = ntt_threads(T.n);
     { LaunchScope scope(L, KID_RS_INTT);
@@ -959,7 +1001,8 @@ const char *kernels_init() {
     SETSM((k_ring_decimate<8, 6>)); SETSM((k_ring_decimate<10, 6>)); SETSM((k_ring_decimate<10, 8>)); SETSM((k_ring_decimate<12, 8>));
 #undef SET_LOGN
 #undef SETSM
-    return e == cudaSuccess ? nullptr : cudaGetErrorString(e);
+    if (e == cudaSuccess) return kernels_blk_init();
+    return cudaGetErrorString(e);
 }
 
 }  // namespace lmn

@@ -72,7 +72,7 @@ struct EncPassArgs {
 
 // kernel classes (profiling / launch accounting)
 enum KernelId { KID_ENCODE = 0, KID_MULPT, KID_INTT_C1, KID_VFIX, KID_MAC, KID_PINTT, KID_VPFIX, KID_DOWN, KID_RS_INTT,
-                KID_RS_APPLY, KID_PACK, KID_GATHER, KID_DECIMATE, KID_OTHER, KID_COUNT };
+                KID_RS_PRE, KID_RS_APPLY, KID_PACK, KID_GATHER, KID_DECIMATE, KID_OTHER, KID_COUNT };
 const char *kernel_name(int id);
 
 // optional per-class device timing: CUDA event pairs recorded on the launch stream around each launch
@@ -115,14 +115,17 @@ void launch_encode_pass(const Launch &L, const EncPassArgs &A);
 // ---- key switch + automorphism + accumulate, for `jobs` columns laid out with fixed strides ----
 struct KsJobs {
     u64 *col;  uint64_t col_words;   // [jobs][2][k][N]
+    u64 *col2;                       // second buffer of the same shape: the block path (log N >= 11) rotates out of place
+                                     // (col -> col2) and swaps the two pointers of the view it was given
     u64 *y;    uint64_t y_words;     // [jobs][k][N]
     u64 *acc;  uint64_t acc_words;   // [jobs][2][k+np][N]
     u64 *mu;   uint64_t mu_words;    // [jobs][beta_max][k+np][N] base-converted digits (first NTT level applied when N = 16384)
     int jobs;
 };
 // col += pi_galEl( keyswitch(col) )      (AutomorphismHoisted + Add, lattigo rlwe/inner_sum.go)
+// On return J.col holds the result (the block path has swapped J.col and J.col2).
 void launch_rotate_accumulate(const Launch &L, const DeviceTables &T, const KsConsts *ksc_dev, const KsConsts &ksc_host,
-                              const KsJobs &J, const u64 *evk, uint32_t gal_el);
+                              KsJobs &J, const u64 *evk, uint32_t gal_el);
 // plain key switch without automorphism into (out0,out1) = (u0 + c0, u1) at level 0 (ring switch)
 // one Rescale step from level l on every job's col (in place, limb l dropped)
 void launch_rescale_step(const Launch &L, const DeviceTables &T, const RescaleConsts *rc_dev, int level,
@@ -137,7 +140,29 @@ void launch_ring_decimate(const Launch &L, const DeviceTables &T, const KsJobs &
                           const ulonglong2 *small_tw_fwd, u64 *out);
 // key switch at level 0 without automorphism: col[0][0] += u0 ; col[1][0] = u1
 void launch_keyswitch_level0(const Launch &L, const DeviceTables &T, const KsConsts *ksc_dev, const KsConsts &ksc_host,
-                             const KsJobs &J, const u64 *evk);
+                             KsJobs &J, const u64 *evk);
+
+// ---- 2048-point block pipeline (rings of 2048*S coefficients, S = 2, 4, 8; kernels_blk.cu) ----
+inline int blk_blocks(int logn) { return logn >= 12 ? 1 << (logn - 11) : 0; }   // S, or 0: whole-limb kernels
+struct BlkSlots {           // limb slots of one batched block transform
+    const u64 *src; uint64_t src_job_words;
+    u64 *dst;       uint64_t dst_job_words;
+    int nslots;
+    int mod[MAX_LIMBS];                                    // modulus index of the slot
+    uint32_t src_limb[MAX_LIMBS], dst_limb[MAX_LIMBS];     // limb offsets (units of N words) inside one job
+};
+// dst = raw block INTT of src (no N^-1, the log2(S) coupling levels pending; values in [0, 4q))
+void launch_blk_intt(const Launch &L, const DeviceTables &T, const BlkSlots &A, int jobs, int kid);
+// y (raw block INTTs of c1) -> mu: coupling levels, scaling, float64 v, base conversion, forward coupling levels
+void launch_modup_blk(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch, const KsJobs &J);
+// acc P limbs (raw block INTTs) -> mu[c][i]: coupling, scaling + P/2, float64 v, P -> q_i conversion, forward coupling levels
+void launch_down_pre(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch, const KsJobs &J);
+// block NTT of mu[c][i], (acc - ext) P^-1 (+c0), automorphism, col2 = col + pi(u)  (mode 1: col2 = u, no automorphism)
+void launch_down_blk(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch, const KsJobs &J,
+                     uint32_t gal_el, int mode);
+// rescale step from `level`: acc slots c (raw block INTT of limb `level`) -> mu[c][i], then block NTT + apply in place
+void launch_rs_pre(const Launch &L, const DeviceTables &T, const RescaleConsts *Rd, int level, const KsJobs &J);
+void launch_rs_blk(const Launch &L, const DeviceTables &T, const RescaleConsts *Rd, int level, const KsJobs &J);
 
 const char *kernels_init();  // sets dynamic shared memory attributes; returns nullptr or error string
 

@@ -1,0 +1,460 @@
+// 2048-point block pipeline of the hybrid key switch and the rescale for rings of N = 2048*S coefficients (S = 2, 4, 8
+// <-> log N = 12, 13, 14; configs A/B, C, D of BASELINE.json).
+//
+// Every length-N transform is S independent 2048-point block transforms (256 threads x 8 register-resident residues, all
+// of the block's twiddles in shared memory, ntt_r16.cuh) plus log2(S) levels that couple the blocks.  The coupling levels
+// are pointwise over the S points n + r*M of a limb, so they live in the elementwise kernels that sit between an inverse
+// and a forward transform anyway (base conversions):
+//
+//   k_blk_intt   raw block INTT                      (DecomposeNTT's INTT of c1; ModDown's INTT of the P part; Rescale's INTT)
+//   k_modup_blk  coupling + N^-1 (Q_d/q_i)^-1, float64 v, digit -> every other modulus, forward coupling
+//   k_mac_ra     block NTT + gadget MAC              (kernels.cu)
+//   k_down_pre   coupling + N^-1 (P/p_j)^-1 + P/2, float64 v, P -> q_i, forward coupling
+//   k_blk_fwd<0> block NTT, (acc - ext) P^-1 (+c0), automorphism, out = in + pi(u)
+//   k_rs_pre / k_blk_fwd<2>   the same shape for DivRoundByLastModulusNTT
+//
+// References: lattigo rlwe.Evaluator.DecomposeNTT / GadgetProductHoisted / ModDownQPtoQNTT / AutomorphismHoisted and
+// ring.DivRoundByLastModulusNTT as called from fhe/ligero.go:325 (InnerSum) and :331-333, :271-273 (Rescale); restated
+// in oracle/lumenos_oracle.c.
+#include "kernels.cuh"
+#include "ntt_r16.cuh"
+
+namespace lmn {
+
+constexpr size_t BLK_SMEM = (2 * (size_t)RA_M + 2 * (size_t)RA_WORDS) * 8;   // twiddle table + two transposition buffers
+template <int S> struct LogS { static constexpr int v = S == 8 ? 3 : S == 4 ? 2 : S == 2 ? 1 : 0; };
+
+// ---------------------------------------------------------------------------------------------------
+// raw block INTT of `nslots` limbs of `jobs` jobs.  grid (S*nslots, ceil(jobs/jb)); one CTA owns block h of slot s for jb
+// consecutive jobs (the 32 KB twiddle table is filled once).  In-place use (src == dst) is safe: a CTA reads its whole
+// block of a job before it writes it.
+// ---------------------------------------------------------------------------------------------------
+template <int S>
+__global__ void __launch_bounds__(RA_THREADS, 3) k_blk_intt(const ModDev *mods, const ulonglong2 *tw_inv, const BlkSlots A, int jobs, int jb) {
+    extern __shared__ u64 sm[];
+    constexpr int LOGN = RA_LOGM + LogS<S>::v;
+    ulonglong2 *stw = reinterpret_cast<ulonglong2 *>(sm);
+    u64 *buf0 = sm + 2 * RA_M, *buf1 = buf0 + RA_WORDS;
+    const int slot = blockIdx.x / S, h = blockIdx.x % S;
+    const int gm = A.mod[slot];
+    const ModDev md = mods[gm];
+    const FwdMod fm = {md.q, 0 - md.q, md.q3};
+    ra_fill_stw(stw, tw_inv + ((size_t)gm << LOGN), S + h);
+    const unsigned u = threadIdx.x;
+    const size_t soff = ((size_t)A.src_limb[slot] << LOGN) + (size_t)h * RA_M + 8 * u;
+    const size_t doff = ((size_t)A.dst_limb[slot] << LOGN) + (size_t)h * RA_M + u;
+    const int j0 = blockIdx.y * jb, j1 = min(jobs, j0 + jb);
+    u64 a[8];
+    auto load = [&](int job) {
+        const ulonglong2 *p = reinterpret_cast<const ulonglong2 *>(A.src + (size_t)job * A.src_job_words + soff);
+#pragma unroll
+        for (int r = 0; r < 4; r++) { const ulonglong2 v = p[r]; a[2 * r] = v.x; a[2 * r + 1] = v.y; }
+    };
+    load(j0);
+    __syncthreads();   // twiddle table visible
+    int flip = 0;
+    for (int job = j0; job < j1; job++) {
+        ntt2048_inv(a, flip ? buf1 : buf0, stw, fm);
+        flip ^= 1;
+        u64 *o = A.dst + (size_t)job * A.dst_job_words + doff;
+#pragma unroll
+        for (int r = 0; r < 8; r++) o[256 * r] = a[r];
+        if (job + 1 < j1) load(job + 1);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// digit d of y (raw block INTTs of c1) -> every other modulus (lattigo DecomposeAndSplit: reconstructRNS + multSum).
+// One thread owns the S points n + r*M of the limb: it finishes the INTT (coupling levels, then the exact product with
+// N^-1 (Q_d/q_a)^-1), folds the float64 overflow estimate v = floor(sum_a float64(y_a)/float64(q_a)) (same operation order
+// as Go) into the first residue, z_0 = y_0 + (nd-1-v) q_0, converts to each target modulus and applies the forward
+// coupling levels, so that k_mac_ra runs independent block transforms.  ND = digit size (0: read at run time).
+// grid (M/256, digits, jobs)
+// ---------------------------------------------------------------------------------------------------
+template <int S, int ND>
+__global__ void __launch_bounds__(256) k_modup_blk(const ModDev *mods, const ulonglong2 *tw_fwd, const ulonglong2 *tw_inv,
+                                                    const KsConsts *C, const KsJobs J, int d0) {
+    constexpr int LOGN = RA_LOGM + LogS<S>::v;
+    constexpr int M = RA_M;
+    constexpr int NDM = ND ? ND : MAX_P;
+    const int d = d0 + blockIdx.y, job = blockIdx.z;
+    const int nd = ND ? ND : C->dig_size[d], s0 = C->dig_start[d];
+    const int nq = C->nq, k = C->k, KP = k + C->np;
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    const u64 *y = J.y + (size_t)job * J.y_words;
+    u64 *mu = J.mu + (size_t)job * J.mu_words + (((size_t)d * KP) << LOGN);
+    u64 z[NDM][S];
+#pragma unroll
+    for (int a = 0; a < NDM; a++) {
+        if (a < nd) {
+            const int gm = s0 + a;
+            const u64 q = mods[gm].q;
+            const FwdMod fm = {q, 0 - q, mods[gm].q3};
+            const u64 *src = y + ((size_t)gm << LOGN) + n;
+#pragma unroll
+            for (int r = 0; r < S; r++) z[a][r] = src[(size_t)r * M];
+            couple_inv<S>(z[a], tw_inv + ((size_t)gm << LOGN), fm);
+            const u64 w = C->intt_w[gm], ws = C->intt_ws[gm];
+#pragma unroll
+            for (int r = 0; r < S; r++) z[a][r] = mul_shoup(z[a][r], w, ws, q);
+        } else {
+#pragma unroll
+            for (int r = 0; r < S; r++) z[a][r] = 0;
+        }
+    }
+    if (nd >= 2) {
+        const u64 q0 = mods[s0].q;
+#pragma unroll
+        for (int r = 0; r < S; r++) {
+            double vf = 0.0;
+#pragma unroll
+            for (int a = 0; a < NDM; a++)
+                if (a < nd) vf = __dadd_rn(vf, __ddiv_rn(__ull2double_rn(z[a][r]), __ull2double_rn(mods[s0 + a].q)));
+            z[0][r] += (u64)(nd - 1 - (int)__double2ull_rz(vf)) * q0;
+        }
+    }
+    const int ntix = nq + C->np;
+#pragma unroll 1
+    for (int tix = 0; tix < ntix; tix++) {
+        if (tix < nq && tix >= s0 && tix < s0 + nd) continue;   // own limbs are copied from the NTT-domain input
+        const int gm = ks_mod_index(tix, nq, k);
+        const u64 p = mods[gm].q, pinv = mods[gm].qinv;
+        const FwdMod fm = {p, 0 - p, mods[gm].q3};
+        u64 vals[S];
+        if (nd == 1) {
+            // single-prime digit: centred lift (DecomposeAndSplit, decompLvl < 0), then the key-row scale 2^(e-64)
+            const u64 qd = mods[s0].q, hq = qd >> 1, gw = C->mu_g_w[d][tix], gws = C->mu_g_ws[d][tix], pmu = mods[gm].mu;
+#pragma unroll
+            for (int r = 0; r < S; r++) {
+                const u64 c = z[0][r];
+                const bool neg = c >= hq;
+                const u64 rr = barrett(neg ? qd - c : c, p, pmu);
+                vals[r] = mul_shoup_lazy(neg ? (rr ? p - rr : 0) : rr, gw, gws, p);
+            }
+        } else if (C->mu_fast[d][tix]) {
+            const uint32_t sgn = C->mu_sgn[d][tix];
+            uint32_t mag[NDM];
+#pragma unroll
+            for (int a = 0; a < NDM; a++) mag[a] = a < nd ? C->mu_mag[d][tix][a] : 0;
+            const u64 klo = C->mu_k_lo[d][tix], khi = C->mu_k_hi[d][tix];
+#pragma unroll
+            for (int r = 0; r < S; r++) {
+                u64 lo = klo, hi = khi;
+#pragma unroll
+                for (int a = 0; a < NDM; a++) {
+                    if (a < nd) {
+                        // 64 x 32 -> 96-bit product with two 32x32 multiplies
+                        const u64 p0 = (u64)(uint32_t)z[a][r] * mag[a];
+                        const u64 p1 = (u64)(uint32_t)(z[a][r] >> 32) * mag[a];
+                        const u64 plo = p0 + (p1 << 32);
+                        const u64 phi = (p1 >> 32) + (plo < p0);
+                        if ((sgn >> a) & 1) { const u64 t = lo; lo -= plo; hi -= phi + (t < plo); }
+                        else { lo += plo; hi += phi + (lo < plo); }
+                    }
+                }
+                vals[r] = mont_reduce_lazy(lo, hi, p, pinv);
+            }
+        } else {
+            u64 cm[NDM];
+#pragma unroll
+            for (int a = 0; a < NDM; a++) cm[a] = a < nd ? C->mu_c[d][tix][a] : 0;
+            const u64 klo = C->mu_k_lo[d][tix], khi = C->mu_k_hi[d][tix];
+#pragma unroll
+            for (int r = 0; r < S; r++) {
+                u64 lo = klo, hi = khi;
+#pragma unroll
+                for (int a = 0; a < NDM; a++)
+                    if (a < nd) mac128(lo, hi, z[a][r], cm[a]);
+                vals[r] = csub(mont_reduce_lazy(lo, hi, p, pinv), 2 * p);
+            }
+        }
+        couple_fwd<S>(vals, tw_fwd + ((size_t)gm << LOGN), fm);
+        u64 *o = mu + ((size_t)gm << LOGN) + n;
+#pragma unroll
+        for (int r = 0; r < S; r++) o[(size_t)r * M] = vals[r];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// ModDown, pointwise part (lattigo BasisExtender.ModDownQPtoQNTT): the P limbs of the accumulators arrive as raw block
+// INTTs; finish them (coupling levels, N^-1 (P/p_j)^-1, + P/2), fold the float64 v of ModUpExact into the first residue,
+// convert to every q_i and apply the forward coupling levels.  Output: mu[c][i][N].  grid (M/256, 2, jobs)
+// ---------------------------------------------------------------------------------------------------
+template <int S>
+__global__ void __launch_bounds__(256) k_down_pre(const ModDev *mods, const ulonglong2 *tw_fwd, const ulonglong2 *tw_inv,
+                                                   const KsConsts *C, const KsJobs J) {
+    constexpr int LOGN = RA_LOGM + LogS<S>::v;
+    constexpr int M = RA_M;
+    const int c = blockIdx.y, job = blockIdx.z;
+    const int k = C->k, np = C->np, nq = C->nq, KP = k + np;
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    const u64 *accp = J.acc + (size_t)job * J.acc_words + (((size_t)c * KP + k) << LOGN) + n;
+    u64 z[MAX_P][S];
+#pragma unroll
+    for (int a = 0; a < MAX_P; a++) {
+        if (a < np) {
+            const int gm = k + a;
+            const u64 p = mods[gm].q;
+            const FwdMod fm = {p, 0 - p, mods[gm].q3};
+#pragma unroll
+            for (int r = 0; r < S; r++) z[a][r] = accp[((size_t)a << LOGN) + (size_t)r * M];
+            couple_inv<S>(z[a], tw_inv + ((size_t)gm << LOGN), fm);
+            const u64 w = C->pin_w[a], ws = C->pin_ws[a], ad = C->pin_add[a];
+#pragma unroll
+            for (int r = 0; r < S; r++) z[a][r] = add_mod(mul_shoup(z[a][r], w, ws, p), ad, p);
+        } else {
+#pragma unroll
+            for (int r = 0; r < S; r++) z[a][r] = 0;
+        }
+    }
+    if (np >= 2) {
+        const u64 p0 = mods[k].q;
+#pragma unroll
+        for (int r = 0; r < S; r++) {
+            double vf = 0.0;
+#pragma unroll
+            for (int a = 0; a < MAX_P; a++)
+                if (a < np) vf = __dadd_rn(vf, __ddiv_rn(__ull2double_rn(z[a][r]), __ull2double_rn(mods[k + a].q)));
+            z[0][r] += (u64)(np - 1 - (int)__double2ull_rz(vf)) * p0;
+        }
+    }
+    u64 *tmp = J.mu + (size_t)job * J.mu_words + (((size_t)c * nq) << LOGN) + n;
+#pragma unroll 1
+    for (int i = 0; i < nq; i++) {
+        const u64 q = mods[i].q, qinv = mods[i].qinv;
+        const FwdMod fm = {q, 0 - q, mods[i].q3};
+        u64 cm[MAX_P];
+#pragma unroll
+        for (int a = 0; a < MAX_P; a++) cm[a] = a < np ? C->md_c[i][a] : 0;
+        const u64 neg = C->md_neg[i];
+        u64 vals[S];
+#pragma unroll
+        for (int r = 0; r < S; r++) {
+            u64 lo = 0, hi = neg;
+#pragma unroll
+            for (int a = 0; a < MAX_P; a++)
+                if (a < np) mac128(lo, hi, z[a][r], cm[a]);
+            vals[r] = csub(mont_reduce_lazy(lo, hi, q, qinv), 2 * q);
+        }
+        couple_fwd<S>(vals, tw_fwd + ((size_t)i << LOGN), fm);
+        u64 *o = tmp + ((size_t)i << LOGN);
+#pragma unroll
+        for (int r = 0; r < S; r++) o[(size_t)r * M] = vals[r];
+    }
+}
+
+// Rescale, pointwise part (ring.DivRoundByLastModulusNTT): acc slot c holds the raw block INTT of limb `level`; finish it
+// (coupling, N^-1), add q_l/2, and for every remaining limb reduce, subtract q_l/2 mod q_i and apply the forward coupling
+// levels.  Output mu[c][i][N].  grid (M/256, 2, jobs)
+template <int S>
+__global__ void __launch_bounds__(256) k_rs_pre(const ModDev *mods, const ulonglong2 *tw_fwd, const ulonglong2 *tw_inv,
+                                                 const RescaleConsts *R, const KsJobs J, int level) {
+    constexpr int LOGN = RA_LOGM + LogS<S>::v;
+    constexpr int M = RA_M;
+    const int c = blockIdx.y, job = blockIdx.z;
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    const ModDev ml = mods[level];
+    const FwdMod fl = {ml.q, 0 - ml.q, ml.q3};
+    const u64 *raw = J.acc + (size_t)job * J.acc_words + ((size_t)c << LOGN) + n;
+    u64 v[S];
+#pragma unroll
+    for (int r = 0; r < S; r++) v[r] = raw[(size_t)r * M];
+    couple_inv<S>(v, tw_inv + ((size_t)level << LOGN), fl);
+    const u64 half = R->half;
+#pragma unroll
+    for (int r = 0; r < S; r++) v[r] = add_mod(mul_shoup(v[r], ml.ninv, ml.ninvs, ml.q), half, ml.q);
+    u64 *tmp = J.mu + (size_t)job * J.mu_words + (((size_t)c * level) << LOGN) + n;
+#pragma unroll 1
+    for (int i = 0; i < level; i++) {
+        const u64 q = mods[i].q, qmu = mods[i].mu, hm = R->half_mod[i];
+        const FwdMod fm = {q, 0 - q, mods[i].q3};
+        u64 vals[S];
+#pragma unroll
+        for (int r = 0; r < S; r++) vals[r] = sub_mod(barrett(v[r], q, qmu), hm, q);
+        couple_fwd<S>(vals, tw_fwd + ((size_t)i << LOGN), fm);
+        u64 *o = tmp + ((size_t)i << LOGN);
+#pragma unroll
+        for (int r = 0; r < S; r++) o[(size_t)r * M] = vals[r];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// block NTT of mu[c][i] + epilogue.  grid (S*nlimbs, 2, ceil(jobs/jb)); one CTA owns block h of limb i of poly c for jb jobs.
+//   MODE 0  u = (acc - ext) P^-1 (+ c0), then AutomorphismHoisted + Add: col2 = col + pi(u).  The permutation
+//           out[n] = in[index(n)] of the NTT domain maps blocks onto blocks (the top log2(S) bits of index(n) depend only
+//           on those of n), so the CTA stages its block of u in shared memory and gathers from it while it streams the
+//           one destination block of col -> col2 (coalesced).  Out of place: other CTAs read col block-wise for "+ c0".
+//   MODE 1  col2 = u  (no automorphism: the ring-switch key switch)
+//   MODE 2  Rescale: col_i = (col_i - ext) q_l^-1, in place
+// ---------------------------------------------------------------------------------------------------
+template <int S, int MODE>
+__global__ void __launch_bounds__(RA_THREADS, 3) k_blk_fwd(const ModDev *mods, const ulonglong2 *tw_fwd, const KsConsts *C,
+                                                            const RescaleConsts *R, const KsJobs J, uint32_t gal_el, int nlimbs,
+                                                            int k, int np, int jobs, int jb) {
+    extern __shared__ u64 sm[];
+    constexpr int LOGN = RA_LOGM + LogS<S>::v;
+    constexpr int M = RA_M;
+    ulonglong2 *stw = reinterpret_cast<ulonglong2 *>(sm);
+    u64 *buf0 = sm + 2 * RA_M, *buf1 = buf0 + RA_WORDS;
+    const int i = blockIdx.x / S, h = blockIdx.x % S, c = blockIdx.y;
+    const ModDev md = mods[i];
+    const u64 q = md.q;
+    const FwdMod fm = {q, 0 - q, md.q3};
+    ra_fill_stw(stw, tw_fwd + ((size_t)i << LOGN), S + h);
+    const unsigned u = threadIdx.x;
+    const int KP = k + np;   // k = limb stride of col (Q limbs of the context), KP = limb stride of acc
+    const u64 w = MODE == 2 ? R->qlinv_w[i] : C->pinv_w[i], ws = MODE == 2 ? R->qlinv_ws[i] : C->pinv_ws[i];
+    const size_t blk = (size_t)h * M;
+    int hd = 0;   // destination block of the automorphism
+    if (MODE == 0) {
+#pragma unroll
+        for (int hp = 0; hp < S; hp++)
+            if ((int)(auto_index((unsigned)hp * M, gal_el, LOGN) >> RA_LOGM) == h) hd = hp;
+    }
+    const int j0 = blockIdx.z * jb, j1 = min(jobs, j0 + jb);
+    u64 a[8];
+    auto load = [&](int job) {
+        const u64 *src = J.mu + (size_t)job * J.mu_words + (((size_t)c * nlimbs + i) << LOGN) + blk + u;
+#pragma unroll
+        for (int r = 0; r < 8; r++) a[r] = src[256 * r];
+    };
+    load(j0);
+    __syncthreads();   // twiddle table visible
+    int flip = 0;
+    for (int job = j0; job < j1; job++) {
+        u64 *s = flip ? buf1 : buf0;
+        flip ^= 1;
+        ntt2048_fwd(a, s, stw, fm, []() {});
+        // a[r] = point 8u + r of the block, lazy
+        if (MODE == 2) {
+            ulonglong2 *x = reinterpret_cast<ulonglong2 *>(J.col + (size_t)job * J.col_words + (((size_t)c * k + i) << LOGN) + blk + 8 * u);
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                ulonglong2 v = x[r];
+                v.x = mul_shoup(v.x + q - barrett(a[2 * r], q, md.mu), w, ws, q);
+                v.y = mul_shoup(v.y + q - barrett(a[2 * r + 1], q, md.mu), w, ws, q);
+                x[r] = v;
+            }
+        } else {
+            const ulonglong2 *aq = reinterpret_cast<const ulonglong2 *>(J.acc + (size_t)job * J.acc_words + (((size_t)c * KP + i) << LOGN) + blk + 8 * u);
+            const u64 *colin = J.col + (size_t)job * J.col_words + (((size_t)c * k + i) << LOGN);
+            u64 *colout = J.col2 + (size_t)job * J.col_words + (((size_t)c * k + i) << LOGN);
+            const ulonglong2 *c0 = reinterpret_cast<const ulonglong2 *>(colin + blk + 8 * u);
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                ulonglong2 v = aq[r];
+                v.x = mul_shoup(v.x + q - barrett(a[2 * r], q, md.mu), w, ws, q);
+                v.y = mul_shoup(v.y + q - barrett(a[2 * r + 1], q, md.mu), w, ws, q);
+                if (c == 0) { const ulonglong2 t = c0[r]; v.x = add_mod(v.x, t.x, q); v.y = add_mod(v.y, t.y, q); }
+                if (MODE == 1) reinterpret_cast<ulonglong2 *>(colout + blk + 8 * u)[r] = v;
+                else { s[PAD(8 * u + 2 * r)] = v.x; s[PAD(8 * u + 2 * r + 1)] = v.y; }   // the thread's own pass-D slots
+            }
+            if (MODE == 0) {
+                __syncthreads();
+                const size_t nb = (size_t)hd * M + 8 * u;
+                const ulonglong2 *ci = reinterpret_cast<const ulonglong2 *>(colin + nb);
+                ulonglong2 *co = reinterpret_cast<ulonglong2 *>(colout + nb);
+#pragma unroll
+                for (int r = 0; r < 4; r++) {
+                    ulonglong2 v = ci[r];
+                    const unsigned sa = auto_index((unsigned)nb + 2 * r, gal_el, LOGN) & (M - 1);
+                    const unsigned sb = auto_index((unsigned)nb + 2 * r + 1, gal_el, LOGN) & (M - 1);
+                    v.x = add_mod(v.x, s[PAD(sa)], q);
+                    v.y = add_mod(v.y, s[PAD(sb)], q);
+                    co[r] = v;
+                }
+            }
+        }
+        if (job + 1 < j1) load(job + 1);
+    }
+}
+
+// =====================================================================================================
+// launchers
+// =====================================================================================================
+// jobs per CTA: as many as keep at least four waves of CTAs in flight (the twiddle table is filled once per CTA)
+static int pick_jb(int ctas_per_job, int jobs) {
+    const int want = 4 * 148 * 3;
+    for (int jb = 4; jb > 1; jb >>= 1)
+        if ((long)ctas_per_job * ((jobs + jb - 1) / jb) >= want) return jb;
+    return 1;
+}
+#define LMN_DISPATCH_S(SB, ...)                                  \
+    switch (SB) {                                                \
+        case 2: { constexpr int SS = 2; __VA_ARGS__; } break;    \
+        case 4: { constexpr int SS = 4; __VA_ARGS__; } break;    \
+        case 8: { constexpr int SS = 8; __VA_ARGS__; } break;    \
+        default: break;                                          \
+    }
+
+void launch_blk_intt(const Launch &L, const DeviceTables &T, const BlkSlots &A, int jobs, int kid) {
+    LaunchScope scope(L, kid);
+    const int SB = blk_blocks(T.logn);
+    const int jb = pick_jb(SB * A.nslots, jobs);
+    const dim3 g(SB * A.nslots, (jobs + jb - 1) / jb);
+    LMN_DISPATCH_S(SB, k_blk_intt<SS><<<g, RA_THREADS, BLK_SMEM, L.stream>>>(T.mods, T.tw_inv, A, jobs, jb));
+}
+
+void launch_modup_blk(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch, const KsJobs &J) {
+    LaunchScope scope(L, KID_VFIX);
+    const int SB = blk_blocks(T.logn);
+    // digits of the common size np run with the digit size as a template parameter; a shorter last digit separately
+    int full = 0;
+    while (full < Ch.beta && Ch.dig_size[full] == Ch.np) full++;
+    const int xb = RA_M / 256;
+    if (full) {
+        const dim3 g(xb, full, J.jobs);
+        if (Ch.np == 2) { LMN_DISPATCH_S(SB, k_modup_blk<SS, 2><<<g, 256, 0, L.stream>>>(T.mods, T.tw_fwd, T.tw_inv, Cd, J, 0)); }
+        else if (Ch.np == 1) { LMN_DISPATCH_S(SB, k_modup_blk<SS, 1><<<g, 256, 0, L.stream>>>(T.mods, T.tw_fwd, T.tw_inv, Cd, J, 0)); }
+        else { LMN_DISPATCH_S(SB, k_modup_blk<SS, 0><<<g, 256, 0, L.stream>>>(T.mods, T.tw_fwd, T.tw_inv, Cd, J, 0)); }
+    }
+    if (full < Ch.beta) {
+        const dim3 g(xb, Ch.beta - full, J.jobs);
+        if (Ch.dig_size[full] == 1 && Ch.beta - full == 1) { LMN_DISPATCH_S(SB, k_modup_blk<SS, 1><<<g, 256, 0, L.stream>>>(T.mods, T.tw_fwd, T.tw_inv, Cd, J, full)); }
+        else { LMN_DISPATCH_S(SB, k_modup_blk<SS, 0><<<g, 256, 0, L.stream>>>(T.mods, T.tw_fwd, T.tw_inv, Cd, J, full)); }
+    }
+}
+
+void launch_down_pre(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch, const KsJobs &J) {
+    LaunchScope scope(L, KID_VPFIX);
+    const int SB = blk_blocks(T.logn);
+    const dim3 g(RA_M / 256, 2, J.jobs);
+    LMN_DISPATCH_S(SB, k_down_pre<SS><<<g, 256, 0, L.stream>>>(T.mods, T.tw_fwd, T.tw_inv, Cd, J));
+}
+
+void launch_down_blk(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch, const KsJobs &J,
+                     uint32_t gal_el, int mode) {
+    LaunchScope scope(L, KID_DOWN);
+    const int SB = blk_blocks(T.logn);
+    const int jb = pick_jb(SB * Ch.nq * 2, J.jobs);
+    const dim3 g(SB * Ch.nq, 2, (J.jobs + jb - 1) / jb);
+    if (mode == 1) { LMN_DISPATCH_S(SB, k_blk_fwd<SS, 1><<<g, RA_THREADS, BLK_SMEM, L.stream>>>(T.mods, T.tw_fwd, Cd, nullptr, J, gal_el, Ch.nq, T.k, T.np, J.jobs, jb)); }
+    else { LMN_DISPATCH_S(SB, k_blk_fwd<SS, 0><<<g, RA_THREADS, BLK_SMEM, L.stream>>>(T.mods, T.tw_fwd, Cd, nullptr, J, gal_el, Ch.nq, T.k, T.np, J.jobs, jb)); }
+}
+
+void launch_rs_pre(const Launch &L, const DeviceTables &T, const RescaleConsts *Rd, int level, const KsJobs &J) {
+    LaunchScope scope(L, KID_RS_PRE);
+    const int SB = blk_blocks(T.logn);
+    const dim3 g(RA_M / 256, 2, J.jobs);
+    LMN_DISPATCH_S(SB, k_rs_pre<SS><<<g, 256, 0, L.stream>>>(T.mods, T.tw_fwd, T.tw_inv, Rd, J, level));
+}
+
+void launch_rs_blk(const Launch &L, const DeviceTables &T, const RescaleConsts *Rd, int level, const KsJobs &J) {
+    LaunchScope scope(L, KID_RS_APPLY);
+    const int SB = blk_blocks(T.logn);
+    const int jb = pick_jb(SB * level * 2, J.jobs);
+    const dim3 g(SB * level, 2, (J.jobs + jb - 1) / jb);
+    LMN_DISPATCH_S(SB, k_blk_fwd<SS, 2><<<g, RA_THREADS, BLK_SMEM, L.stream>>>(T.mods, T.tw_fwd, nullptr, Rd, J, 0u, level, T.k, T.np, J.jobs, jb));
+}
+
+const char *kernels_blk_init() {
+    cudaError_t e = cudaSuccess;
+#define SETSM(K) do { if (e == cudaSuccess) e = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BLK_SMEM); } while (0)
+#define SETS(SS) SETSM(k_blk_intt<SS>); SETSM((k_blk_fwd<SS, 0>)); SETSM((k_blk_fwd<SS, 1>)); SETSM((k_blk_fwd<SS, 2>));
+    SETS(2) SETS(4) SETS(8)
+#undef SETS
+#undef SETSM
+    return e == cudaSuccess ? nullptr : cudaGetErrorString(e);
+}
+
+}  // namespace lmn

@@ -251,4 +251,98 @@ __device__ __forceinline__ void ntt2048_fwd(u64 (&a)[8], u64 *s, const ulonglong
         bfly_ct3(a[2 * b], a[2 * b + 1], w, m);
     }
 }
+
+// ---------------------------------------------------------------------------------------------------
+// inverse of a 2048-point block (Gentleman-Sande).  Invariant [0, 4q): the sum is corrected by 4q once, the difference
+// (x - y + 4q < 8q) is multiplied with the 3-product quotient estimate, whose lazy result lies in [0, 3q).  The exact
+// transform mod q is unchanged; consumers finish with an exact (canonical) multiplication by N^-1.
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void bfly_gs3(u64 &x, u64 &y, const ulonglong2 w, const FwdMod &m, u64 q4) {
+    const u64 s = x + y;
+    const u64 d = x - y + q4;
+    x = s >= q4 ? s - q4 : s;
+    y = mul_shoup_approx(d, w.x, w.y, m.nq);
+}
+template <class F>
+__device__ __forceinline__ void r8_inv_f(u64 (&a)[8], F tw_of, const FwdMod &m, u64 q4) {
+#pragma unroll
+    for (int t = 2; t >= 0; t--) {
+        const int half = 4 >> t;
+#pragma unroll
+        for (int b = 0; b < (1 << t); b++) {
+            const ulonglong2 w = tw_of(t, b);
+#pragma unroll
+            for (int j = 0; j < half; j++) bfly_gs3(a[b * 2 * half + j], a[b * 2 * half + j + half], w, m, q4);
+        }
+    }
+}
+// in a[r] = point 8u + r of the block (values in [0, 4q)); out a[r] = point u + 256 r, in [0, 4q), NOT scaled by N^-1;
+// the log2(S) levels that couple the S blocks of a limb remain to be applied by the consumer.  stw = the block's table of
+// INVERSE twiddles (ra_fill_stw on RootsBackward).  `s` as in ntt2048_fwd.
+__device__ __forceinline__ void ntt2048_inv(u64 (&a)[8], u64 *s, const ulonglong2 *stw, const FwdMod &m) {
+    const unsigned u = threadIdx.x;
+    const u64 q4 = 4 * m.q;
+#pragma unroll
+    for (int b = 0; b < 4; b++) {                                                           // level 10: groups 4u + b
+        const ulonglong2 w = stw[1024 + b * 256 + u];
+        bfly_gs3(a[2 * b], a[2 * b + 1], w, m, q4);
+    }
+#pragma unroll
+    for (int b = 0; b < 2; b++) {                                                           // level 9: groups 2u + b
+        const ulonglong2 w = stw[512 + b * 256 + u];
+        bfly_gs3(a[4 * b], a[4 * b + 2], w, m, q4); bfly_gs3(a[4 * b + 1], a[4 * b + 3], w, m, q4);
+    }
+#pragma unroll
+    for (int r = 0; r < 8; r++) s[PAD(8 * u + r)] = a[r];
+    __syncthreads();
+    { const unsigned i = u >> 2, j = u & 3;
+#pragma unroll
+      for (int r = 0; r < 8; r++) a[r] = s[PAD(i * 32 + j + 4 * r)];
+      r8_inv_f(a, [&](int t, int b) { return stw[((64 + i) << t) + b]; }, m, q4);           // levels 8-6
+#pragma unroll
+      for (int r = 0; r < 8; r++) s[PAD(i * 32 + j + 4 * r)] = a[r]; }
+    __syncthreads();
+    { const unsigned i = u >> 5, j = u & 31;
+#pragma unroll
+      for (int r = 0; r < 8; r++) a[r] = s[PAD(i * 256 + j + 32 * r)];
+      r8_inv_f(a, [&](int t, int b) { return stw[((8 + i) << t) + b]; }, m, q4);            // levels 5-3
+#pragma unroll
+      for (int r = 0; r < 8; r++) s[PAD(i * 256 + j + 32 * r)] = a[r]; }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < 8; r++) a[r] = s[PAD(u + 256 * r)];
+    r8_inv_f(a, [&](int t, int b) { return stw[(1 << t) + b]; }, m, q4);                    // levels 2-0
+}
+
+// the log2(S) Gentleman-Sande levels that couple the S blocks of a limb, on the S values v[r] = point n + r*M of the limb
+// (inverse twiddle table of the limb's modulus: index (1 << t) + b at the level with 2^t groups); [0, 4q) in and out
+template <int S>
+__device__ __forceinline__ void couple_inv(u64 (&v)[S], const ulonglong2 *__restrict__ twi, const FwdMod &m) {
+    const u64 q4 = 4 * m.q;
+#pragma unroll
+    for (int half = 1; half < S; half <<= 1) {          // level with S / (2 half) groups
+        const int groups = S / (2 * half);
+#pragma unroll
+        for (int b = 0; b < groups; b++) {
+            const ulonglong2 w = __ldg(&twi[groups + b]);
+#pragma unroll
+            for (int j = 0; j < half; j++) bfly_gs3(v[b * 2 * half + j], v[b * 2 * half + j + half], w, m, q4);
+        }
+    }
+}
+// the log2(S) Cooley-Tukey levels that couple the S blocks (forward twiddle table of the limb's modulus); values grow by 3q
+// per level
+template <int S>
+__device__ __forceinline__ void couple_fwd(u64 (&v)[S], const ulonglong2 *__restrict__ twf, const FwdMod &m) {
+#pragma unroll
+    for (int half = S / 2; half >= 1; half >>= 1) {     // level with S / (2 half) groups
+        const int groups = S / (2 * half);
+#pragma unroll
+        for (int b = 0; b < groups; b++) {
+            const ulonglong2 w = __ldg(&twf[groups + b]);
+#pragma unroll
+            for (int j = 0; j < half; j++) bfly_ct3(v[b * 2 * half + j], v[b * 2 * half + j + half], w, m);
+        }
+    }
+}
 }  // namespace lmn

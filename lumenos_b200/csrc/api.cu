@@ -627,9 +627,12 @@ int lmn_load_galois_key(lmn_ctx *c, uint64_t gal_el, const uint64_t *evk) {
     u64 *d = nullptr;
     auto it = c->galois.find(gal_el);
     if (it != c->galois.end()) d = it->second; else CK(cudaMalloc(&d, bytes));
-    CK(cudaMemcpyAsync(d, evk, bytes, cudaMemcpyHostToDevice, c->stream));
-    launch_scale_rows(c->L(), c->T, d, c->d_key_fm, beta);   // fold 2^s into the rows the base-converted digits multiply
+    u64 *stage = nullptr;
+    CK(cudaMalloc(&stage, bytes));
+    CK(cudaMemcpyAsync(stage, evk, bytes, cudaMemcpyHostToDevice, c->stream));
+    launch_scale_rows(c->L(), c->T, stage, d, c->d_key_fm, beta);   // fold 2^s into the rows the base-converted digits multiply
     CK(cudaStreamSynchronize(c->stream));
+    cudaFree(stage);
     c->galois[gal_el] = d;
     return 0;
 }
@@ -643,9 +646,12 @@ int lmn_load_ring_switch_key(lmn_ctx *c, uint32_t logns, const uint64_t *evk, ui
     const int beta = (c->k + c->np - 1) / c->np;
     size_t bytes = (size_t)beta * 2 * (c->k + c->np) * c->n * 8;
     if (!c->d_rs_evk) CK(cudaMalloc(&c->d_rs_evk, bytes));
-    CK(cudaMemcpy(c->d_rs_evk, evk, bytes, cudaMemcpyHostToDevice));
-    launch_scale_rows(c->L(), c->T, c->d_rs_evk, c->d_key_fm, beta);
+    u64 *stage = nullptr;
+    CK(cudaMalloc(&stage, bytes));
+    CK(cudaMemcpy(stage, evk, bytes, cudaMemcpyHostToDevice));
+    launch_scale_rows(c->L(), c->T, stage, c->d_rs_evk, c->d_key_fm, beta);
     CK(cudaStreamSynchronize(c->stream));
+    cudaFree(stage);
     u64 q0 = c->q[0];
     if (!psi_small) {
         // psi_small = psi^(N/N'): read psi back from the forward table (entry bitrev(1) = N/2 holds psi)

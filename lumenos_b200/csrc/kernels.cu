@@ -155,22 +155,30 @@ void launch_mul_pt(const Launch &L, const DeviceTables &T, int level, const u64 
     k_mul_pt<<<g, bs, 0, L.stream>>>(T.mods, nl, T.logn, in, in_words, ptm0, ptm1, out0, out1, col_words, kstride);
 }
 
-// key rows (digit d, component c, modulus gm) times a per-(d, gm) constant given in Montgomery form (0 = leave the row)
-__global__ void k_scale_rows(u64 *__restrict__ evk, const ModDev *mods, const u64 *__restrict__ fm, int KP, int logn) {
+// key rows (digit d, component c, modulus gm) times a per-(d, gm) constant given in Montgomery form (0 = copy the row), out
+// of place.  For the block pipeline (log N >= 12) the words of every 2048-block are stored in the order the block kernels
+// read them: thread u of 256 owns words 8u..8u+7 and reads them as four 16-byte pairs j = 0..3, so pair (u, j) goes to
+// slot j*256 + u - a warp then reads 512 contiguous bytes per j, from global or shared memory alike.
+__host__ __device__ inline uint32_t key_slot(uint32_t i, int permute) {
+    if (!permute) return i;
+    const uint32_t e = i & 2047u, u = e >> 3, r = e & 7u;
+    return (i & ~2047u) | ((((r >> 1) * 256u + u) << 1) | (r & 1u));
+}
+__global__ void k_scale_rows(const u64 *__restrict__ in, u64 *__restrict__ out, const ModDev *mods, const u64 *__restrict__ fm, int KP,
+                             int logn, int permute) {
     const int row = blockIdx.y, gm = row % KP, d = row / (2 * KP);
     const u64 f = fm[d * KP + gm];
-    if (!f) return;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (1 << logn)) return;
     const ModDev md = mods[gm];
-    u64 *x = evk + ((size_t)row << logn);
-    x[i] = mont_mul(x[i], f, md.q, md.qinv);
+    const u64 x = in[((size_t)row << logn) + i];
+    out[((size_t)row << logn) + key_slot((uint32_t)i, permute)] = f ? mont_mul(x, f, md.q, md.qinv) : x;
 }
-void launch_scale_rows(const Launch &L, const DeviceTables &T, u64 *evk, const u64 *fm_dev, int beta) {
+void launch_scale_rows(const Launch &L, const DeviceTables &T, const u64 *in, u64 *evk, const u64 *fm_dev, int beta) {
     LaunchScope scope(L, KID_OTHER);
     int bs = T.n < 256 ? T.n : 256;
     const int KP = T.k + T.np;
-    k_scale_rows<<<dim3((T.n + bs - 1) / bs, beta * 2 * KP), bs, 0, L.stream>>>(evk, T.mods, fm_dev, KP, T.logn);
+    k_scale_rows<<<dim3((T.n + bs - 1) / bs, beta * 2 * KP), bs, 0, L.stream>>>(in, evk, T.mods, fm_dev, KP, T.logn, blk_blocks(T.logn) > 0);
 }
 
 // =====================================================================================================
@@ -432,211 +440,6 @@ __global__ void __launch_bounds__(1024) k_mac(const ModDev *mods, const ulonglon
     }
 }
 
-// (3') the same for rings of 4096*S coefficients on the radix-16 block core: one CTA of 256 threads per (target modulus,
-//      block h, job), two CTAs per SM (34 KB data + 64 KB accumulators + 4 KB twiddles each).  Thread u owns output
-//      points 16u+r of its block: the gadget MAC reads the key rows and accumulates in thread-private shared-memory
-//      slots, the last digit reduces and stores.  Only 4 warps per scheduler are resident, so every global load is
-//      issued one stage ahead of its use by hand: the twiddles of the first eight levels come from a shared-memory
-//      table, those of the last four and the key rows are prefetched into registers, the next digit streams in during
-//      the MAC.
-template <int S, int PF>
-__global__ void __launch_bounds__(R16_THREADS, 2) k_mac_r16(const ModDev *mods, const ulonglong2 *tw_fwd, const KsConsts *C,
-                                                             const KsJobs J, const u64 *__restrict__ evk) {
-    extern __shared__ u64 sm[];
-    auto LD2 = [](const ulonglong2 *q) { return (PF & 2) ? ld_pin2(q) : __ldg(q); };
-    auto LD1 = [](const u64 *q) { return (PF & 2) ? ld_pin(q) : __ldg(q); };
-    constexpr int M = R16_M;
-    constexpr int LOGN = R16_LOGM + (S == 4 ? 2 : S == 2 ? 1 : 0);
-    u64 *data = sm;
-    u64 *acc0 = sm + R16_WORDS;
-    u64 *acc1 = acc0 + M;
-    ulonglong2 *stw = reinterpret_cast<ulonglong2 *>(acc1 + M);
-    const int tix = blockIdx.x / S, h = blockIdx.x % S, job = blockIdx.y;
-    const int nq = C->nq, k = C->k, KP = k + C->np;
-    const int gm = ks_mod_index(tix, nq, k);
-    const ModDev md = mods[gm];
-    const u64 p = md.q;
-    const FwdMod fm = {p, 0 - p, md.q3};
-    const unsigned SH = S + h;
-    const ulonglong2 *tw = tw_fwd + ((size_t)gm << LOGN);
-    const unsigned u = threadIdx.x, gi = u >> 4, gj = u & 15;
-    const size_t blk = (size_t)h * M;
-    const u64 *c1 = J.col + (size_t)job * J.col_words + ((size_t)k << LOGN) + ((size_t)tix << LOGN) + blk + 16 * u;  // own limb of poly 1
-    const u64 *mu = J.mu + (size_t)job * J.mu_words + ((size_t)gm << LOGN) + blk + u;
-    u64 *o0 = J.acc + (size_t)job * J.acc_words + ((size_t)gm << LOGN) + blk + 16 * u;
-    u64 *o1 = o0 + ((size_t)KP << LOGN);
-    const int beta = C->beta;
-    // digit whose own limb this target is (copied from the NTT-domain input, DecomposeSingleNTT), or -1
-    int own = -1;
-    for (int d = 0; d < beta; d++) if (tix < nq && tix >= C->dig_start[d] && tix < C->dig_start[d] + C->dig_size[d]) own = d;
-
-    r16_fill_stw(stw, tw, SH);
-    u64 a[16];
-    auto load_digit = [&](int d, u64 (&x)[16]) {
-        if (d == own) {
-#pragma unroll
-            for (int r = 0; r < 8; r++) { const ulonglong2 v = LD2(reinterpret_cast<const ulonglong2 *>(c1) + r); x[2 * r] = v.x; x[2 * r + 1] = v.y; }
-        } else {
-            const u64 *src = mu + (((size_t)d * KP) << LOGN);
-#pragma unroll
-            for (int r = 0; r < 16; r++) x[r] = LD1(src + 256 * r);
-        }
-    };
-    load_digit(0, a);
-    __syncthreads();   // twiddle table visible
-    bool used = false; // `data` holds a previous digit that may still be read
-
-    for (int d = 0; d < beta; d++) {
-        const ulonglong2 *e0 = reinterpret_cast<const ulonglong2 *>(evk + ((((size_t)d * 2 + 0) * KP + gm) << LOGN) + blk + 16 * u);
-        const ulonglong2 *e1 = reinterpret_cast<const ulonglong2 *>(evk + ((((size_t)d * 2 + 1) * KP + gm) << LOGN) + blk + 16 * u);
-        ulonglong2 k0[3], k1[3];
-        if (d != own) {
-            r16_fwd_f(a, [&](int t, int b) { return stw[(1 << t) - 1 + b]; }, fm);
-            if (used) __syncthreads();
-            used = true;
-#pragma unroll
-            for (int r = 0; r < 16; r++) data[PAD(u + 256 * r)] = a[r];
-            ulonglong2 w2[7];
-#pragma unroll
-            for (int t = 0; t < 3; t++)
-#pragma unroll
-                for (int b = 0; b < (1 << t); b++) w2[(1 << t) - 1 + b] = LD2(&tw[((256 * SH + u) << t) + b]);
-            __syncthreads();
-#pragma unroll
-            for (int r = 0; r < 16; r++) a[r] = data[PAD(gi * 256 + gj + 16 * r)];
-            r16_fwd_f(a, [&](int t, int b) { return stw[15 + 15 * gi + (1 << t) - 1 + b]; }, fm);
-#pragma unroll
-            for (int r = 0; r < 16; r++) data[PAD(gi * 256 + gj + 16 * r)] = a[r];
-            __syncthreads();
-#pragma unroll
-            for (int r = 0; r < 16; r++) a[r] = data[PAD(16 * u + r)];
-            ulonglong2 w3[8];
-#pragma unroll
-            for (int b = 0; b < 8; b++) w3[b] = LD2(&tw[((256 * SH + u) << 3) + b]);
-            r16_fwd_f(a, [&](int t, int b) { return w2[(1 << t) - 1 + b]; }, fm, 0, 3);
-            k0[0] = LD2(e0); k1[0] = LD2(e1); k0[1] = LD2(e0 + 1); k1[1] = LD2(e1 + 1);
-            r16_fwd_f(a, [&](int t, int b) { return w3[b]; }, fm, 3, 4);
-        } else {
-            k0[0] = LD2(e0); k1[0] = LD2(e1); k0[1] = LD2(e0 + 1); k1[1] = LD2(e1 + 1);
-        }
-        u64 nx[16];
-        if ((PF & 1) && d + 1 < beta) load_digit(d + 1, nx);
-#pragma unroll
-        for (int r = 0; r < 8; r++) {
-            if (r + 2 < 8) { k0[(r + 2) % 3] = LD2(e0 + r + 2); k1[(r + 2) % 3] = LD2(e1 + r + 2); }
-            const ulonglong2 x0 = k0[r % 3], x1 = k1[r % 3];
-            u64 v0 = mont_mul_lazy(a[2 * r], x0.x, p, md.qinv), v1 = mont_mul_lazy(a[2 * r], x1.x, p, md.qinv);
-            u64 w0 = mont_mul_lazy(a[2 * r + 1], x0.y, p, md.qinv), w1 = mont_mul_lazy(a[2 * r + 1], x1.y, p, md.qinv);
-            const int ia = (2 * r) * R16_THREADS + u, ib = (2 * r + 1) * R16_THREADS + u;   // thread-private, conflict-free
-            if (d) { v0 += acc0[ia]; v1 += acc1[ia]; w0 += acc0[ib]; w1 += acc1[ib]; }
-            if (d == beta - 1) {
-                ulonglong2 r0, r1;
-                r0.x = barrett(v0, p, md.mu); r0.y = barrett(w0, p, md.mu);
-                r1.x = barrett(v1, p, md.mu); r1.y = barrett(w1, p, md.mu);
-                reinterpret_cast<ulonglong2 *>(o0)[r] = r0;
-                reinterpret_cast<ulonglong2 *>(o1)[r] = r1;
-            } else { acc0[ia] = v0; acc1[ia] = v1; acc0[ib] = w0; acc1[ib] = w1; }
-        }
-        if (d + 1 < beta) {
-            if (PF & 1) {
-#pragma unroll
-                for (int r = 0; r < 16; r++) a[r] = nx[r];
-            } else load_digit(d + 1, a);
-        }
-    }
-}
-
-// (3") register-accumulator variant on 2048-point blocks (N = 2048*S): the two accumulators of the thread's 8 output points
-//      stay in registers for all digits, shared memory holds only the block's twiddles (32 KB, loaded once per CTA) and
-//      two 17 KB transposition buffers, so three CTAs fit per SM and the transform issues no global loads.  Per digit a
-//      thread loads 8 residues (issued before the previous digit's MAC) and 8 key-row vectors (issued two passes early).
-template <int S, int OCC, int PF>
-__global__ void __launch_bounds__(RA_THREADS, OCC) k_mac_ra(const ModDev *mods, const ulonglong2 *tw_fwd, const KsConsts *C,
-                                                           const KsJobs J, const u64 *__restrict__ evk) {
-    extern __shared__ u64 sm[];
-    constexpr int M = RA_M;
-    constexpr int LOGS = S == 8 ? 3 : S == 4 ? 2 : S == 2 ? 1 : 0;
-    constexpr int LOGN = RA_LOGM + LOGS;
-    ulonglong2 *stw = reinterpret_cast<ulonglong2 *>(sm);
-    u64 *buf0 = sm + 2 * RA_M, *buf1 = buf0 + RA_WORDS;
-    const int tix = blockIdx.x / S, h = blockIdx.x % S, job = blockIdx.y;
-    const int nq = C->nq, k = C->k, KP = k + C->np;
-    const int gm = ks_mod_index(tix, nq, k);
-    const ModDev md = mods[gm];
-    const u64 p = md.q;
-    const FwdMod fm = {p, 0 - p, md.q3};
-    const unsigned u = threadIdx.x;
-    const size_t blk = (size_t)h * M;
-    const ulonglong2 *c1 = reinterpret_cast<const ulonglong2 *>(J.col + (size_t)job * J.col_words + ((size_t)(k + tix) << LOGN) + blk + 8 * u);
-    const u64 *mu = J.mu + (size_t)job * J.mu_words + ((size_t)gm << LOGN) + blk + u;
-    const int beta = C->beta;
-    int own = -1;   // digit whose own limb this target is (copied from the NTT-domain input, DecomposeSingleNTT)
-    for (int d = 0; d < beta; d++) if (tix < nq && tix >= C->dig_start[d] && tix < C->dig_start[d] + C->dig_size[d]) own = d;
-    ra_fill_stw(stw, tw_fwd + ((size_t)gm << LOGN), S + h);
-
-    auto load_digit = [&](int d, u64 (&x)[8]) {
-        if (d == own) {
-#pragma unroll
-            for (int r = 0; r < 4; r++) { const ulonglong2 v = __ldg(c1 + r); x[2 * r] = v.x; x[2 * r + 1] = v.y; }
-        } else {
-            const u64 *src = mu + (((size_t)d * KP) << LOGN);
-#pragma unroll
-            for (int r = 0; r < 8; r++) x[r] = __ldg(src + 256 * r);
-        }
-    };
-    u64 acc0[8], acc1[8], a[8];
-#pragma unroll
-    for (int r = 0; r < 8; r++) { acc0[r] = 0; acc1[r] = 0; }
-    load_digit(0, a);
-    __syncthreads();   // twiddle table visible
-    int flip = 0;
-    for (int d = 0; d < beta; d++) {
-        const ulonglong2 *e0 = reinterpret_cast<const ulonglong2 *>(evk + ((((size_t)d * 2 + 0) * KP + gm) << LOGN) + blk + 8 * u);
-        const ulonglong2 *e1 = reinterpret_cast<const ulonglong2 *>(evk + ((((size_t)d * 2 + 1) * KP + gm) << LOGN) + blk + 8 * u);
-        // key rows: component 0 is requested before the transform, component 1 before its third pass; both are plain loads
-        // pinned in front of the next barrier (ld_pin2), a full pass or more ahead of the MAC that consumes them
-        ulonglong2 k0[4], k1[4];
-#pragma unroll
-        for (int r = 0; r < 4; r++) k0[r] = ld_pin2(e0 + r);
-        auto load_k1 = [&]() {
-#pragma unroll
-            for (int r = 0; r < 4; r++) k1[r] = ld_pin2(e1 + r);
-        };
-        if (d != own) {
-            if (PF & 2) ntt2048_fwd(a, flip ? buf1 : buf0, stw, fm, load_k1);
-            else { ntt2048_fwd(a, flip ? buf1 : buf0, stw, fm, []() {}); load_k1(); }
-            flip ^= 1;
-        } else load_k1();
-        u64 nx[8];
-        if ((PF & 1) && d + 1 < beta) load_digit(d + 1, nx);
-#pragma unroll
-        for (int r = 0; r < 4; r++) {
-            acc0[2 * r] += mont_mul_lazy(a[2 * r], k0[r].x, p, md.qinv);
-            acc0[2 * r + 1] += mont_mul_lazy(a[2 * r + 1], k0[r].y, p, md.qinv);
-        }
-#pragma unroll
-        for (int r = 0; r < 4; r++) {
-            acc1[2 * r] += mont_mul_lazy(a[2 * r], k1[r].x, p, md.qinv);
-            acc1[2 * r + 1] += mont_mul_lazy(a[2 * r + 1], k1[r].y, p, md.qinv);
-        }
-        if (d + 1 < beta) {
-            if (PF & 1) {
-#pragma unroll
-                for (int r = 0; r < 8; r++) a[r] = nx[r];
-            } else load_digit(d + 1, a);
-        }
-    }
-    ulonglong2 *o0 = reinterpret_cast<ulonglong2 *>(J.acc + (size_t)job * J.acc_words + ((size_t)gm << LOGN) + blk + 8 * u);
-    ulonglong2 *o1 = o0 + ((size_t)KP << (LOGN - 1));
-#pragma unroll
-    for (int r = 0; r < 4; r++) {
-        ulonglong2 r0, r1;
-        r0.x = barrett(acc0[2 * r], p, md.mu); r0.y = barrett(acc0[2 * r + 1], p, md.mu);
-        r1.x = barrett(acc1[2 * r], p, md.mu); r1.y = barrett(acc1[2 * r + 1], p, md.mu);
-        o0[r] = r0; o1[r] = r1;
-    }
-}
-
 // (4) P limbs of the accumulators out of the NTT domain, centred by P/2 and premultiplied by (P/p_j)^-1
 //     (ModDownQPtoQNTT: INTT of the P part, ModUpPtoQ's AddScalar(PHalf) and reconstructRNS's y_j)
 template <int LOGN>
@@ -713,11 +516,7 @@ __global__ void __launch_bounds__(1024) k_down(const ModDev *mods, const ulonglo
 }
 
 const char *kernels_blk_init();
-static bool use_blk_pipeline(int logn) {
-    static const bool off = getenv("LMN_BLK") && !strcmp(getenv("LMN_BLK"), "0");   // A/B switch: whole-limb kernels
-    return !off && blk_blocks(logn) > 0;
-}
-static void launch_mac_ra(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch, const KsJobs &J, const u64 *evk);
+static bool use_blk_pipeline(int logn) { return blk_blocks(logn) > 0; }   // log N >= 12; smaller rings: whole-limb kernels
 
 // block pipeline (kernels_blk.cu): six launches per rotation, out of place col -> col2
 static void rotate_accumulate_blk(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch, KsJobs &J,
@@ -728,7 +527,7 @@ static void rotate_accumulate_blk(const Launch &L, const DeviceTables &T, const 
     for (int i = 0; i < nq; i++) { A.mod[i] = i; A.src_limb[i] = (uint32_t)(k + i); A.dst_limb[i] = (uint32_t)i; }
     launch_blk_intt(L, T, A, J.jobs, KID_INTT_C1);
     launch_modup_blk(L, T, Cd, Ch, J);
-    launch_mac_ra(L, T, Cd, Ch, J, evk);
+    launch_mac_blk(L, T, Cd, Ch, J, evk);
     BlkSlots B;
     B.src = J.acc; B.src_job_words = J.acc_words; B.dst = J.acc; B.dst_job_words = J.acc_words; B.nslots = 2 * np;
     for (int c = 0; c < 2; c++)
@@ -747,43 +546,17 @@ void launch_rotate_accumulate(const Launch &L, const DeviceTables &T, const KsCo
     const int nt_full = ntt_threads(N);
     { LaunchScope scope(L, KID_INTT_C1);
     LMN_DISPATCH_LOGN(T.logn, k_intt_c1<LG><<<dim3(nq, jobs), nt_full, sm_full, L.stream>>>(T.mods, T.tw_inv, Cd, J, Ch.k)); }
-    // block cores: log N >= 12 runs on 2048-point blocks with register accumulators (LMN_MAC_CORE=r16: 4096-point blocks)
-    static const bool use_r16 = getenv("LMN_MAC_CORE") && !strcmp(getenv("LMN_MAC_CORE"), "r16");
-    const int SB = T.logn < R16_LOGM ? 0 : use_r16 ? N >> R16_LOGM : N >> RA_LOGM;   // blocks per limb (0: whole-limb kernels)
     {
         LaunchScope scope(L, KID_VFIX);
-        const int Sm = SB ? SB : (T.logn >= 14 ? 2 : 1);
-        const int M = N / Sm;
-        const int bs = M < 256 ? M : 256;
+        const int bs = N < 256 ? N : 256;
         const int beta_max = (Ch.k + np - 1) / np;
-        const dim3 g((M + bs - 1) / bs, Ch.beta, jobs);
-        if (Sm == 8) k_modup<8><<<g, bs, 0, L.stream>>>(T.mods, T.tw_fwd, Cd, J, T.logn, beta_max);
-        else if (Sm == 4) k_modup<4><<<g, bs, 0, L.stream>>>(T.mods, T.tw_fwd, Cd, J, T.logn, beta_max);
-        else if (Sm == 2) k_modup<2><<<g, bs, 0, L.stream>>>(T.mods, T.tw_fwd, Cd, J, T.logn, beta_max);
-        else k_modup<1><<<g, bs, 0, L.stream>>>(T.mods, T.tw_fwd, Cd, J, T.logn, beta_max);
+        k_modup<1><<<dim3((N + bs - 1) / bs, Ch.beta, jobs), bs, 0, L.stream>>>(T.mods, T.tw_fwd, Cd, J, T.logn, beta_max);
     }
-    if (SB && !use_r16) launch_mac_ra(L, T, Cd, Ch, J, evk);
-    else { LaunchScope scope(L, KID_MAC);
-    if (SB) {
-        const int S16 = SB;
-        const size_t smm = ((size_t)R16_WORDS + 2 * (size_t)R16_M + 2 * R16_STW) * 8;
-        const dim3 g((nq + np) * S16, jobs);
-        static const int pf = getenv("LMN_MAC_PF") ? atoi(getenv("LMN_MAC_PF")) : 0;
-#define MACR16(SS) do { if (pf == 1) k_mac_r16<SS, 1><<<g, R16_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk); \
-            else if (pf == 2) k_mac_r16<SS, 2><<<g, R16_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk); \
-            else if (pf == 3) k_mac_r16<SS, 3><<<g, R16_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk); \
-            else k_mac_r16<SS, 0><<<g, R16_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk); } while (0)
-        if (S16 == 4) MACR16(4); else if (S16 == 2) MACR16(2); else MACR16(1);
-#undef MACR16
-    } else if (T.logn <= 13) {
+    {
+        LaunchScope scope(L, KID_MAC);
         const size_t smm = ((size_t)padded_words(N) + 2 * (size_t)N) * 8;
-        LMN_DISPATCH_LOGN(T.logn, k_mac<(LG <= 13 ? LG : 13), 1><<<dim3(nq + np, jobs), nt_full, smm, L.stream>>>(
-                                      T.mods, T.tw_fwd, Cd, J, evk));
-    } else {
-        const int M = N / 2;
-        const size_t smm = ((size_t)padded_words(M) + 2 * (size_t)M) * 8;
-        k_mac<13, 2><<<dim3((nq + np) * 2, jobs), ntt_threads(M), smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk);
-    } }
+        LMN_DISPATCH_LOGN(T.logn, k_mac<(LG <= 13 ? LG : 13), 1><<<dim3(nq + np, jobs), nt_full, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk));
+    }
     { LaunchScope scope(L, KID_PINTT);
     LMN_DISPATCH_LOGN(T.logn, k_pintt<LG><<<dim3(np, 2, jobs), nt_full, sm_full, L.stream>>>(T.mods, T.tw_inv, Cd, J)); }
     if (np > 1) {
@@ -794,21 +567,6 @@ void launch_rotate_accumulate(const Launch &L, const DeviceTables &T, const KsCo
     { LaunchScope scope(L, KID_DOWN);
     LMN_DISPATCH_LOGN(T.logn, k_down<LG><<<dim3(nq, 2, jobs), nt_full, sm_full, L.stream>>>(T.mods, T.tw_fwd, Cd, J, gal_el,
                                                                                         gal_el == 0 ? 1 : 0)); }
-}
-
-static void launch_mac_ra(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch, const KsJobs &J, const u64 *evk) {
-    LaunchScope scope(L, KID_MAC);
-    const int SB = T.n >> RA_LOGM;
-    const size_t smm = (2 * (size_t)RA_M + 2 * (size_t)RA_WORDS) * 8;
-    const dim3 g((Ch.nq + Ch.np) * SB, J.jobs);
-    static const int var = getenv("LMN_MAC_VAR") ? atoi(getenv("LMN_MAC_VAR")) : 0;   // experiment switch: occupancy x prefetch
-#define MACRA(SS) do { \
-        if (var == 1) k_mac_ra<SS, 3, 3><<<g, RA_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk); \
-        else if (var == 2) k_mac_ra<SS, 3, 2><<<g, RA_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk); \
-        else if (var == 3) k_mac_ra<SS, 3, 0><<<g, RA_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk); \
-        else k_mac_ra<SS, 2, 3><<<g, RA_THREADS, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk); } while (0)
-    if (SB == 8) MACRA(8); else if (SB == 4) MACRA(4); else MACRA(2);
-#undef MACRA
 }
 
 void launch_keyswitch_level0(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch,
@@ -989,19 +747,14 @@ const char *kernels_init() {
     SETSM(k_rs_intt<LG>); SETSM(k_rs_apply<LG>);
     SET_LOGN(6) SET_LOGN(8) SET_LOGN(10) SET_LOGN(12) SET_LOGN(13) SET_LOGN(14)
     SETSM((k_mac<6, 1>)); SETSM((k_mac<8, 1>)); SETSM((k_mac<10, 1>)); SETSM((k_mac<12, 1>)); SETSM((k_mac<13, 1>));
-    SETSM((k_mac<13, 2>));
-#define SETRA(SS) SETSM((k_mac_ra<SS, 2, 3>)); SETSM((k_mac_ra<SS, 3, 3>)); SETSM((k_mac_ra<SS, 3, 2>)); SETSM((k_mac_ra<SS, 3, 0>));
-    SETRA(2) SETRA(4) SETRA(8)
-#undef SETRA
-#define SETMAC(SS) SETSM((k_mac_r16<SS, 0>)); SETSM((k_mac_r16<SS, 1>)); SETSM((k_mac_r16<SS, 2>)); SETSM((k_mac_r16<SS, 3>));
-    SETMAC(1) SETMAC(2) SETMAC(4)
-#undef SETMAC
     SETSM(k_encode_pass);
     SETSM((k_ring_decimate<12, 10>)); SETSM((k_ring_decimate<13, 10>)); SETSM((k_ring_decimate<14, 10>));
     SETSM((k_ring_decimate<8, 6>)); SETSM((k_ring_decimate<10, 6>)); SETSM((k_ring_decimate<10, 8>)); SETSM((k_ring_decimate<12, 8>));
 #undef SET_LOGN
 #undef SETSM
-    if (e == cudaSuccess) return kernels_blk_init();
+    if (e != cudaSuccess) return cudaGetErrorString(e);
+    if (const char *m = kernels_blk_init()) return m;
+    return kernels_mac_init();
     return cudaGetErrorString(e);
 }
 

@@ -105,8 +105,9 @@ void launch_prep_pt(const Launch &L, const DeviceTables &T, int level, const u64
 // out_x[job] = in[col] * ptm_x  (x = 0,1; ptm1 may be null); in: cts with stride in_words; out: job cols with stride col_words
 void launch_mul_pt(const Launch &L, const DeviceTables &T, int level, const u64 *in, uint64_t in_words, int ncols,
                    const u64 *ptm0, const u64 *ptm1, u64 *out0, u64 *out1, uint64_t col_words);
-// evk rows (d, c, gm) *= fm[d][gm] (Montgomery-form factors, 0 = skip); beta digits
-void launch_scale_rows(const Launch &L, const DeviceTables &T, u64 *evk, const u64 *fm_dev, int beta);
+// evk = in with rows (d, c, gm) times fm[d][gm] (Montgomery-form factors, 0 = copy); beta digits.  Out of place; for
+// log N >= 12 the words of every 2048-block are stored in the block kernels' read order (key_slot in kernels.cu)
+void launch_scale_rows(const Launch &L, const DeviceTables &T, const u64 *in, u64 *evk, const u64 *fm_dev, int beta);
 void launch_limb_ntt(const Launch &L, const DeviceTables &T, int mod_idx, u64 *limb, int inverse);
 
 // ---- Encode ----
@@ -163,6 +164,9 @@ void launch_down_blk(const Launch &L, const DeviceTables &T, const KsConsts *Cd,
 // rescale step from `level`: acc slots c (raw block INTT of limb `level`) -> mu[c][i], then block NTT + apply in place
 void launch_rs_pre(const Launch &L, const DeviceTables &T, const RescaleConsts *Rd, int level, const KsJobs &J);
 void launch_rs_blk(const Launch &L, const DeviceTables &T, const RescaleConsts *Rd, int level, const KsJobs &J);
+// block NTT + gadget MAC of the block pipeline (kernels_mac.cu)
+void launch_mac_blk(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch, const KsJobs &J, const u64 *evk);
+const char *kernels_mac_init();
 
 const char *kernels_init();  // sets dynamic shared memory attributes; returns nullptr or error string
 

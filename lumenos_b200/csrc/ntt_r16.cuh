@@ -216,10 +216,12 @@ __device__ __forceinline__ void r8_fwd_f(u64 (&a)[8], F tw_of, const FwdMod &m) 
 }
 // forward transform of one 2048-point block: in a[r] = point u + 256 r, out a[r] = point 8u + r (lazy, entry bound + 33 q).
 // `s` = RA_WORDS words; the caller guarantees the previous readers of `s` are done (double buffer or barrier).
-template <class Hook>
-__device__ __forceinline__ void ntt2048_fwd(u64 (&a)[8], u64 *s, const ulonglong2 *stw, const FwdMod &m, Hook before_pass_c) {
+// Hook0 runs after the first register stage and before the first store to `s` (a barrier there makes one buffer enough).
+template <class Hook0, class Hook>
+__device__ __forceinline__ void ntt2048_fwd(u64 (&a)[8], u64 *s, const ulonglong2 *stw, const FwdMod &m, Hook0 before_store_a, Hook before_pass_c) {
     const unsigned u = threadIdx.x;
     r8_fwd_f(a, [&](int t, int b) { return stw[(1 << t) + b]; }, m);                       // levels 0-2
+    before_store_a();
 #pragma unroll
     for (int r = 0; r < 8; r++) s[PAD(u + 256 * r)] = a[r];
     __syncthreads();
@@ -250,6 +252,10 @@ __device__ __forceinline__ void ntt2048_fwd(u64 (&a)[8], u64 *s, const ulonglong
         const ulonglong2 w = stw[1024 + b * 256 + u];
         bfly_ct3(a[2 * b], a[2 * b + 1], w, m);
     }
+}
+template <class Hook>
+__device__ __forceinline__ void ntt2048_fwd(u64 (&a)[8], u64 *s, const ulonglong2 *stw, const FwdMod &m, Hook before_pass_c) {
+    ntt2048_fwd(a, s, stw, m, []() {}, before_pass_c);
 }
 
 // ---------------------------------------------------------------------------------------------------

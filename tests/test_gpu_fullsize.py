@@ -82,7 +82,7 @@ def test_encode_full_size_sampled_lanes_and_linearity(logN, cols, k):
     be.Close()
 
 
-@pytest.mark.parametrize("logN,rows,k", [(12, 4096, 11), (14, 16384, 12)])
+@pytest.mark.parametrize("logN,rows,k", [(12, 4096, 11), (13, 8192, 12), (14, 16384, 12)])
 def test_prove_full_ring_sampled_columns(logN, rows, k):
     """inner products + query rescale at the full ring size and chain length of configs B / D (columns are independent,
     so 48 columns exercise exactly the per-column work of the full matrix)"""
@@ -117,6 +117,12 @@ def test_prove_full_ring_sampled_columns(logN, rows, k):
         _capi.check(lib.lmn_inner_product2(be.ctx, sM.h, rpt.ctypes.data_as(vp), bpt.ctypes.data_as(vp), rows, mr.h, mz.h))
         outs[batch] = (mr.download(), mz.download())
     assert np.array_equal(outs[64][0], outs[10][0]) and np.array_equal(outs[64][1], outs[10][1]), "result depends on the batch size"
+    # the kernels overlap asynchronous copies with compute: repeated runs must reproduce the result bit for bit
+    be.SetBatch(64)
+    for rep in range(4):
+        mr, mz = be.NewStore(cols, 1), be.NewStore(cols, 1)
+        _capi.check(lib.lmn_inner_product2(be.ctx, sM.h, rpt.ctypes.data_as(vp), bpt.ctypes.data_as(vp), rows, mr.h, mz.h))
+        assert np.array_equal(mr.download(), outs[64][0]) and np.array_equal(mz.download(), outs[64][1]), "run %d differs from the first" % rep
     Mh = M.cpu().numpy().astype(np.uint64)
     for j in (0, 17, 47):
         wr, _ = P.inner_sum_eval_column(Mh[j], rpt, rows, gal, evks)

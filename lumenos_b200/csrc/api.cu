@@ -31,7 +31,7 @@ struct lmn_ctx {
     bool scalar_centered = true, round_nearest = true, rowswap_last = true;
     cudaStream_t own_stream = nullptr, stream = nullptr;
     ModDev *d_mods = nullptr;
-    ulonglong2 *d_twf = nullptr, *d_twi = nullptr;
+    ulonglong2 *d_twf = nullptr, *d_twi = nullptr, *d_twbf = nullptr, *d_twbi = nullptr;
     DeviceTables T{};
     std::map<int, std::pair<KsConsts, KsConsts *>> ks;      // per level
     std::map<int, RescaleConsts *> rs;                      // per level
@@ -196,6 +196,7 @@ static void build_ks_consts(const lmn_ctx *c, int level, KsConsts &K) {
         K.md_neg[i] = v ? qi - v : 0;
         u64 pinv = h_invmod(Pm, qi);
         K.pinv_w[i] = pinv; K.pinv_ws[i] = h_shoup(pinv, qi);
+        K.pmod_w[i] = Pm; K.pmod_ws[i] = h_shoup(Pm, qi);
     }
 }
 
@@ -315,7 +316,14 @@ int lmn_ctx_create(const lmn_params *P, int device, lmn_ctx **out) {
     if (e == cudaSuccess) e = cudaMemcpy(c->d_twi, twi.data(), sizeof(ulonglong2) * KP * N, cudaMemcpyHostToDevice);
     if (e != cudaSuccess) { int rc = fail(LMN_ERR_CUDA, std::string("context setup: ") + cudaGetErrorString(e)); lmn_ctx_destroy(c); return rc; }
     c->stream = c->own_stream;
-    c->T = DeviceTables{c->logn, c->n, c->k, c->np, c->d_mods, c->d_twf, c->d_twi};
+    c->T = DeviceTables{c->logn, c->n, c->k, c->np, c->d_mods, c->d_twf, c->d_twi, nullptr, nullptr};
+    if (blk_blocks(c->logn)) {   // per-block twiddle tables of the 2048-point block pipeline (same words as d_twf / d_twi, block order)
+        e = cudaMalloc(&c->d_twbf, sizeof(ulonglong2) * KP * N);
+        if (e == cudaSuccess) e = cudaMalloc(&c->d_twbi, sizeof(ulonglong2) * KP * N);
+        if (e == cudaSuccess) { launch_build_blk_tables(c->stream, c->T, c->d_twbf, c->d_twbi); e = cudaStreamSynchronize(c->stream); }
+        if (e != cudaSuccess) { int rc = fail(LMN_ERR_CUDA, std::string("context setup: ") + cudaGetErrorString(e)); lmn_ctx_destroy(c); return rc; }
+        c->T.twb_fwd = c->d_twbf; c->T.twb_inv = c->d_twbi;
+    }
     build_key_scale(c);
     {
         const int beta = (c->k + c->np - 1) / c->np;
@@ -343,7 +351,7 @@ void lmn_ctx_destroy(lmn_ctx *c) {
     for (auto &kv : c->ks) cudaFree(kv.second.second);
     for (auto &kv : c->rs) cudaFree(kv.second);
     for (auto &kv : c->galois) cudaFree(kv.second);
-    cudaFree(c->d_mods); cudaFree(c->d_twf); cudaFree(c->d_twi); cudaFree(c->ws_pt); cudaFree(c->ws_scalar);
+    cudaFree(c->d_mods); cudaFree(c->d_twf); cudaFree(c->d_twi); cudaFree(c->d_twbf); cudaFree(c->d_twbi); cudaFree(c->ws_pt); cudaFree(c->ws_scalar);
     cudaFree(c->ws_col); cudaFree(c->ws_col2); cudaFree(c->ws_y); cudaFree(c->ws_acc); cudaFree(c->ws_idx);
     cudaFree(c->d_rs_evk); cudaFree(c->d_small_mod); cudaFree(c->d_small_tw); cudaFree(c->d_key_fm); cudaFree(c->ws_mu);
     for (int i = 0; i < KID_COUNT; i++) for (auto &sp : c->prof.spans[i]) { cudaEventDestroy(sp.first); cudaEventDestroy(sp.second); }

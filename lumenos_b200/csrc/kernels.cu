@@ -5,7 +5,7 @@
 //                    (fhe/ligero.go:319-325 = MulNew + InnerSum; lattigo DecomposeNTT / GadgetProduct / ModDown)
 //   Rescale          k_rs_intt, k_rs_apply              integer-bound (fhe/ligero.go:331-333, 271-273)
 #include "kernels.cuh"
-#include "ntt_r16.cuh"
+#include "ntt_blk.cuh"
 
 #include <cstdio>
 #include <cstdlib>

@@ -34,6 +34,7 @@ struct KsConsts {
     u64 md_c[MAX_LIMBS][MAX_P];                              // (P/p_a mod q_i) * 2^64 mod q_i
     u64 md_neg[MAX_LIMBS];                                   // -((np-1) P + Phalf) mod q_i
     u64 pinv_w[MAX_LIMBS], pinv_ws[MAX_LIMBS];               // P^-1 mod q_i
+    u64 pmod_w[MAX_LIMBS], pmod_ws[MAX_LIMBS];               // P mod q_i (block pipeline: "+ c0" enters as c0 P before ModDown)
 };
 // target index tix in [0, nq+np): modulus index in the global table
 __host__ __device__ inline int ks_mod_index(int tix, int nq, int k) { return tix < nq ? tix : k + (tix - nq); }
@@ -49,7 +50,10 @@ struct DeviceTables {
     const ModDev *mods;              // [k+np (+1 small-ring modulus)]
     const ulonglong2 *tw_fwd;        // [k+np][N]
     const ulonglong2 *tw_inv;        // [k+np][N]
+    const ulonglong2 *twb_fwd;       // log N >= 12: [k+np][S][2048] per-block tables in shared-memory layout (ntt_blk.cuh)
+    const ulonglong2 *twb_inv;
 };
+void launch_build_blk_tables(cudaStream_t stream, const DeviceTables &T, ulonglong2 *fwd, ulonglong2 *inv);
 
 struct EncPassArgs {
     const ModDev *mods;

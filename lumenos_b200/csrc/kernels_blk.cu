@@ -2,7 +2,7 @@
 // <-> log N = 12, 13, 14; configs A/B, C, D of BASELINE.json).
 //
 // Every length-N transform is S independent 2048-point block transforms (256 threads x 8 register-resident residues, all
-// of the block's twiddles in shared memory, ntt_r16.cuh) plus log2(S) levels that couple the blocks.  The coupling levels
+// of the block's twiddles in shared memory, ntt_blk.cuh) plus log2(S) levels that couple the blocks.  The coupling levels
 // are pointwise over the S points n + r*M of a limb, so they live in the elementwise kernels that sit between an inverse
 // and a forward transform anyway (base conversions):
 //
@@ -17,51 +17,80 @@
 // ring.DivRoundByLastModulusNTT as called from fhe/ligero.go:325 (InnerSum) and :331-333, :271-273 (Rescale); restated
 // in oracle/lumenos_oracle.c.
 #include "kernels.cuh"
-#include "ntt_r16.cuh"
+#include "ntt_blk.cuh"
+#include "tma.cuh"
 
 namespace lmn {
 
-constexpr size_t BLK_SMEM = (2 * (size_t)RA_M + 2 * (size_t)RA_WORDS) * 8;   // twiddle table + two transposition buffers
+constexpr size_t BLK_INTT_SMEM = (2 * (size_t)RA_M + (size_t)RA_WORDS + (size_t)RA_M + 2) * 8;       // twiddles, buffer, one landing block, barriers
+constexpr size_t BLK_FWD_SMEM = (2 * (size_t)RA_M + (size_t)RA_WORDS + 3 * (size_t)RA_M + 4) * 8;    // twiddles, buffer, three landing blocks, barriers
+constexpr unsigned BLK_BYTES = RA_M * 8;
 template <int S> struct LogS { static constexpr int v = S == 8 ? 3 : S == 4 ? 2 : S == 2 ? 1 : 0; };
+
+// block twiddle tables in the shared-memory layout of ra_fill_stw, one 32 KB table per (modulus, block): a CTA fetches its
+// table with one bulk copy.  grid (S, moduli)
+__global__ void k_build_blk_tw(const ulonglong2 *__restrict__ tw, ulonglong2 *__restrict__ out, int logn, int S) {
+    const int h = blockIdx.x, gm = blockIdx.y;
+    ulonglong2 *o = out + (((size_t)gm * S + h) << RA_LOGM);
+    if (threadIdx.x == 0) o[0] = make_ulonglong2(0, 0);
+    ra_fill_stw(o, tw + ((size_t)gm << logn), (unsigned)(S + h));
+}
+void launch_build_blk_tables(cudaStream_t stream, const DeviceTables &T, ulonglong2 *fwd, ulonglong2 *inv) {
+    const int S = blk_blocks(T.logn);
+    k_build_blk_tw<<<dim3(S, T.k + T.np), RA_THREADS, 0, stream>>>(T.tw_fwd, fwd, T.logn, S);
+    k_build_blk_tw<<<dim3(S, T.k + T.np), RA_THREADS, 0, stream>>>(T.tw_inv, inv, T.logn, S);
+}
 
 // ---------------------------------------------------------------------------------------------------
 // raw block INTT of `nslots` limbs of `jobs` jobs.  grid (S*nslots, ceil(jobs/jb)); one CTA owns block h of slot s for jb
-// consecutive jobs (the 32 KB twiddle table is filled once).  In-place use (src == dst) is safe: a CTA reads its whole
-// block of a job before it writes it.
+// consecutive jobs.  The block's twiddle table and every job's 16 KB block arrive by bulk copies (TMA), the next job's while
+// the current one is transformed.  In-place use (src == dst) is safe: the block of a job has landed in shared memory
+// before the CTA writes it, and other jobs' blocks are other addresses.
 // ---------------------------------------------------------------------------------------------------
 template <int S>
-__global__ void __launch_bounds__(RA_THREADS, 3) k_blk_intt(const ModDev *mods, const ulonglong2 *tw_inv, const BlkSlots A, int jobs, int jb) {
-    extern __shared__ u64 sm[];
+__global__ void __launch_bounds__(RA_THREADS, 3) k_blk_intt(const ModDev *mods, const ulonglong2 *twb_inv, const BlkSlots A, int jobs, int jb) {
+    extern __shared__ __align__(16) u64 sm[];
     constexpr int LOGN = RA_LOGM + LogS<S>::v;
     ulonglong2 *stw = reinterpret_cast<ulonglong2 *>(sm);
-    u64 *buf0 = sm + 2 * RA_M, *buf1 = buf0 + RA_WORDS;
+    u64 *buf = sm + 2 * RA_M;
+    u64 *land = buf + RA_WORDS;       // the job's block, natural order
+    u64 *bars = land + RA_M;          // [0] block landed, [1] table landed
     const int slot = blockIdx.x / S, h = blockIdx.x % S;
     const int gm = A.mod[slot];
     const ModDev md = mods[gm];
     const FwdMod fm = {md.q, 0 - md.q, md.q3};
-    ra_fill_stw(stw, tw_inv + ((size_t)gm << LOGN), S + h);
     const unsigned u = threadIdx.x;
-    const size_t soff = ((size_t)A.src_limb[slot] << LOGN) + (size_t)h * RA_M + 8 * u;
+    const size_t soff = ((size_t)A.src_limb[slot] << LOGN) + (size_t)h * RA_M;
     const size_t doff = ((size_t)A.dst_limb[slot] << LOGN) + (size_t)h * RA_M + u;
     const int j0 = blockIdx.y * jb, j1 = min(jobs, j0 + jb);
-    u64 a[8];
-    auto load = [&](int job) {
-        const ulonglong2 *p = reinterpret_cast<const ulonglong2 *>(A.src + (size_t)job * A.src_job_words + soff);
-#pragma unroll
-        for (int r = 0; r < 4; r++) { const ulonglong2 v = p[r]; a[2 * r] = v.x; a[2 * r + 1] = v.y; }
-    };
-    load(j0);
-    __syncthreads();   // twiddle table visible
-    int flip = 0;
+    if (u == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init_fence(); }
+    __syncthreads();
+    if (u == 0) {
+        mbar_expect_tx(&bars[1], 2 * BLK_BYTES);
+        bulk_g2s(stw, twb_inv + (((size_t)gm * S + h) << RA_LOGM), 2 * BLK_BYTES, &bars[1]);
+        mbar_expect_tx(&bars[0], BLK_BYTES);
+        bulk_g2s(land, A.src + (size_t)j0 * A.src_job_words + soff, BLK_BYTES, &bars[0]);
+    }
+    mbar_wait(&bars[1], 0);
     for (int job = j0; job < j1; job++) {
-        ntt2048_inv(a, flip ? buf1 : buf0, stw, fm);
-        flip ^= 1;
+        u64 a[8];
+        mbar_wait(&bars[0], (job - j0) & 1);
+#pragma unroll
+        for (int r = 0; r < 4; r++) { const ulonglong2 v = reinterpret_cast<const ulonglong2 *>(land)[4 * u + r]; a[2 * r] = v.x; a[2 * r + 1] = v.y; }
+        ntt2048_inv(a, buf, stw, fm, [&]() {
+            release_smem_to_async_proxy();
+            __syncthreads();   // every thread holds its residues (consumed by the first butterflies) and is past the previous job's last pass
+            if (u == 0 && job + 1 < j1) {
+                mbar_expect_tx(&bars[0], BLK_BYTES);
+                bulk_g2s(land, A.src + (size_t)(job + 1) * A.src_job_words + soff, BLK_BYTES, &bars[0]);
+            }
+        });
         u64 *o = A.dst + (size_t)job * A.dst_job_words + doff;
 #pragma unroll
         for (int r = 0; r < 8; r++) o[256 * r] = a[r];
-        if (job + 1 < j1) load(job + 1);
     }
 }
+
 
 // ---------------------------------------------------------------------------------------------------
 // digit d of y (raw block INTTs of c1) -> every other modulus (lattigo DecomposeAndSplit: reconstructRNS + multSum).
@@ -280,27 +309,33 @@ __global__ void __launch_bounds__(256) k_rs_pre(const ModDev *mods, const ulongl
 
 // ---------------------------------------------------------------------------------------------------
 // block NTT of mu[c][i] + epilogue.  grid (S*nlimbs, 2, ceil(jobs/jb)); one CTA owns block h of limb i of poly c for jb jobs.
-//   MODE 0  u = (acc - ext) P^-1 (+ c0), then AutomorphismHoisted + Add: col2 = col + pi(u).  The permutation
-//           out[n] = in[index(n)] of the NTT domain maps blocks onto blocks (the top log2(S) bits of index(n) depend only
-//           on those of n), so the CTA stages its block of u in shared memory and gathers from it while it streams the
-//           one destination block of col -> col2 (coalesced).  Out of place: other CTAs read col block-wise for "+ c0".
+//   MODE 0  u = (acc - ext) P^-1 (k_mac has already added c0 P to acc_0), then AutomorphismHoisted + Add: col2 = col + pi(u).
+//           The permutation out[n] = in[index(n)] of the NTT domain maps blocks onto blocks (the top log2(S) bits of
+//           index(n) depend only on those of n), so the CTA stages its block of u in shared memory and gathers from it
+//           while it adds the one destination block of col and stores it to col2 (coalesced, out of place).
 //   MODE 1  col2 = u  (no automorphism: the ring-switch key switch)
 //   MODE 2  Rescale: col_i = (col_i - ext) q_l^-1, in place
+// All operands are 16 KB blocks that arrive by bulk copies: the transform's input of job j+1, and the epilogue's operands of
+// job j (acc block; destination block of col), requested right after the one barrier of job j that proves the landing
+// buffers free, so they land while the CTA transforms.
 // ---------------------------------------------------------------------------------------------------
 template <int S, int MODE>
-__global__ void __launch_bounds__(RA_THREADS, 3) k_blk_fwd(const ModDev *mods, const ulonglong2 *tw_fwd, const KsConsts *C,
+__global__ void __launch_bounds__(RA_THREADS, 2) k_blk_fwd(const ModDev *mods, const ulonglong2 *twb_fwd, const KsConsts *C,
                                                             const RescaleConsts *R, const KsJobs J, uint32_t gal_el, int nlimbs,
                                                             int k, int np, int jobs, int jb) {
-    extern __shared__ u64 sm[];
+    extern __shared__ __align__(16) u64 sm[];
     constexpr int LOGN = RA_LOGM + LogS<S>::v;
     constexpr int M = RA_M;
     ulonglong2 *stw = reinterpret_cast<ulonglong2 *>(sm);
-    u64 *buf0 = sm + 2 * RA_M, *buf1 = buf0 + RA_WORDS;
+    u64 *buf = sm + 2 * RA_M;
+    u64 *landD = buf + RA_WORDS;      // transform input of the next job (words u + 256 r)
+    u64 *landA = landD + RA_M;        // acc block (MODE 2: the col block), natural order
+    u64 *landX = landA + RA_M;        // MODE 0: destination block of col, natural order
+    u64 *bars = landX + RA_M;         // [0] input landed, [1] epilogue operands landed, [2] table landed
     const int i = blockIdx.x / S, h = blockIdx.x % S, c = blockIdx.y;
     const ModDev md = mods[i];
     const u64 q = md.q;
     const FwdMod fm = {q, 0 - q, md.q3};
-    ra_fill_stw(stw, tw_fwd + ((size_t)i << LOGN), S + h);
     const unsigned u = threadIdx.x;
     const int KP = k + np;   // k = limb stride of col (Q limbs of the context), KP = limb stride of acc
     const u64 w = MODE == 2 ? R->qlinv_w[i] : C->pinv_w[i], ws = MODE == 2 ? R->qlinv_ws[i] : C->pinv_ws[i];
@@ -312,60 +347,66 @@ __global__ void __launch_bounds__(RA_THREADS, 3) k_blk_fwd(const ModDev *mods, c
             if ((int)(auto_index((unsigned)hp * M, gal_el, LOGN) >> RA_LOGM) == h) hd = hp;
     }
     const int j0 = blockIdx.z * jb, j1 = min(jobs, j0 + jb);
-    u64 a[8];
-    auto load = [&](int job) {
-        const u64 *src = J.mu + (size_t)job * J.mu_words + (((size_t)c * nlimbs + i) << LOGN) + blk + u;
-#pragma unroll
-        for (int r = 0; r < 8; r++) a[r] = src[256 * r];
-    };
-    load(j0);
-    __syncthreads();   // twiddle table visible
-    int flip = 0;
+    const size_t d_off = (((size_t)c * nlimbs + i) << LOGN) + blk;
+    const size_t col_off = ((size_t)c * k + i) << LOGN;
+    const size_t a_off = MODE == 2 ? col_off + blk : (((size_t)c * KP + i) << LOGN) + blk;
+    const u64 *a_base = MODE == 2 ? J.col : J.acc;
+    const size_t a_words = MODE == 2 ? J.col_words : J.acc_words;
+    if (u == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(&bars[2], 1); mbar_init_fence(); }
+    __syncthreads();
+    if (u == 0) {
+        mbar_expect_tx(&bars[2], 2 * BLK_BYTES);
+        bulk_g2s(stw, twb_fwd + (((size_t)i * S + h) << RA_LOGM), 2 * BLK_BYTES, &bars[2]);
+        mbar_expect_tx(&bars[0], BLK_BYTES);
+        bulk_g2s(landD, J.mu + (size_t)j0 * J.mu_words + d_off, BLK_BYTES, &bars[0]);
+    }
+    mbar_wait(&bars[2], 0);
     for (int job = j0; job < j1; job++) {
-        u64 *s = flip ? buf1 : buf0;
-        flip ^= 1;
-        ntt2048_fwd(a, s, stw, fm, []() {});
-        // a[r] = point 8u + r of the block, lazy
-        if (MODE == 2) {
-            ulonglong2 *x = reinterpret_cast<ulonglong2 *>(J.col + (size_t)job * J.col_words + (((size_t)c * k + i) << LOGN) + blk + 8 * u);
+        const unsigned ph = (unsigned)(job - j0) & 1u;
+        u64 a[8];
+        mbar_wait(&bars[0], ph);
 #pragma unroll
-            for (int r = 0; r < 4; r++) {
-                ulonglong2 v = x[r];
-                v.x = mul_shoup(v.x + q - barrett(a[2 * r], q, md.mu), w, ws, q);
-                v.y = mul_shoup(v.y + q - barrett(a[2 * r + 1], q, md.mu), w, ws, q);
-                x[r] = v;
-            }
-        } else {
-            const ulonglong2 *aq = reinterpret_cast<const ulonglong2 *>(J.acc + (size_t)job * J.acc_words + (((size_t)c * KP + i) << LOGN) + blk + 8 * u);
-            const u64 *colin = J.col + (size_t)job * J.col_words + (((size_t)c * k + i) << LOGN);
-            u64 *colout = J.col2 + (size_t)job * J.col_words + (((size_t)c * k + i) << LOGN);
-            const ulonglong2 *c0 = reinterpret_cast<const ulonglong2 *>(colin + blk + 8 * u);
-#pragma unroll
-            for (int r = 0; r < 4; r++) {
-                ulonglong2 v = aq[r];
-                v.x = mul_shoup(v.x + q - barrett(a[2 * r], q, md.mu), w, ws, q);
-                v.y = mul_shoup(v.y + q - barrett(a[2 * r + 1], q, md.mu), w, ws, q);
-                if (c == 0) { const ulonglong2 t = c0[r]; v.x = add_mod(v.x, t.x, q); v.y = add_mod(v.y, t.y, q); }
-                if (MODE == 1) reinterpret_cast<ulonglong2 *>(colout + blk + 8 * u)[r] = v;
-                else { s[PAD(8 * u + 2 * r)] = v.x; s[PAD(8 * u + 2 * r + 1)] = v.y; }   // the thread's own pass-D slots
-            }
-            if (MODE == 0) {
-                __syncthreads();
-                const size_t nb = (size_t)hd * M + 8 * u;
-                const ulonglong2 *ci = reinterpret_cast<const ulonglong2 *>(colin + nb);
-                ulonglong2 *co = reinterpret_cast<ulonglong2 *>(colout + nb);
-#pragma unroll
-                for (int r = 0; r < 4; r++) {
-                    ulonglong2 v = ci[r];
-                    const unsigned sa = auto_index((unsigned)nb + 2 * r, gal_el, LOGN) & (M - 1);
-                    const unsigned sb = auto_index((unsigned)nb + 2 * r + 1, gal_el, LOGN) & (M - 1);
-                    v.x = add_mod(v.x, s[PAD(sa)], q);
-                    v.y = add_mod(v.y, s[PAD(sb)], q);
-                    co[r] = v;
+        for (int r = 0; r < 8; r++) a[r] = landD[u + 256 * r];
+        ntt2048_fwd(a, buf, stw, fm, [&]() {
+            release_smem_to_async_proxy();
+            __syncthreads();   // every thread holds its input and is past the previous job's epilogue (buf, landA, landX free)
+            if (u == 0) {
+                if (job + 1 < j1) {
+                    mbar_expect_tx(&bars[0], BLK_BYTES);
+                    bulk_g2s(landD, J.mu + (size_t)(job + 1) * J.mu_words + d_off, BLK_BYTES, &bars[0]);
                 }
+                mbar_expect_tx(&bars[1], MODE == 0 ? 2 * BLK_BYTES : BLK_BYTES);
+                bulk_g2s(landA, a_base + (size_t)job * a_words + a_off, BLK_BYTES, &bars[1]);
+                if (MODE == 0) bulk_g2s(landX, J.col + (size_t)job * J.col_words + col_off + (size_t)hd * M, BLK_BYTES, &bars[1]);
+            }
+        }, []() {});
+        // a[r] = point 8u + r of the block, lazy
+        mbar_wait(&bars[1], ph);
+        const ulonglong2 *av = reinterpret_cast<const ulonglong2 *>(landA) + 4 * u;
+        u64 *gout = (MODE == 2 ? J.col : J.col2) + (size_t)job * J.col_words + col_off;
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            ulonglong2 v = av[r];
+            v.x = mul_shoup(v.x + q - barrett(a[2 * r], q, md.mu), w, ws, q);
+            v.y = mul_shoup(v.y + q - barrett(a[2 * r + 1], q, md.mu), w, ws, q);
+            if (MODE != 0) reinterpret_cast<ulonglong2 *>(gout + blk + 8 * u)[r] = v;
+            else { buf[PAD(8 * u + 2 * r)] = v.x; buf[PAD(8 * u + 2 * r + 1)] = v.y; }   // the thread's own last-pass slots
+        }
+        if (MODE == 0) {
+            __syncthreads();
+            const unsigned nb = (unsigned)hd * M + 8 * u;
+            const ulonglong2 *xv = reinterpret_cast<const ulonglong2 *>(landX) + 4 * u;
+            ulonglong2 *co = reinterpret_cast<ulonglong2 *>(gout + nb);
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                ulonglong2 v = xv[r];
+                const unsigned sa = auto_index(nb + 2 * r, gal_el, LOGN) & (M - 1);
+                const unsigned sb = auto_index(nb + 2 * r + 1, gal_el, LOGN) & (M - 1);
+                v.x = add_mod(v.x, buf[PAD(sa)], q);
+                v.y = add_mod(v.y, buf[PAD(sb)], q);
+                co[r] = v;
             }
         }
-        if (job + 1 < j1) load(job + 1);
     }
 }
 
@@ -392,7 +433,7 @@ void launch_blk_intt(const Launch &L, const DeviceTables &T, const BlkSlots &A, 
     const int SB = blk_blocks(T.logn);
     const int jb = pick_jb(SB * A.nslots, jobs);
     const dim3 g(SB * A.nslots, (jobs + jb - 1) / jb);
-    LMN_DISPATCH_S(SB, k_blk_intt<SS><<<g, RA_THREADS, BLK_SMEM, L.stream>>>(T.mods, T.tw_inv, A, jobs, jb));
+    LMN_DISPATCH_S(SB, k_blk_intt<SS><<<g, RA_THREADS, BLK_INTT_SMEM, L.stream>>>(T.mods, T.twb_inv, A, jobs, jb));
 }
 
 void launch_modup_blk(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch, const KsJobs &J) {
@@ -428,8 +469,8 @@ void launch_down_blk(const Launch &L, const DeviceTables &T, const KsConsts *Cd,
     const int SB = blk_blocks(T.logn);
     const int jb = pick_jb(SB * Ch.nq * 2, J.jobs);
     const dim3 g(SB * Ch.nq, 2, (J.jobs + jb - 1) / jb);
-    if (mode == 1) { LMN_DISPATCH_S(SB, k_blk_fwd<SS, 1><<<g, RA_THREADS, BLK_SMEM, L.stream>>>(T.mods, T.tw_fwd, Cd, nullptr, J, gal_el, Ch.nq, T.k, T.np, J.jobs, jb)); }
-    else { LMN_DISPATCH_S(SB, k_blk_fwd<SS, 0><<<g, RA_THREADS, BLK_SMEM, L.stream>>>(T.mods, T.tw_fwd, Cd, nullptr, J, gal_el, Ch.nq, T.k, T.np, J.jobs, jb)); }
+    if (mode == 1) { LMN_DISPATCH_S(SB, k_blk_fwd<SS, 1><<<g, RA_THREADS, BLK_FWD_SMEM, L.stream>>>(T.mods, T.twb_fwd, Cd, nullptr, J, gal_el, Ch.nq, T.k, T.np, J.jobs, jb)); }
+    else { LMN_DISPATCH_S(SB, k_blk_fwd<SS, 0><<<g, RA_THREADS, BLK_FWD_SMEM, L.stream>>>(T.mods, T.twb_fwd, Cd, nullptr, J, gal_el, Ch.nq, T.k, T.np, J.jobs, jb)); }
 }
 
 void launch_rs_pre(const Launch &L, const DeviceTables &T, const RescaleConsts *Rd, int level, const KsJobs &J) {
@@ -444,12 +485,12 @@ void launch_rs_blk(const Launch &L, const DeviceTables &T, const RescaleConsts *
     const int SB = blk_blocks(T.logn);
     const int jb = pick_jb(SB * level * 2, J.jobs);
     const dim3 g(SB * level, 2, (J.jobs + jb - 1) / jb);
-    LMN_DISPATCH_S(SB, k_blk_fwd<SS, 2><<<g, RA_THREADS, BLK_SMEM, L.stream>>>(T.mods, T.tw_fwd, nullptr, Rd, J, 0u, level, T.k, T.np, J.jobs, jb));
+    LMN_DISPATCH_S(SB, k_blk_fwd<SS, 2><<<g, RA_THREADS, BLK_FWD_SMEM, L.stream>>>(T.mods, T.twb_fwd, nullptr, Rd, J, 0u, level, T.k, T.np, J.jobs, jb));
 }
 
 const char *kernels_blk_init() {
     cudaError_t e = cudaSuccess;
-#define SETSM(K) do { if (e == cudaSuccess) e = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BLK_SMEM); } while (0)
+#define SETSM(K) do { if (e == cudaSuccess) e = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BLK_FWD_SMEM); } while (0)
 #define SETS(SS) SETSM(k_blk_intt<SS>); SETSM((k_blk_fwd<SS, 0>)); SETSM((k_blk_fwd<SS, 1>)); SETSM((k_blk_fwd<SS, 2>));
     SETS(2) SETS(4) SETS(8)
 #undef SETS

@@ -1,30 +1,24 @@
-// Radix-16 negacyclic NTT / INTT core for blocks of 4096 residues (sm_100a).
+// 2048-point block core of the negacyclic NTT / INTT (sm_100a).
 //
-// A ring of N = 4096*S coefficients (S = 1, 2, 4  <->  log N = 12, 13, 14) is transformed as S independent block
-// transforms of M = 4096 points; the log2(S) levels that couple the blocks are applied by the elementwise kernel that
-// produces (forward) or consumes (inverse) the data.  One CTA of 256 threads owns one block: every thread carries 16
-// residues in registers through 4 butterfly levels per pass, 3 passes, with two trips through (padded) shared memory
-// in between.  34 KB of shared memory per block transform leaves room for two to six CTAs per SM, so that one CTA's
-// barrier / load phase overlaps another's arithmetic (the 1024-thread whole-limb kernels alternate between "all warps
-// load" and "all warps multiply": sm__pipe_fmaheavy_cycles_active 59 % in profiles/r1b_*).
+// A ring of N = 2048*S coefficients (S = 2, 4, 8  <->  log N = 12, 13, 14) is transformed as S independent block transforms
+// of M = 2048 points; the log2(S) levels that couple the blocks are applied by the elementwise kernel that produces
+// (forward) or consumes (inverse) the data.  One CTA of 256 threads owns one block: every thread carries 8 residues in
+// registers through 3 butterfly levels per pass (3 + 3 + 3 + 2), with three trips through padded shared memory in between;
+// all 2047 twiddles of the block sit in shared memory.  (A 4096-point radix-16 core was measured slower: fewer resident
+// warps per scheduler.)
 //
-// Arithmetic (measured with tools/int_pipe_probe.cu, profiles/r1b_int_pipe_probe.txt): IMAD.WIDE.U32 occupies the
-// fmaheavy pipe for 4 cycles per warp, IMAD for 2, the ALU pipe is separate.  The forward butterfly therefore uses a
-// Shoup quotient estimate that drops the low x low partial product (3 wide multiplies instead of 4): the estimate is
-// at most 1 below the exact one, so the lazy product lies in [0, 3q) and values grow by 3q per level.  With every
-// modulus below 2^64 / (3 log N + 8) (checked in lmn_ctx_create) nothing overflows, and one Barrett step at the end gives
-// the canonical residue - the same number the exact transform gives.  1167 vs 940 Gbutterfly/s register-resident.
+// Arithmetic (measured with tools/int_pipe_probe.cu): IMAD.WIDE.U32 occupies the fmaheavy pipe for 4 cycles per warp, IMAD
+// for 2, the ALU pipe is separate.  The butterflies therefore use a Shoup quotient estimate that drops the low x low
+// partial product (3 wide multiplies instead of 4): the estimate is at most 1 below the exact one, so the lazy product
+// lies in [0, 3q) and forward values grow by 3q per level.  With every modulus below 2^64 / (3 log N + 8) (checked in
+// lmn_ctx_create) nothing overflows, and one Barrett step at the end gives the canonical residue - the same number the exact
+// transform gives.  1167 vs 940 Gbutterfly/s register-resident.
 //
 // Twiddles are Lattigo's tables (ring.SubRing.RootsForward / RootsBackward): index m + i at the level with m groups.
 #pragma once
 #include "device.cuh"
 
 namespace lmn {
-
-constexpr int R16_THREADS = 256;
-constexpr int R16_LOGM = 12;
-constexpr int R16_M = 1 << R16_LOGM;
-constexpr int R16_WORDS = R16_M + (R16_M >> 4);   // padded block
 
 // Loads that must be ISSUED where they are written (prefetch into registers one or two stages ahead of their use):
 // ptxas sinks ld.global.nc towards the first use to shorten live ranges - even across bar.sync - which puts an L2 round
@@ -71,119 +65,6 @@ __device__ __forceinline__ void bfly_ct3(u64 &x, u64 &y, const ulonglong2 w, con
     x = x + t;
 }
 
-// 4 Cooley-Tukey levels on 16 register-resident residues.  The thread's 16 points are a[r] <-> offset r * stride inside
-// one group of the first level; tw_first = index of that group's twiddle at the first level (m*SH + G): the level t
-// twiddles are tw[(tw_first << t) + b], b = 0 .. 2^t - 1.
-__device__ __forceinline__ void r16_fwd(u64 (&a)[16], const ulonglong2 *__restrict__ tw, unsigned tw_first, const FwdMod &m) {
-#pragma unroll
-    for (int t = 0; t < 4; t++) {
-        const int half = 8 >> t;
-#pragma unroll
-        for (int b = 0; b < (1 << t); b++) {
-            const ulonglong2 w = __ldg(&tw[(tw_first << t) + b]);
-#pragma unroll
-            for (int j = 0; j < half; j++) bfly_ct3(a[b * 2 * half + j], a[b * 2 * half + j + half], w, m);
-        }
-    }
-}
-
-// the same with the twiddle of (level t, sub-group b) supplied by a functor (shared-memory table / prefetched registers)
-template <class F>
-__device__ __forceinline__ void r16_fwd_f(u64 (&a)[16], F tw_of, const FwdMod &m, int t0 = 0, int t1 = 4) {
-#pragma unroll
-    for (int t = 0; t < 4; t++) {
-        if (t < t0 || t >= t1) continue;
-        const int half = 8 >> t;
-#pragma unroll
-        for (int b = 0; b < (1 << t); b++) {
-            const ulonglong2 w = tw_of(t, b);
-#pragma unroll
-            for (int j = 0; j < half; j++) bfly_ct3(a[b * 2 * half + j], a[b * 2 * half + j + half], w, m);
-        }
-    }
-}
-// Shared-memory table of the twiddles of passes 0 and 1 of block SH (255 pairs, 4 KB): entry (1<<t)-1+b of pass 0,
-// 15 + 15 i + (1<<t)-1+b for group i of pass 1.  Filled once per CTA; removes an L2 round trip per butterfly level.
-constexpr int R16_STW = 256;
-__device__ __forceinline__ void r16_fill_stw(ulonglong2 *stw, const ulonglong2 *__restrict__ tw, unsigned SH) {
-    const unsigned e = threadIdx.x;
-    if (e < 255) {
-        unsigned first, f;
-        if (e < 15) { first = SH; f = e; } else { first = 16 * SH + (e - 15) / 15; f = (e - 15) % 15; }
-        const unsigned t = 31 - __clz(f + 1), b = f + 1 - (1u << t);
-        stw[e] = __ldg(&tw[(first << t) + b]);
-    }
-}
-
-// Forward transform of one 4096-point block.  in[] : the thread's points u + 256 r (r = 0..15) of the block (already
-// carrying the levels that couple the S blocks); on return a[r] = point 16 u + r of the block's output (bit-reversed
-// order inside the ring, as Lattigo), lazy: below (entry bound + 36 q).  SH = S + h for block h of S.
-// `s` = R16_WORDS words of shared memory owned by the CTA; the caller must have a barrier between the previous use of
-// `s` and this call.
-__device__ __forceinline__ void ntt4096_fwd(u64 (&a)[16], u64 *s, const ulonglong2 *__restrict__ tw, unsigned SH, const FwdMod &m) {
-    const unsigned u = threadIdx.x;
-    r16_fwd(a, tw, SH, m);                                   // levels with 1, 2, 4, 8 groups per block
-#pragma unroll
-    for (int r = 0; r < 16; r++) s[PAD(u + 256 * r)] = a[r];
-    __syncthreads();
-    const unsigned i = u >> 4, j = u & 15;
-#pragma unroll
-    for (int r = 0; r < 16; r++) a[r] = s[PAD(i * 256 + j + 16 * r)];
-    r16_fwd(a, tw, 16 * SH + i, m);                          // 16 .. 128 groups
-#pragma unroll
-    for (int r = 0; r < 16; r++) s[PAD(i * 256 + j + 16 * r)] = a[r];
-    __syncthreads();
-#pragma unroll
-    for (int r = 0; r < 16; r++) a[r] = s[PAD(16 * u + r)];
-    r16_fwd(a, tw, 256 * SH + u, m);                         // 256 .. 2048 groups
-}
-
-// ---------------------------------------------------------------------------------------------------
-// inverse (Gentleman-Sande, Harvey [0, 2q) invariant, exact Shoup products)
-// 4 levels on 16 registers; a[r] <-> offset r * stride, first level pairs (2b, 2b+1).  tw_last = index of the
-// thread's group at the LAST of the 4 levels (h*SH + G); level t (t = 3 first .. 0 last) uses tw[(tw_last << t) + b].
-__device__ __forceinline__ void r16_inv(u64 (&a)[16], const ulonglong2 *__restrict__ tw, unsigned tw_last, u64 q, u64 q2) {
-#pragma unroll
-    for (int t = 3; t >= 0; t--) {
-        const int half = 8 >> t;
-#pragma unroll
-        for (int b = 0; b < (1 << t); b++) {
-            const ulonglong2 w = __ldg(&tw[(tw_last << t) + b]);
-#pragma unroll
-            for (int j = 0; j < half; j++) bfly_gs(a[b * 2 * half + j], a[b * 2 * half + j + half], w, q, q2);
-        }
-    }
-}
-// Inverse transform of one 4096-point block: in a[r] = point 16 u + r (values in [0, 2q)), out a[r] = point u + 256 r,
-// in [0, 2q), not scaled by N^-1; the log2(S) levels that couple the blocks remain to be applied by the consumer.
-__device__ __forceinline__ void ntt4096_inv(u64 (&a)[16], u64 *s, const ulonglong2 *__restrict__ tw, unsigned SH, u64 q) {
-    const unsigned u = threadIdx.x;
-    const u64 q2 = 2 * q;
-    r16_inv(a, tw, 256 * SH + u, q, q2);                     // levels with 2048 .. 256 groups per block
-#pragma unroll
-    for (int r = 0; r < 16; r++) s[PAD(16 * u + r)] = a[r];
-    __syncthreads();
-    const unsigned i = u >> 4, j = u & 15;
-#pragma unroll
-    for (int r = 0; r < 16; r++) a[r] = s[PAD(i * 256 + j + 16 * r)];
-    r16_inv(a, tw, 16 * SH + i, q, q2);                      // 128 .. 16 groups
-#pragma unroll
-    for (int r = 0; r < 16; r++) s[PAD(i * 256 + j + 16 * r)] = a[r];
-    __syncthreads();
-#pragma unroll
-    for (int r = 0; r < 16; r++) a[r] = s[PAD(u + 256 * r)];
-    r16_inv(a, tw, SH, q, q2);                               // 8 .. 1 groups
-}
-
-}  // namespace lmn
-
-// =====================================================================================================
-// Radix-8 core for blocks of 2048 residues (256 threads x 8 residues, passes of 3 + 3 + 3 + 2 levels), used where the
-// thread must keep other state in registers (k_mac_ra: the gadget-product accumulators).  ALL 2047 twiddles of the
-// block live in shared memory (32 KB, loaded once per CTA and reused for every digit), so that the transform itself
-// issues no global loads.
-// =====================================================================================================
-namespace lmn {
 constexpr int RA_THREADS = 256;
 constexpr int RA_LOGM = 11;
 constexpr int RA_M = 1 << RA_LOGM;
@@ -285,7 +166,8 @@ __device__ __forceinline__ void r8_inv_f(u64 (&a)[8], F tw_of, const FwdMod &m, 
 // in a[r] = point 8u + r of the block (values in [0, 4q)); out a[r] = point u + 256 r, in [0, 4q), NOT scaled by N^-1;
 // the log2(S) levels that couple the S blocks of a limb remain to be applied by the consumer.  stw = the block's table of
 // INVERSE twiddles (ra_fill_stw on RootsBackward).  `s` as in ntt2048_fwd.
-__device__ __forceinline__ void ntt2048_inv(u64 (&a)[8], u64 *s, const ulonglong2 *stw, const FwdMod &m) {
+template <class Hook0>
+__device__ __forceinline__ void ntt2048_inv(u64 (&a)[8], u64 *s, const ulonglong2 *stw, const FwdMod &m, Hook0 before_store) {
     const unsigned u = threadIdx.x;
     const u64 q4 = 4 * m.q;
 #pragma unroll
@@ -298,6 +180,7 @@ __device__ __forceinline__ void ntt2048_inv(u64 (&a)[8], u64 *s, const ulonglong
         const ulonglong2 w = stw[512 + b * 256 + u];
         bfly_gs3(a[4 * b], a[4 * b + 2], w, m, q4); bfly_gs3(a[4 * b + 1], a[4 * b + 3], w, m, q4);
     }
+    before_store();   // runs after the first register stage and before the first store to `s`
 #pragma unroll
     for (int r = 0; r < 8; r++) s[PAD(8 * u + r)] = a[r];
     __syncthreads();

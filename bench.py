@@ -164,7 +164,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--config", default="D", choices=list(CONFIGS))
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--batch", type=int, default=592, help="column-vector jobs per launch; multiples of 37 make every grid a whole number of waves on 148 SMs")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cols-override", type=int, default=0, help="profiling only: shrink the matrix to this many columns, keeping the named config's k, N and rows")
@@ -281,11 +281,18 @@ def main():
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
+        t0 = time.perf_counter()
         for _ in range(steps):
             fn()
         e1.record(stream)
         barrier()
-        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        wall_ms = (time.perf_counter() - t0) * 1e3
+        ev_ms = e0.elapsed_time(e1)
+        # the events must bracket the library's kernels (same stream): a device time well below the host's wall clock around
+        # the same region means they were recorded on another stream
+        if ev_ms < 0.9 * wall_ms - 5.0:
+            raise RuntimeError("device-timed %.1f ms vs wall %.1f ms: events are not ordered with the library's stream" % (ev_ms, wall_ms))
+        ms = torch.tensor([ev_ms], device=dev)
         if G > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())

@@ -66,7 +66,8 @@ typedef struct lmn_params {
 int lmn_ctx_create(const lmn_params *params, int device, lmn_ctx **out);
 void lmn_ctx_destroy(lmn_ctx *ctx);
 const char *lmn_last_error(void);
-/* run all work of this context on an existing CUDA stream (cudaStream_t); NULL = the context's own stream */
+/* run all work of this context on an existing CUDA stream (cudaStream_t); NULL = the context's own (non-blocking) stream;
+ * pass cudaStreamLegacy (0x1) / cudaStreamPerThread (0x2) to name CUDA's default streams */
 int lmn_ctx_set_stream(lmn_ctx *ctx, void *cuda_stream);
 int lmn_ctx_synchronize(lmn_ctx *ctx);
 /* number of kernels launched by this context since creation (bench.py's gpu_launches) */

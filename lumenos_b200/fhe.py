@@ -208,6 +208,10 @@ class ServerBFV:
 
     # -- plumbing --
     def SetStream(self, cuda_stream_ptr):
+        # torch's default stream has handle 0, which the C ABI reads as "the context's own stream": name the legacy default
+        # stream explicitly (cudaStreamLegacy = 0x1) so that events recorded on torch's stream order with the library's kernels
+        if cuda_stream_ptr == 0:
+            cuda_stream_ptr = 1
         check(_capi.lib().lmn_ctx_set_stream(self.ctx, cuda_stream_ptr))
 
     def Synchronize(self):

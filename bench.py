@@ -32,6 +32,7 @@ sys.path.insert(0, ROOT)
 CONFIGS = {  # rows, cols, logN  (scripts/benchmark_server.sh:34-39, README.md:59-61)
     "A": (2048, 1024, 12), "B": (4096, 2048, 12), "C": (8192, 4096, 13), "D": (16384, 4096, 14),
 }
+PUBLISHED_COMMIT_S = {"A": 1.03, "B": 2.04, "C": 9.17, "D": 18.79}  # "Commit eval": leaf rescale + Merkle (BASELINE.md:23)
 PUBLISHED_S = {"A": 14.77, "B": 36.80, "C": 179.93, "D": 397.85}  # Encode + Prove eval, m7i.8xlarge 32 vCPU
 RHO_INV, SECURITY_BITS = 2, 128
 
@@ -166,6 +167,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=592, help="column-vector jobs per launch; multiples of 37 make every grid a whole number of waves on 148 SMs")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-commit", action="store_true", help="skip the Commit Merkle span (reported beside the headline)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cols-override", type=int, default=0, help="profiling only: shrink the matrix to this many columns, keeping the named config's k, N and rows")
     args = ap.parse_args()
@@ -364,6 +366,40 @@ def main():
             breakdown[name] = {"ms": round(ms.value, 3), "launches": cnt.value}
     _capi.check(lib.lmn_profile_enable(be.ctx, 0))
 
+    # ---- Commit's "Merkle tree built" span (fhe/ligero.go:105-116), reported beside the headline, not inside it ----
+    commit_merkle = None
+    if G == 1 and not args.no_commit:
+        leaves = be.NewStore(n, lout)
+        lf = fhe.LeafFormat.lattigo_like(b"\x00" * 48, lout, N)     # 48 placeholder MetaData bytes + lattigo's u64 length prefixes
+        qsel = be.NewStore(len(my_idx), lout)
+
+        def commit_tail():
+            _capi.check(lib.lmn_commit_leaves(be.ctx, enc_store.h, leaves.h))
+            t = fhe.MerkleTree(be, leaves, lf)
+            root = t.MerkleRoot()
+            t.free()
+            return root
+        commit_tail()
+        for i in range(lib.lmn_kernel_count()):
+            lib.lmn_profile_read(be.ctx, i, None, None, 1)
+        _capi.check(lib.lmn_profile_enable(be.ctx, 0xFFFFFFFF))
+        cm_ms = timed(commit_tail, 1)
+        cm_parts = {}
+        for name, i in KID.items():
+            ms, cnt = C.c_double(), C.c_uint64()
+            _capi.check(lib.lmn_profile_read(be.ctx, i, C.byref(ms), C.byref(cnt), 1))
+            if cnt.value:
+                cm_parts[name] = {"ms": round(ms.value, 3), "launches": cnt.value}
+        _capi.check(lib.lmn_profile_enable(be.ctx, 0))
+        gq_ms = timed(lambda: _capi.check(lib.lmn_store_gather(be.ctx, leaves.h, my_idx.ctypes.data_as(vp), len(my_idx), qsel.h)), 1)
+        leaf_len = len(lf.header) + 2 * (len(lf.polyHeader) + (lout + 1) * (len(lf.limbHeader) + 8 * N))
+        sha_ms = cm_parts.get("k_sha256_leaves", {}).get("ms", 0.0)
+        commit_merkle = {"ms": cm_ms, "leaves": n, "leaf_bytes": leaf_len, "kernels": cm_parts,
+                         "sha256_leaves_GBps": (n * leaf_len / (sha_ms * 1e-3) / 1e9) if sha_ms else None,
+                         "query_gather_from_leaves_ms": gq_ms, "published_reference_s": PUBLISHED_COMMIT_S.get(args.config),
+                         "note": "leaf rescale of all n encoded columns to level 1 + leaf serialisation + SHA-256 Merkle tree on the GPU; root read back to the host"}
+        leaves.free(); qsel.free()
+
     # ---- e2e: host buffers through the C ABI, H2D + D2H inside the timed region ----
     e2e = None
     if not args.no_e2e:
@@ -411,7 +447,7 @@ def main():
                        "sharding": "1 GPU" if G == 1 else "columns/%d for inner products + query rescale, coefficient slices/%d for Encode, all-to-all of queried slices" % (G, G),
                        "batch_jobs": args.batch},
             "e2e": e2e, "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "roofline_int": roofline_int,
-            "roofline_encode": roofline_encode, "kernel_breakdown_one_step": breakdown, "cpu_baseline": cpu,
+            "roofline_encode": roofline_encode, "kernel_breakdown_one_step": breakdown, "commit_merkle": commit_merkle, "cpu_baseline": cpu,
             "published_reference_s": PUBLISHED_S[args.config],
         }
         print(json.dumps(out))

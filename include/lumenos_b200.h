@@ -154,6 +154,34 @@ int lmn_query_columns(lmn_ctx *ctx, const lmn_store *encoded, const uint32_t *id
 /* product of q_l^-1 mod t for l = from_level .. to_level+1: the factor by which bgv Rescale updates Scale */
 uint64_t lmn_rescale_scale(const lmn_ctx *ctx, uint32_t from_level, uint32_t to_level);
 
+/* ---------------- Commit eval: leaves + Merkle tree (fhe/ligero.go:105-116, 126-183; core/tree.go:37-219) ---------------- */
+/* leaves[i] = encoded[i] rescaled to level 1: the CopyNew + Rescale loop of processLeafParallel (ligero.go:146-154).
+ * The leaves store also serves the query stage: lmn_store_gather(leaves, idx) == lmn_query_columns(encoded, idx). */
+int lmn_commit_leaves(lmn_ctx *ctx, const lmn_store *encoded, lmn_store *leaves);
+/* out[i] = src[idx[i]] (same level) */
+int lmn_store_gather(lmn_ctx *ctx, const lmn_store *src, const uint32_t *idx, uint32_t n_idx, lmn_store *out);
+/* Byte stream of one leaf = what ct.WriteTo(buf) emits (ligero.go:157-158):
+ *   header || for each of the 2 polynomials: poly_header || for each limb: limb_header || N coefficients as little-endian u64.
+ * The framing bytes are the caller's: lattigo's (MetaData bytes, slice-length prefixes) are produced by the Go host once per
+ * Commit (they do not depend on the column); poly_header_len, limb_header_len <= 16. */
+typedef struct {
+    const uint8_t *header; uint32_t header_len;
+    const uint8_t *poly_header; uint32_t poly_header_len;
+    const uint8_t *limb_header; uint32_t limb_header_len;
+} lmn_leaf_format;
+typedef struct lmn_merkle lmn_merkle;
+/* core.NewTree(leafs) (tree.go:76-163): SHA-256 leaf hashes, parents = SHA-256(left || right), an unpaired last node is paired
+ * with itself.  Hashing runs on the GPU; the node hashes (32 B each) are kept on the host for root and paths. */
+int lmn_merkle_build(lmn_ctx *ctx, const lmn_store *leaves, const lmn_leaf_format *fmt, lmn_merkle **out);
+void lmn_merkle_destroy(lmn_merkle *tree);
+uint32_t lmn_merkle_leaf_count(const lmn_merkle *tree);
+uint32_t lmn_merkle_depth(const lmn_merkle *tree);                            /* hashes per path */
+int lmn_merkle_root(const lmn_merkle *tree, uint8_t *out32);                  /* MerkleTree.MerkleRoot, tree.go:165-172 */
+int lmn_merkle_leaf_hash(const lmn_merkle *tree, uint32_t index, uint8_t *out32);
+int lmn_merkle_path(const lmn_merkle *tree, uint32_t index, uint8_t *out);    /* GetMerklePath, tree.go:176-219: 32*depth bytes */
+/* test hook: the serialised bytes of leaf `index` (out may be NULL to query *len) */
+int lmn_leaf_bytes(lmn_ctx *ctx, const lmn_store *leaves, uint32_t index, const lmn_leaf_format *fmt, uint8_t *out, size_t cap, size_t *len);
+
 /* ---------------- ServerBFV operator level (fhe/bfv.go:13-58; promoted bgv.Evaluator methods) ---------------- */
 /* each operand is (store, index); stores must be at the same level unless noted */
 int lmn_ct_add(lmn_ctx *ctx, const lmn_store *a, uint32_t ai, const lmn_store *b, uint32_t bi, lmn_store *o, uint32_t oi); /* Evaluator.Add, ntt.go:27 */

@@ -11,6 +11,11 @@ u32p = C.POINTER(C.c_uint32)
 vp = C.c_void_p
 
 
+class LmnLeafFormat(C.Structure):
+    _fields_ = [("header", C.c_char_p), ("header_len", C.c_uint32), ("poly_header", C.c_char_p), ("poly_header_len", C.c_uint32),
+                ("limb_header", C.c_char_p), ("limb_header_len", C.c_uint32)]
+
+
 class LmnParams(C.Structure):
     _fields_ = [("log_n", C.c_uint32), ("num_q", C.c_uint32), ("num_p", C.c_uint32),
                 ("q", u64p), ("p", u64p), ("psi_q", u64p), ("psi_p", u64p), ("t", C.c_uint64),
@@ -60,6 +65,16 @@ SIGNATURES = {
     "lmn_inner_product2": (C.c_int, [vp, vp, vp, vp, C.c_uint32, vp, vp]),
     "lmn_ring_switch": (C.c_int, [vp, vp, vp]),
     "lmn_query_columns": (C.c_int, [vp, vp, vp, C.c_uint32, vp]),
+    "lmn_commit_leaves": (C.c_int, [vp, vp, vp]),
+    "lmn_store_gather": (C.c_int, [vp, vp, vp, C.c_uint32, vp]),
+    "lmn_merkle_build": (C.c_int, [vp, vp, C.POINTER(LmnLeafFormat), C.POINTER(vp)]),
+    "lmn_merkle_destroy": (None, [vp]),
+    "lmn_merkle_leaf_count": (C.c_uint32, [vp]),
+    "lmn_merkle_depth": (C.c_uint32, [vp]),
+    "lmn_merkle_root": (C.c_int, [vp, vp]),
+    "lmn_merkle_leaf_hash": (C.c_int, [vp, C.c_uint32, vp]),
+    "lmn_merkle_path": (C.c_int, [vp, C.c_uint32, vp]),
+    "lmn_leaf_bytes": (C.c_int, [vp, vp, C.c_uint32, C.POINTER(LmnLeafFormat), vp, C.c_size_t, C.POINTER(C.c_size_t)]),
     "lmn_rescale_scale": (C.c_uint64, [vp, C.c_uint32, C.c_uint32]),
     "lmn_ct_add": (C.c_int, [vp, vp, C.c_uint32, vp, C.c_uint32, vp, C.c_uint32]),
     "lmn_ct_sub": (C.c_int, [vp, vp, C.c_uint32, vp, C.c_uint32, vp, C.c_uint32]),

@@ -6,8 +6,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "liblumenos_b200.so")
-SOURCES = ["api.cu", "kernels.cu", "kernels_blk.cu", "kernels_mac.cu", "plan.cpp"]
-HEADERS = ["device.cuh", "ntt_blk.cuh", "tma.cuh", "kernels.cuh", "plan.hpp", "hostmath.hpp", os.path.join("..", "..", "include", "lumenos_b200.h")]
+SOURCES = ["api.cu", "kernels.cu", "kernels_blk.cu", "kernels_mac.cu", "kernels_commit.cu", "plan.cpp"]
+HEADERS = ["device.cuh", "ntt_blk.cuh", "tma.cuh", "kernels.cuh", "commit.cuh", "plan.hpp", "hostmath.hpp", os.path.join("..", "..", "include", "lumenos_b200.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--fmad=false",
          "-Xcompiler", "-fPIC,-O3,-Wall", "-shared", "-cudart", "static"]

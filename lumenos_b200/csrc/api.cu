@@ -10,6 +10,7 @@
 
 #include "../../include/lumenos_b200.h"
 #include "hostmath.hpp"
+#include "commit.cuh"
 #include "kernels.cuh"
 #include "plan.hpp"
 
@@ -722,7 +723,7 @@ int lmn_inner_product2(lmn_ctx *c, const lmn_store *matrix, const uint64_t *pt_r
     const size_t N = c->n, k = c->k;
     const int nvec = pt_b ? 2 : 1;
     const uint32_t bc = std::max(1u, c->batch / nvec);
-    if (int rc = ensure_workspace(c, bc * nvec)) return rc;
+    if (int rc = ensure_workspace(c, std::min(bc, matrix->count) * nvec)) return rc;
     Launch L = c->L();
     // plaintexts: upload, fold T and the Montgomery factor (tensorStandard's T * pt)
     u64 *d_pt = c->ws_pt, *d_ptm = c->ws_pt + 2 * k * N;
@@ -756,18 +757,20 @@ uint64_t lmn_rescale_scale(const lmn_ctx *c, uint32_t from_level, uint32_t to_le
     return s;
 }
 
-// ---------------- Query columns ----------------
-int lmn_query_columns(lmn_ctx *c, const lmn_store *enc, const uint32_t *idx, uint32_t n_idx, lmn_store *out) {
-    if (!c || !enc || !idx || !out || n_idx == 0) return fail(LMN_ERR_INVALID, "null argument");
+// ---------------- Query columns / leaf rescale ----------------
+// out[j] = enc[idx[j]] rescaled to level 1, for host indices idx (nullptr: idx[j] = j).  Caller holds the context lock.
+static int rescale_select(lmn_ctx *c, const lmn_store *enc, const uint32_t *idx, uint32_t n_idx, lmn_store *out) {
     const int Lmax = c->k - 1, lout = std::min(1, Lmax);
-    if ((int)enc->level != Lmax || (int)out->level != lout || out->count < n_idx) return fail(LMN_ERR_INVALID, "query needs max-level input and a level-1 output store with n_idx entries");
-    for (uint32_t i = 0; i < n_idx; i++) if (idx[i] >= enc->count) return fail(LMN_ERR_INVALID, "query index out of range");
-    std::lock_guard<std::mutex> g(c->mu);
+    if ((int)enc->level != Lmax || (int)out->level != lout || out->count < n_idx) return fail(LMN_ERR_INVALID, "rescale needs max-level input and a level-1 output store with one entry per index");
+    std::vector<uint32_t> iota;
+    if (!idx) { iota.resize(n_idx); for (uint32_t i = 0; i < n_idx; i++) iota[i] = i; idx = iota.data(); }
+    for (uint32_t i = 0; i < n_idx; i++) if (idx[i] >= enc->count) return fail(LMN_ERR_INVALID, "column index out of range");
     cudaSetDevice(c->device);
-    if (c->ws_idx_cap < n_idx) { cudaFree(c->ws_idx); c->ws_idx = nullptr; CK(cudaMalloc(&c->ws_idx, n_idx * sizeof(uint32_t))); c->ws_idx_cap = n_idx; }
+    if (c->ws_idx_cap < n_idx) { cudaFree(c->ws_idx); c->ws_idx = nullptr; c->ws_idx_cap = 0; CK(cudaMalloc(&c->ws_idx, n_idx * sizeof(uint32_t))); c->ws_idx_cap = n_idx; }
     CK(cudaMemcpyAsync(c->ws_idx, idx, n_idx * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+    if (!iota.empty()) CK(cudaStreamSynchronize(c->stream));   // the pageable source dies with this frame
     const uint32_t bc = c->batch;
-    if (int rc = ensure_workspace(c, bc)) return rc;
+    if (int rc = ensure_workspace(c, std::min(bc, n_idx))) return rc;
     Launch L = c->L();
     const size_t out_words = 2 * (size_t)(lout + 1) * c->n;
     for (uint32_t j0 = 0; j0 < n_idx; j0 += bc) {
@@ -779,6 +782,11 @@ int lmn_query_columns(lmn_ctx *c, const lmn_store *enc, const uint32_t *idx, uin
     }
     CK(cudaGetLastError());
     return 0;
+}
+int lmn_query_columns(lmn_ctx *c, const lmn_store *enc, const uint32_t *idx, uint32_t n_idx, lmn_store *out) {
+    if (!c || !enc || !idx || !out || n_idx == 0) return fail(LMN_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> g(c->mu);
+    return rescale_select(c, enc, idx, n_idx, out);
 }
 
 // ---------------- ring switch ----------------
@@ -900,6 +908,142 @@ int lmn_limb_ntt(lmn_ctx *c, lmn_store *a, uint32_t ai, uint32_t poly, uint32_t 
     cudaSetDevice(c->device);
     launch_limb_ntt(c->L(), c->T, (int)limb, a->d + ai * a->words() + ((size_t)poly * (a->level + 1) + limb) * c->n, inverse);
     CK(cudaGetLastError());
+    return 0;
+}
+
+// ---------------- Commit eval: leaves and Merkle tree (fhe/ligero.go:105-116, 126-183; core/tree.go) ----------------
+struct lmn_merkle {
+    uint32_t n_leaves = 0;
+    std::vector<uint32_t> level_off;     // node offset of every level (level 0 = leaf hashes)
+    std::vector<uint32_t> level_cnt;
+    std::vector<uint8_t> nodes;          // 32 bytes per node, host copy of the whole tree
+};
+
+int lmn_commit_leaves(lmn_ctx *c, const lmn_store *enc, lmn_store *leaves) {
+    if (!c || !enc || !leaves) return fail(LMN_ERR_INVALID, "null argument");
+    if (leaves->count != enc->count) return fail(LMN_ERR_INVALID, "one leaf per encoded column");
+    std::lock_guard<std::mutex> g(c->mu);
+    return rescale_select(c, enc, nullptr, enc->count, leaves);
+}
+
+int lmn_store_gather(lmn_ctx *c, const lmn_store *src, const uint32_t *idx, uint32_t n_idx, lmn_store *out) {
+    if (!c || !src || !idx || !out || n_idx == 0) return fail(LMN_ERR_INVALID, "null argument");
+    if (src->level != out->level || src->n != out->n || out->count < n_idx) return fail(LMN_ERR_INVALID, "gather needs stores of one level and n_idx output entries");
+    for (uint32_t i = 0; i < n_idx; i++) if (idx[i] >= src->count) return fail(LMN_ERR_INVALID, "index out of range");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    // copies queued in index order on the context's stream (<= a few hundred level-1 ciphertexts on the query path)
+    for (uint32_t i = 0; i < n_idx; i++)
+        CK(cudaMemcpyAsync(out->d + i * out->words(), src->d + (size_t)idx[i] * src->words(), src->words() * 8, cudaMemcpyDeviceToDevice, c->stream));
+    return 0;
+}
+
+static int make_leaf_format(lmn_ctx *c, const lmn_store *leaves, const lmn_leaf_format *fmt, LeafFormat &F, uint8_t **d_hdr) {
+    if (fmt->poly_header_len > LEAF_HDR_MAX || fmt->limb_header_len > LEAF_HDR_MAX) return fail(LMN_ERR_INVALID, "poly / limb headers are at most 16 bytes");
+    if ((fmt->header_len && !fmt->header) || (fmt->poly_header_len && !fmt->poly_header) || (fmt->limb_header_len && !fmt->limb_header))
+        return fail(LMN_ERR_INVALID, "null header with non-zero length");
+    memset(&F, 0, sizeof(F));
+    F.hdr_len = fmt->header_len; F.poly_hdr_len = fmt->poly_header_len; F.limb_hdr_len = fmt->limb_header_len;
+    if (F.poly_hdr_len) memcpy(F.poly_hdr, fmt->poly_header, F.poly_hdr_len);
+    if (F.limb_hdr_len) memcpy(F.limb_hdr, fmt->limb_header, F.limb_hdr_len);
+    F.nl = leaves->level + 1;
+    int logn = 0; while ((1u << logn) < leaves->n) logn++;
+    F.logn = (uint32_t)logn;
+    const uint64_t limb_len = F.limb_hdr_len + 8ull * leaves->n, poly_len = F.poly_hdr_len + F.nl * limb_len, total = F.hdr_len + 2 * poly_len;
+    if (total + 72 >= (1ull << 31)) return fail(LMN_ERR_UNSUPPORTED, "leaf stream longer than 2 GiB");
+    F.limb_len = (uint32_t)limb_len; F.poly_len = (uint32_t)poly_len; F.total_len = (uint32_t)total;
+    F.padded_len = (uint32_t)((total + 9 + 63) / 64 * 64);
+    *d_hdr = nullptr;
+    if (F.hdr_len) {
+        CK(cudaMalloc(d_hdr, F.hdr_len));
+        CK(cudaMemcpy(*d_hdr, fmt->header, F.hdr_len, cudaMemcpyHostToDevice));
+    }
+    F.hdr = *d_hdr;
+    return 0;
+}
+
+int lmn_leaf_bytes(lmn_ctx *c, const lmn_store *leaves, uint32_t index, const lmn_leaf_format *fmt, uint8_t *out, size_t cap, size_t *len) {
+    if (!c || !leaves || !fmt || !len) return fail(LMN_ERR_INVALID, "null argument");
+    if (index >= leaves->count) return fail(LMN_ERR_INVALID, "leaf index out of range");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    LeafFormat F; uint8_t *d_hdr = nullptr;
+    if (int rc = make_leaf_format(c, leaves, fmt, F, &d_hdr)) return rc;
+    *len = F.total_len;
+    int rc = 0;
+    if (out) {
+        if (cap < F.total_len) rc = fail(LMN_ERR_INVALID, "output buffer too small for the leaf");
+        else {
+            u64 *ser = nullptr;
+            cudaError_t e = cudaMalloc(&ser, F.padded_len);
+            if (e == cudaSuccess) {
+                launch_leaf_serialize(c->L(), F, leaves->d + (size_t)index * leaves->words(), leaves->words(), 1, ser);
+                e = cudaMemcpyAsync(out, ser, F.total_len, cudaMemcpyDeviceToHost, c->stream);
+                if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+                cudaFree(ser);
+            }
+            if (e != cudaSuccess) rc = fail(LMN_ERR_CUDA, cudaGetErrorString(e));
+        }
+    }
+    cudaFree(d_hdr);
+    return rc;
+}
+
+int lmn_merkle_build(lmn_ctx *c, const lmn_store *leaves, const lmn_leaf_format *fmt, lmn_merkle **out) {
+    if (!c || !leaves || !fmt || !out) return fail(LMN_ERR_INVALID, "null argument");
+    if (leaves->count == 0) return fail(LMN_ERR_INVALID, "no leaves");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    LeafFormat F; uint8_t *d_hdr = nullptr;
+    if (int rc = make_leaf_format(c, leaves, fmt, F, &d_hdr)) return rc;
+    const uint32_t n = leaves->count;
+    auto *m = new lmn_merkle();
+    m->n_leaves = n;
+    uint32_t total_nodes = 0;
+    for (uint32_t cnt = n;; cnt = (cnt + 1) / 2) { m->level_off.push_back(total_nodes); m->level_cnt.push_back(cnt); total_nodes += cnt; if (cnt == 1) break; }
+    u64 *ser = nullptr; uint32_t *d_nodes = nullptr;
+    cudaError_t e = cudaMalloc(&ser, (size_t)n * F.padded_len);
+    if (e == cudaSuccess) e = cudaMalloc(&d_nodes, (size_t)total_nodes * 32);
+    if (e == cudaSuccess) {
+        Launch L = c->L();
+        launch_leaf_serialize(L, F, leaves->d, leaves->words(), n, ser);
+        launch_sha256_leaves(L, ser, F.padded_len, n, d_nodes);
+        for (size_t l = 0; l + 1 < m->level_cnt.size(); l++)
+            launch_sha256_nodes(L, d_nodes + (size_t)m->level_off[l] * 8, m->level_cnt[l], d_nodes + (size_t)m->level_off[l + 1] * 8);
+        e = cudaGetLastError();
+        m->nodes.resize((size_t)total_nodes * 32);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(m->nodes.data(), d_nodes, m->nodes.size(), cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    }
+    cudaFree(ser); cudaFree(d_nodes); cudaFree(d_hdr);
+    if (e != cudaSuccess) { delete m; return fail(LMN_ERR_CUDA, std::string("merkle build: ") + cudaGetErrorString(e)); }
+    *out = m;
+    return 0;
+}
+void lmn_merkle_destroy(lmn_merkle *m) { delete m; }
+uint32_t lmn_merkle_leaf_count(const lmn_merkle *m) { return m ? m->n_leaves : 0; }
+uint32_t lmn_merkle_depth(const lmn_merkle *m) { return m ? (uint32_t)m->level_cnt.size() - 1 : 0; }
+int lmn_merkle_root(const lmn_merkle *m, uint8_t *out32) {
+    if (!m || !out32) return fail(LMN_ERR_INVALID, "null argument");
+    memcpy(out32, m->nodes.data() + (size_t)m->level_off.back() * 32, 32);
+    return 0;
+}
+int lmn_merkle_leaf_hash(const lmn_merkle *m, uint32_t index, uint8_t *out32) {
+    if (!m || !out32) return fail(LMN_ERR_INVALID, "null argument");
+    if (index >= m->n_leaves) return fail(LMN_ERR_INVALID, "index out of bounds");
+    memcpy(out32, m->nodes.data() + (size_t)index * 32, 32);
+    return 0;
+}
+// sibling hashes from the leaf level up (core/tree.go:176-219); the unpaired last node of a level is its own sibling
+int lmn_merkle_path(const lmn_merkle *m, uint32_t index, uint8_t *out) {
+    if (!m || !out) return fail(LMN_ERR_INVALID, "null argument");
+    if (index >= m->n_leaves) return fail(LMN_ERR_INVALID, "index out of bounds");
+    uint32_t i = index;
+    for (size_t l = 0; l + 1 < m->level_cnt.size(); l++, i >>= 1) {
+        uint32_t sib = i ^ 1u;
+        if (sib >= m->level_cnt[l]) sib = i;
+        memcpy(out + 32 * l, m->nodes.data() + ((size_t)m->level_off[l] + sib) * 32, 32);
+    }
     return 0;
 }
 

@@ -27,7 +27,7 @@ namespace lmn {
 static inline int ntt_threads(int m) { int t = m / 8; return t < 32 ? 32 : (t > 1024 ? 1024 : t); }
 const char *kernel_name(int id) {
     static const char *names[KID_COUNT] = {"k_encode_pass", "k_mul_pt", "k_intt_c1", "k_modup", "k_mac", "k_pintt", "k_down_pre",
-                                           "k_down", "k_rs_intt", "k_rs_pre", "k_rs_apply", "k_pack_out", "k_gather_in", "k_ring_decimate", "other"};
+                                           "k_down", "k_rs_intt", "k_rs_pre", "k_rs_apply", "k_pack_out", "k_gather_in", "k_ring_decimate", "k_leaf_serialize", "k_sha256_leaves", "k_sha256_nodes", "other"};
     return id >= 0 && id < KID_COUNT ? names[id] : "?";
 }
 cudaEvent_t Profiler::get() {

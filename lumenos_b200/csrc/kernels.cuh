@@ -76,7 +76,7 @@ struct EncPassArgs {
 
 // kernel classes (profiling / launch accounting)
 enum KernelId { KID_ENCODE = 0, KID_MULPT, KID_INTT_C1, KID_VFIX, KID_MAC, KID_PINTT, KID_VPFIX, KID_DOWN, KID_RS_INTT,
-                KID_RS_PRE, KID_RS_APPLY, KID_PACK, KID_GATHER, KID_DECIMATE, KID_OTHER, KID_COUNT };
+                KID_RS_PRE, KID_RS_APPLY, KID_PACK, KID_GATHER, KID_DECIMATE, KID_LEAF_SER, KID_SHA_LEAF, KID_SHA_NODE, KID_OTHER, KID_COUNT };
 const char *kernel_name(int id);
 
 // optional per-class device timing: CUDA event pairs recorded on the launch stream around each launch

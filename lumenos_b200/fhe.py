@@ -342,17 +342,95 @@ class LigeroMetadata:
 
 
 class EncryptedProof:
-    """ref: fhe/ligero.go:185-192 (Merkle paths and root stay on the host)"""
+    """ref: fhe/ligero.go:185-192"""
 
-    def __init__(self, metadata, matR, matZ, queriedCols):
+    def __init__(self, metadata, matR, matZ, queriedCols, merklePaths=None, root=None):
         self.Metadata, self.MatR, self.MatZ, self.QueriedCols = metadata, matR, matZ, queriedCols
+        self.MerklePaths, self.Root = merklePaths, root
+
+
+class LeafFormat:
+    """Framing of the leaf byte stream `ct.WriteTo(buf)` (fhe/ligero.go:157-158): header || 2 x (polyHeader || limbs x
+    (limbHeader || N little-endian u64)).  The Go host supplies lattigo's bytes; `lattigo_like` reproduces the structure of
+    lattigo's structs.Vector / structs.Matrix writers (u64 length prefixes) around caller-provided MetaData bytes."""
+
+    def __init__(self, header=b"", polyHeader=b"", limbHeader=b""):
+        self.header, self.polyHeader, self.limbHeader = bytes(header), bytes(polyHeader), bytes(limbHeader)
+
+    @staticmethod
+    def lattigo_like(metadata, level, N):
+        le = lambda v: int(v).to_bytes(8, "little")
+        return LeafFormat(bytes(metadata) + le(2), le(level + 1), le(N))
+
+    def c_struct(self):
+        return _capi.LmnLeafFormat(self.header, len(self.header), self.polyHeader, len(self.polyHeader), self.limbHeader, len(self.limbHeader))
+
+
+class MerkleTree:
+    """ref: core/tree.go:15-21, 76-219.  Built on the GPU (leaf serialisation + SHA-256), node hashes held on the host."""
+
+    def __init__(self, backend, leaves, leafFormat):
+        self.h = C.c_void_p()
+        fmt = leafFormat.c_struct()
+        check(_capi.lib().lmn_merkle_build(backend.ctx, leaves.h, C.byref(fmt), C.byref(self.h)))
+        self.depth = _capi.lib().lmn_merkle_depth(self.h)
+        self.n = _capi.lib().lmn_merkle_leaf_count(self.h)
+
+    def MerkleRoot(self):
+        out = C.create_string_buffer(32)
+        check(_capi.lib().lmn_merkle_root(self.h, out))
+        return out.raw
+
+    def LeafHash(self, index):
+        out = C.create_string_buffer(32)
+        check(_capi.lib().lmn_merkle_leaf_hash(self.h, int(index), out))
+        return out.raw
+
+    def GetMerklePath(self, index):
+        if not 0 <= int(index) < self.n:
+            raise IndexError("index %d out of bounds for %d leaves" % (index, self.n))   # tree.go:181-183
+        out = C.create_string_buffer(32 * max(1, self.depth))
+        check(_capi.lib().lmn_merkle_path(self.h, int(index), out))
+        return [out.raw[32 * i:32 * i + 32] for i in range(self.depth)]
+
+    def free(self):
+        if self.h:
+            _capi.lib().lmn_merkle_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def VerifyMerklePath(leafBytes, path, root, index):
+    """ref: core/tree.go:223-268 (host side; used by the tests as the reference's own acceptance check)"""
+    import hashlib
+    cur = hashlib.sha256(leafBytes).digest()
+    for sib in path:
+        cur = hashlib.sha256(cur + sib if index % 2 == 0 else sib + cur).digest()
+        index //= 2
+    return cur == root
+
+
+def LeafBytes(backend, leaves, index, leafFormat):
+    fmt = leafFormat.c_struct()
+    n = C.c_size_t()
+    check(_capi.lib().lmn_leaf_bytes(backend.ctx, leaves.h, int(index), C.byref(fmt), None, 0, C.byref(n)))
+    buf = C.create_string_buffer(n.value)
+    check(_capi.lib().lmn_leaf_bytes(backend.ctx, leaves.h, int(index), C.byref(fmt), buf, n.value, C.byref(n)))
+    return buf.raw
 
 
 class LigeroProver:
     """ref: fhe/ligero.go:32-37, 194-291"""
 
-    def __init__(self, committer, matrix, encoded):
+    def __init__(self, committer, matrix, encoded, leaves=None, tree=None):
         self.Committer, self.Matrix, self.EncodedMatrix = committer, matrix, encoded
+        self.Leaves, self.Tree = leaves, tree     # level-1 leaves kept on the device: the query stage becomes a gather
+        self.Root = tree.MerkleRoot() if tree is not None else None
 
     def Prove(self, rPt, bPt, queryIndices, backend):
         """rPt / bPt: plaintext limbs of backend.Encode(r) and backend.Encode(b) (ligero.go:202-221);
@@ -373,9 +451,14 @@ class LigeroProver:
         if len(idx) != md.Queries:
             raise ValueError("expected %d query indices" % md.Queries)
         queried = backend.NewStore(len(idx), lout)
-        check(lib.lmn_query_columns(backend.ctx, self.EncodedMatrix.h, _ptr(idx), len(idx), queried.h))
+        if self.Leaves is not None:
+            # the leaves of Commit are these columns already rescaled (the reference rescales them a second time, ligero.go:269-273)
+            check(lib.lmn_store_gather(backend.ctx, self.Leaves.h, _ptr(idx), len(idx), queried.h))
+        else:
+            check(lib.lmn_query_columns(backend.ctx, self.EncodedMatrix.h, _ptr(idx), len(idx), queried.h))
         queried.scale = backend.RescaleScale(backend.params.MaxLevel(), lout)
-        return EncryptedProof(LigeroMetadata(md.Rows, md.Cols, md.RhoInv, md.Queries), matR, matZ, queried)
+        paths = [self.Tree.GetMerklePath(int(i)) for i in idx] if self.Tree is not None else None   # ligero.go:275-279
+        return EncryptedProof(LigeroMetadata(md.Rows, md.Cols, md.RhoInv, md.Queries), matR, matZ, queried, paths, self.Root)
 
 
 class LigeroCommitter(LigeroMetadata):
@@ -388,10 +471,18 @@ class LigeroCommitter(LigeroMetadata):
             raise ValueError("securityBits must be positive")
         super().__init__(int(rows), int(cols), int(rhoInv), calculateQueries(securityBits, rhoInv))
 
-    def Commit(self, matrix, backend, zeroCol):
-        """Encode span of Commit (ligero.go:95-104).  The Merkle tree over the leaves (ligero.go:105-116) is
-        SURVEY 8(f) row 1 and stays with the host."""
+    def Commit(self, matrix, backend, zeroCol, leafFormat=None):
+        """ref: ligero.go:95-124.  Encode span, then (when a leaf framing is given) the "Merkle tree built" span: leaves =
+        encoded columns rescaled to level 1 (processLeafParallel, :126-183), serialised and hashed into core.NewTree.
+        Returns the prover; the reference's second return value is prover.Root."""
         if matrix.count != self.Cols:
             raise ValueError("matrix must hold one ciphertext per column")
         encoded = Encode(matrix, self.Rows, self.RhoInv, backend, zeroCol)
-        return LigeroProver(self, matrix, encoded)
+        if leafFormat is None:
+            return LigeroProver(self, matrix, encoded)
+        lout = min(1, backend.params.MaxLevel())
+        leaves = backend.NewStore(encoded.count, lout)
+        check(_capi.lib().lmn_commit_leaves(backend.ctx, encoded.h, leaves.h))
+        leaves.scale = backend.RescaleScale(backend.params.MaxLevel(), lout)
+        tree = MerkleTree(backend, leaves, leafFormat)
+        return LigeroProver(self, matrix, encoded, leaves, tree)

@@ -138,6 +138,13 @@ uint64_t orc_rescale_to_level1(const orc_params *P, const uint64_t *ct, uint64_t
 /* op counters of the last orc_fhe_ntt call (add, sub, mul) -- SURVEY App. D totals */
 void orc_fhe_ntt_counts(uint64_t *adds, uint64_t *subs, uint64_t *muls);
 
+/* ---- "Merkle tree built" span of Commit (merkle_oracle.c: core/tree.go, fhe/ligero.go:126-183) ---- */
+void orc_sha256(const uint8_t *data, uint64_t len, uint8_t out[32]);
+uint64_t orc_leaf_bytes(const uint64_t *ct, int nl, int N, const uint8_t *hdr, uint32_t hdr_len, const uint8_t *ph, uint32_t ph_len,
+                        const uint8_t *lh, uint32_t lh_len, uint8_t *out);
+uint32_t orc_merkle_tree(const uint8_t *leaf_hashes, uint32_t n, uint8_t *nodes);
+uint32_t orc_merkle_path(const uint8_t *nodes, uint32_t n, uint32_t index, uint8_t *out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -16,8 +16,8 @@ T_DEFAULT = 144115188075593729  # 2^57 - 2^18 + 1, ref: cmd/server/main.go:22, f
 
 
 def build(force=False):
-    src = os.path.join(_HERE, "lumenos_oracle.c")
-    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+    srcs = [os.path.join(_HERE, f) for f in ("lumenos_oracle.c", "merkle_oracle.c", "lumenos_oracle.h")]
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s"])
     return _SO
 
@@ -43,6 +43,10 @@ def lib():
     vp, i, u64 = C.c_void_p, C.c_int, C.c_uint64
     sig = {
         "orc_default_switches": (None, [C.POINTER(Switches)]),
+        "orc_sha256": (None, [C.c_char_p, u64, C.c_char_p]),
+        "orc_leaf_bytes": (u64, [_u64p, i, i, C.c_char_p, C.c_uint32, C.c_char_p, C.c_uint32, C.c_char_p, C.c_uint32, C.c_char_p]),
+        "orc_merkle_tree": (C.c_uint32, [C.c_char_p, C.c_uint32, C.c_char_p]),
+        "orc_merkle_path": (C.c_uint32, [C.c_char_p, C.c_uint32, C.c_uint32, C.c_char_p]),
         "orc_params_generate": (vp, [i, i, u64, C.POINTER(Switches)]),
         "orc_params_from_moduli": (vp, [i, i, _u64p, i, _u64p, u64, C.POINTER(Switches)]),
         "orc_params_free": (None, [vp]),
@@ -315,3 +319,44 @@ def core_encode(row, rho_inv, roots, t=T_DEFAULT):
     out = np.zeros(len(row) * rho_inv, np.uint64)
     lib().orc_core_encode(row, len(row), rho_inv, t, roots, out)
     return out
+
+
+# ---- "Merkle tree built" span of Commit (merkle_oracle.c) ----
+def sha256(data):
+    out = C.create_string_buffer(32)
+    lib().orc_sha256(bytes(data), len(data), out)
+    return out.raw
+
+
+def leaf_bytes(ct, header=b"", poly_header=b"", limb_header=b""):
+    """ct: [2][nl][N] level-1 ciphertext -> the leaf buffer of processLeafParallel (fhe/ligero.go:157-158)"""
+    ct = np.ascontiguousarray(ct, dtype=np.uint64)
+    nl, N = ct.shape[1], ct.shape[2]
+    n = len(header) + 2 * (len(poly_header) + nl * (len(limb_header) + 8 * N))
+    out = C.create_string_buffer(n)
+    got = lib().orc_leaf_bytes(ct, nl, N, header, len(header), poly_header, len(poly_header), limb_header, len(limb_header), out)
+    assert got == n
+    return out.raw
+
+
+class MerkleTree:
+    """core.NewTree over leaf buffers (tree.go:76-163)"""
+
+    def __init__(self, leaf_buffers):
+        self.n = len(leaf_buffers)
+        hashes = b"".join(sha256(b) for b in leaf_buffers)
+        total = lib().orc_merkle_tree(hashes, self.n, None)
+        self.nodes = C.create_string_buffer(32 * max(1, total))
+        lib().orc_merkle_tree(hashes, self.n, self.nodes)
+        self.total = total
+
+    def root(self):
+        return self.nodes.raw[32 * (self.total - 1):32 * self.total]
+
+    def leaf_hash(self, i):
+        return self.nodes.raw[32 * i:32 * i + 32]
+
+    def path(self, index):
+        out = C.create_string_buffer(32 * 40)
+        d = lib().orc_merkle_path(self.nodes, self.n, index, out)
+        return [out.raw[32 * j:32 * j + 32] for j in range(d)]

@@ -213,3 +213,73 @@ def test_store_roundtrip_and_errors():
     with pytest.raises(fhe.LumenosError, match="share one level"):
         be.Add((st, 0), (st, 1), (lvl1, 0))
     be.Close()
+
+
+LEAF_FORMATS = [("lattigo-like, odd header", b"\x01MetaData{json-ish}\x00\x07", None, None), ("bare", b"", b"", b""),
+                ("unaligned everywhere", b"abc", b"\x05", b"\x09\x08\x07"), ("aligned", b"A" * 48, None, None)]
+
+
+@pytest.mark.parametrize("logN,rows,cols,k,batch", [(6, 32, 16, 6, 10), (8, 256, 8, 4, 64), (12, 2048, 8, 3, 3), (6, 32, 8, 3, 64)])
+@pytest.mark.parametrize("fmt_id", range(len(LEAF_FORMATS)))
+def test_commit_merkle_bit_exact(logN, rows, cols, k, batch, fmt_id):
+    """Commit incl. the "Merkle tree built" span (fhe/ligero.go:105-116, 126-183; core/tree.go): leaves, leaf bytes, every leaf hash,
+    root and paths against the oracle; paths accepted by the reference's VerifyMerklePath rule; query stage from the leaves."""
+    from lumenos_b200 import fhe
+    S = scenario(logN, rows, cols, k)
+    P = S.P
+    be = S.backend()
+    be.SetBatch(batch)
+    _, hdr, ph, lh = LEAF_FORMATS[fmt_id]
+    N = 1 << logN
+    lf = fhe.LeafFormat.lattigo_like(hdr, 1, N) if ph is None else fhe.LeafFormat(hdr, ph, lh)
+    matrix = be.NewStore(cols).upload(S.cts)
+    zero = be.NewStore(1).upload(S.zero[None])
+    committer = fhe.LigeroCommitter(128, rows, cols, 2)
+    prover = committer.Commit(matrix, be, (zero, 0), leafFormat=lf)
+    n = 2 * cols
+    enc_want = P.fhe_encode(S.cts, 2, S.zero, S.roots)
+    leaves_want = [P.rescale_to_level1(enc_want[j])[0] for j in range(n)]
+    got_leaves = prover.Leaves.download()
+    bufs = []
+    for j in range(n):
+        assert_same(got_leaves[j], leaves_want[j], "leaf %d" % j)
+        bufs.append(O.leaf_bytes(leaves_want[j], lf.header, lf.polyHeader, lf.limbHeader))
+    for j in (0, n - 1):
+        assert fhe.LeafBytes(be, prover.Leaves, j, lf) == bufs[j], "serialised leaf %d" % j
+    tree = O.MerkleTree(bufs)
+    for j in range(n):
+        assert prover.Tree.LeafHash(j) == tree.leaf_hash(j), "leaf hash %d" % j
+    assert prover.Root == tree.root()
+    rng = np.random.default_rng(11)
+    idx = rng.integers(0, n, size=committer.Queries).astype(np.uint32)
+    idx[5] = idx[2]
+    proof = prover.Prove(S.rpt, S.bpt, idx, be)
+    qc = proof.QueriedCols.download()
+    assert proof.Root == tree.root() and len(proof.MerklePaths) == len(idx)
+    for i, ix in enumerate(idx[:48]):
+        assert_same(qc[i], leaves_want[ix], "QueriedCols[%d]" % i)
+        assert proof.MerklePaths[i] == tree.path(int(ix))
+        assert fhe.VerifyMerklePath(bufs[ix], proof.MerklePaths[i], proof.Root, int(ix))
+    with pytest.raises(IndexError):
+        prover.Tree.GetMerklePath(n)
+    be.Close()
+
+
+@pytest.mark.parametrize("n_leaves", [1, 2, 3, 5, 33])
+def test_merkle_odd_leaf_counts(n_leaves):
+    """core.NewTree pairs an unpaired last node with itself (tree.go:122-130): trees over 1, 3, 5, 33 leaves"""
+    from lumenos_b200 import fhe
+    S = scenario(6, 32, 16, 3)
+    be = S.backend()
+    rng = np.random.default_rng(n_leaves)
+    cts = rng.integers(0, 2**55, size=(n_leaves, 2, 2, 64), dtype=np.uint64)
+    leaves = be.NewStore(n_leaves, 1).upload(cts)
+    lf = fhe.LeafFormat.lattigo_like(b"hdr", 1, 64)
+    t = fhe.MerkleTree(be, leaves, lf)
+    bufs = [O.leaf_bytes(cts[j], lf.header, lf.polyHeader, lf.limbHeader) for j in range(n_leaves)]
+    want = O.MerkleTree(bufs)
+    assert t.MerkleRoot() == want.root()
+    for j in range(n_leaves):
+        assert t.GetMerklePath(j) == want.path(j)
+        assert fhe.VerifyMerklePath(bufs[j], t.GetMerklePath(j), t.MerkleRoot(), j)
+    be.Close()

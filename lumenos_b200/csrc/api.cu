@@ -2,6 +2,7 @@
 // drivers that sequence the kernels of kernels.cu on the context's CUDA stream.
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -36,6 +37,7 @@ struct lmn_ctx {
     DeviceTables T{};
     std::map<int, std::pair<KsConsts, KsConsts *>> ks;      // per level
     std::map<int, RescaleConsts *> rs;                      // per level
+    std::map<int, std::pair<RescaleChain, RescaleChain *>> rs_chain;   // per (from, to)
     std::map<u64, u64 *> galois;                            // galEl -> device evk (rows pre-scaled, see key_scale)
     int key_scale[MAX_DIGITS][MAX_LIMBS];                   // s(d, gm): evk rows of non-own (d, gm) carry the factor 2^s
     u64 *d_key_fm = nullptr;                                // [beta][k+np] 2^s in Montgomery form (0 = own row)
@@ -351,6 +353,7 @@ void lmn_ctx_destroy(lmn_ctx *c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     for (auto &kv : c->ks) cudaFree(kv.second.second);
     for (auto &kv : c->rs) cudaFree(kv.second);
+    for (auto &kv : c->rs_chain) cudaFree(kv.second.second);
     for (auto &kv : c->galois) cudaFree(kv.second);
     cudaFree(c->d_mods); cudaFree(c->d_twf); cudaFree(c->d_twi); cudaFree(c->d_twbf); cudaFree(c->d_twbi); cudaFree(c->ws_pt); cudaFree(c->ws_scalar);
     cudaFree(c->ws_col); cudaFree(c->ws_col2); cudaFree(c->ws_y); cudaFree(c->ws_acc); cudaFree(c->ws_idx);
@@ -699,8 +702,42 @@ static int innersum_jobs(lmn_ctx *c, int level, KsJobs &J, uint32_t n) {
     CK(cudaGetLastError());
     return 0;
 }
+static int get_rs_chain(lmn_ctx *c, int from, int to, const RescaleChain **host, const RescaleChain **dev) {
+    const int key = from * 64 + to;
+    auto it = c->rs_chain.find(key);
+    if (it == c->rs_chain.end()) {
+        RescaleChain R; memset(&R, 0, sizeof(R));
+        R.from = from; R.to = to;
+        for (int l = from; l > to; l--) {
+            const u64 ql = c->q[l];
+            R.half[l] = (ql - 1) >> 1;
+            for (int i = 0; i < l; i++) {
+                const u64 qi = c->q[i];
+                R.half_mod[l][i] = R.half[l] % qi;
+                const u64 inv = h_invmod(ql % qi, qi);
+                R.qlinv_w[l][i] = inv; R.qlinv_ws[l][i] = h_shoup(inv, qi);
+            }
+        }
+        RescaleChain *d = nullptr;
+        CK(cudaMalloc(&d, sizeof(R)));
+        CK(cudaMemcpy(d, &R, sizeof(R), cudaMemcpyHostToDevice));
+        it = c->rs_chain.emplace(key, std::make_pair(R, d)).first;
+    }
+    *host = &it->second.first; *dev = it->second.second;
+    return 0;
+}
 static int rescale_jobs_to(lmn_ctx *c, int from_level, int to_level, const KsJobs &J) {
     Launch L = c->L();
+    static const bool stepwise = getenv("LMN_RESCALE_STEPWISE") != nullptr;   // the one-limb-at-a-time evaluation, for A/B tests
+    // log N >= 12, two or more steps: the whole chain in the coefficient domain (3 launches instead of 3 per step)
+    if (!stepwise && blk_blocks(c->logn) > 0 && from_level - to_level >= 2 &&
+        (size_t)(from_level - to_level) * blk_blocks(c->logn) * 128 * 8 <= 96 * 1024 && 2 * (from_level + 1) <= MAX_LIMBS) {
+        const RescaleChain *Rh, *Rd;
+        if (int rc = get_rs_chain(c, from_level, to_level, &Rh, &Rd)) return rc;
+        launch_rescale_chain(L, c->T, Rd, *Rh, J);
+        CK(cudaGetLastError());
+        return 0;
+    }
     for (int l = from_level; l > to_level; l--) {
         const RescaleConsts *Rd;
         if (int rc = get_rs(c, l, &Rd)) return rc;

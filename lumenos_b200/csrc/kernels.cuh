@@ -45,6 +45,15 @@ struct RescaleConsts {   // DivRoundByLastModulusNTT from level l (limb l droppe
     u64 qlinv_w[MAX_LIMBS], qlinv_ws[MAX_LIMBS];
 };
 
+// the whole Rescale chain from level `from` down to level `to` (repeated DivRoundByLastModulusNTT, fhe/ligero.go:331-333,
+// :149-154, :271-273), evaluated in the coefficient domain: step l (limb l dropped) uses row l
+struct RescaleChain {
+    int from, to;
+    u64 half[MAX_LIMBS];                               // (q_l - 1) / 2
+    u64 half_mod[MAX_LIMBS][MAX_LIMBS];                // [l][i] half_l mod q_i
+    u64 qlinv_w[MAX_LIMBS][MAX_LIMBS], qlinv_ws[MAX_LIMBS][MAX_LIMBS];   // [l][i] q_l^-1 mod q_i (Shoup pair)
+};
+
 struct DeviceTables {
     int logn, n, k, np;
     const ModDev *mods;              // [k+np (+1 small-ring modulus)]
@@ -168,6 +177,11 @@ void launch_down_blk(const Launch &L, const DeviceTables &T, const KsConsts *Cd,
 // rescale step from `level`: acc slots c (raw block INTT of limb `level`) -> mu[c][i], then block NTT + apply in place
 void launch_rs_pre(const Launch &L, const DeviceTables &T, const RescaleConsts *Rd, int level, const KsJobs &J);
 void launch_rs_blk(const Launch &L, const DeviceTables &T, const RescaleConsts *Rd, int level, const KsJobs &J);
+// all Rescale steps from level Ch.from to Ch.to at once: one raw block INTT of every limb, the chain of rounded divisions
+// pointwise in the coefficient domain (k_rs_chain), one block NTT of the surviving limbs.  Bit-identical to the step-by-step
+// evaluation (every step is exact arithmetic mod q_i and the NTT is linear), with 2 (from + to + 2) limb transforms per
+// ciphertext instead of 2 sum_l (l + 1).
+void launch_rescale_chain(const Launch &L, const DeviceTables &T, const RescaleChain *Cd, const RescaleChain &Ch, const KsJobs &J);
 // block NTT + gadget MAC of the block pipeline (kernels_mac.cu)
 void launch_mac_blk(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch, const KsJobs &J, const u64 *evk);
 const char *kernels_mac_init();

@@ -308,6 +308,61 @@ __global__ void __launch_bounds__(256) k_rs_pre(const ModDev *mods, const ulongl
 }
 
 // ---------------------------------------------------------------------------------------------------
+// Chained rescale, pointwise part.  acc slot (c, i) holds the raw block INTT of limb i (i <= from) of poly c.  One thread
+// owns the S points n + r*M of the polynomial: limbs are visited from the top; limb i is finished (coupling, N^-1), then every
+// step l = from .. i+1 that drops a limb above it is applied, x_i <- (x_i - ((r_l mod q_i) - half_l mod q_i)) q_l^-1 with
+// r_l = x_l + half_l mod q_l the rounded residue of the dropped limb (ring.DivRoundByLastModulusNTT); a limb that will itself
+// be dropped leaves its r in shared memory, a surviving limb (i <= to) gets the forward coupling levels and goes to mu[c][i]
+// for the block NTT.  grid (M/128, 2, jobs), 128 threads, (from - to) * S * 128 words of shared memory.
+// ---------------------------------------------------------------------------------------------------
+constexpr int CHAIN_THREADS = 128;
+template <int S>
+__global__ void __launch_bounds__(CHAIN_THREADS) k_rs_chain(const ModDev *mods, const ulonglong2 *tw_fwd, const ulonglong2 *tw_inv,
+                                                            const RescaleChain *R, const KsJobs J) {
+    extern __shared__ __align__(16) u64 sm[];   // rr[l - to - 1][r][thread]
+    constexpr int LOGN = RA_LOGM + LogS<S>::v;
+    constexpr int M = RA_M;
+    const int from = R->from, to = R->to;
+    const int c = blockIdx.y, job = blockIdx.z;
+    const int n = blockIdx.x * CHAIN_THREADS + threadIdx.x;
+    const u64 *raw = J.acc + (size_t)job * J.acc_words + (((size_t)c * (from + 1)) << LOGN) + n;
+    u64 *out = J.mu + (size_t)job * J.mu_words + (((size_t)c * (to + 1)) << LOGN) + n;
+#pragma unroll 1
+    for (int i = from; i >= 0; i--) {
+        const ModDev mi = mods[i];
+        const u64 q = mi.q;
+        const FwdMod fm = {q, 0 - q, mi.q3};
+        u64 v[S];
+#pragma unroll
+        for (int r = 0; r < S; r++) v[r] = raw[((size_t)i << LOGN) + (size_t)r * M];
+        couple_inv<S>(v, tw_inv + ((size_t)i << LOGN), fm);
+#pragma unroll
+        for (int r = 0; r < S; r++) v[r] = mul_shoup(v[r], mi.ninv, mi.ninvs, q);
+        const int lmin = i > to ? i + 1 : to + 1;
+#pragma unroll 1
+        for (int l = from; l >= lmin; l--) {
+            const u64 hm = R->half_mod[l][i], w = R->qlinv_w[l][i], ws = R->qlinv_ws[l][i];
+            const u64 *rr = sm + ((size_t)(l - to - 1) * S) * CHAIN_THREADS + threadIdx.x;
+#pragma unroll
+            for (int r = 0; r < S; r++) {
+                const u64 t = sub_mod(barrett(rr[r * CHAIN_THREADS], q, mi.mu), hm, q);
+                v[r] = mul_shoup(v[r] + q - t, w, ws, q);
+            }
+        }
+        if (i > to) {
+            const u64 half = R->half[i];
+            u64 *rr = sm + ((size_t)(i - to - 1) * S) * CHAIN_THREADS + threadIdx.x;
+#pragma unroll
+            for (int r = 0; r < S; r++) rr[r * CHAIN_THREADS] = add_mod(v[r], half, q);
+        } else {
+            couple_fwd<S>(v, tw_fwd + ((size_t)i << LOGN), fm);
+#pragma unroll
+            for (int r = 0; r < S; r++) out[((size_t)i << LOGN) + (size_t)r * M] = v[r];
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
 // block NTT of mu[c][i] + epilogue.  grid (S*nlimbs, 2, ceil(jobs/jb)); one CTA owns block h of limb i of poly c for jb jobs.
 //   MODE 0  u = (acc - ext) P^-1 (k_mac has already added c0 P to acc_0), then AutomorphismHoisted + Add: col2 = col + pi(u).
 //           The permutation out[n] = in[index(n)] of the NTT domain maps blocks onto blocks (the top log2(S) bits of
@@ -315,6 +370,7 @@ __global__ void __launch_bounds__(256) k_rs_pre(const ModDev *mods, const ulongl
 //           while it adds the one destination block of col and stores it to col2 (coalesced, out of place).
 //   MODE 1  col2 = u  (no automorphism: the ring-switch key switch)
 //   MODE 2  Rescale: col_i = (col_i - ext) q_l^-1, in place
+//   MODE 3  col_i = NTT(mu[c][i]) (canonical), no epilogue operands: the tail of the chained rescale
 // All operands are 16 KB blocks that arrive by bulk copies: the transform's input of job j+1, and the epilogue's operands of
 // job j (acc block; destination block of col), requested right after the one barrier of job j that proves the landing
 // buffers free, so they land while the CTA transforms.
@@ -338,7 +394,7 @@ __global__ void __launch_bounds__(RA_THREADS, 2) k_blk_fwd(const ModDev *mods, c
     const FwdMod fm = {q, 0 - q, md.q3};
     const unsigned u = threadIdx.x;
     const int KP = k + np;   // k = limb stride of col (Q limbs of the context), KP = limb stride of acc
-    const u64 w = MODE == 2 ? R->qlinv_w[i] : C->pinv_w[i], ws = MODE == 2 ? R->qlinv_ws[i] : C->pinv_ws[i];
+    const u64 w = MODE == 3 ? 0 : MODE == 2 ? R->qlinv_w[i] : C->pinv_w[i], ws = MODE == 3 ? 0 : MODE == 2 ? R->qlinv_ws[i] : C->pinv_ws[i];
     const size_t blk = (size_t)h * M;
     int hd = 0;   // destination block of the automorphism
     if (MODE == 0) {
@@ -375,15 +431,26 @@ __global__ void __launch_bounds__(RA_THREADS, 2) k_blk_fwd(const ModDev *mods, c
                     mbar_expect_tx(&bars[0], BLK_BYTES);
                     bulk_g2s(landD, J.mu + (size_t)(job + 1) * J.mu_words + d_off, BLK_BYTES, &bars[0]);
                 }
-                mbar_expect_tx(&bars[1], MODE == 0 ? 2 * BLK_BYTES : BLK_BYTES);
-                bulk_g2s(landA, a_base + (size_t)job * a_words + a_off, BLK_BYTES, &bars[1]);
+                if (MODE != 3) {
+                    mbar_expect_tx(&bars[1], MODE == 0 ? 2 * BLK_BYTES : BLK_BYTES);
+                    bulk_g2s(landA, a_base + (size_t)job * a_words + a_off, BLK_BYTES, &bars[1]);
+                }
                 if (MODE == 0) bulk_g2s(landX, J.col + (size_t)job * J.col_words + col_off + (size_t)hd * M, BLK_BYTES, &bars[1]);
             }
         }, []() {});
         // a[r] = point 8u + r of the block, lazy
+        u64 *gout = (MODE >= 2 ? J.col : J.col2) + (size_t)job * J.col_words + col_off;
+        if (MODE == 3) {
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                ulonglong2 v;
+                v.x = barrett(a[2 * r], q, md.mu); v.y = barrett(a[2 * r + 1], q, md.mu);
+                reinterpret_cast<ulonglong2 *>(gout + blk + 8 * u)[r] = v;
+            }
+            continue;
+        }
         mbar_wait(&bars[1], ph);
         const ulonglong2 *av = reinterpret_cast<const ulonglong2 *>(landA) + 4 * u;
-        u64 *gout = (MODE == 2 ? J.col : J.col2) + (size_t)job * J.col_words + col_off;
 #pragma unroll
         for (int r = 0; r < 4; r++) {
             ulonglong2 v = av[r];
@@ -488,10 +555,33 @@ void launch_rs_blk(const Launch &L, const DeviceTables &T, const RescaleConsts *
     LMN_DISPATCH_S(SB, k_blk_fwd<SS, 2><<<g, RA_THREADS, BLK_FWD_SMEM, L.stream>>>(T.mods, T.twb_fwd, nullptr, Rd, J, 0u, level, T.k, T.np, J.jobs, jb));
 }
 
+void launch_rescale_chain(const Launch &L, const DeviceTables &T, const RescaleChain *Cd, const RescaleChain &Ch, const KsJobs &J) {
+    const int SB = blk_blocks(T.logn);
+    const int nl = Ch.from + 1;
+    BlkSlots A;
+    A.src = J.col; A.src_job_words = J.col_words; A.dst = J.acc; A.dst_job_words = J.acc_words; A.nslots = 2 * nl;
+    for (int c = 0; c < 2; c++)
+        for (int i = 0; i < nl; i++) { A.mod[c * nl + i] = i; A.src_limb[c * nl + i] = (uint32_t)(c * T.k + i); A.dst_limb[c * nl + i] = (uint32_t)(c * nl + i); }
+    launch_blk_intt(L, T, A, J.jobs, KID_RS_INTT);
+    {
+        LaunchScope scope(L, KID_RS_PRE);
+        const dim3 g(RA_M / CHAIN_THREADS, 2, J.jobs);
+        const size_t smem = (size_t)(Ch.from - Ch.to) * SB * CHAIN_THREADS * 8;
+        LMN_DISPATCH_S(SB, k_rs_chain<SS><<<g, CHAIN_THREADS, smem, L.stream>>>(T.mods, T.tw_fwd, T.tw_inv, Cd, J));
+    }
+    {
+        LaunchScope scope(L, KID_RS_APPLY);
+        const int keep = Ch.to + 1;
+        const int jb = pick_jb(SB * keep * 2, J.jobs);
+        const dim3 g(SB * keep, 2, (J.jobs + jb - 1) / jb);
+        LMN_DISPATCH_S(SB, k_blk_fwd<SS, 3><<<g, RA_THREADS, BLK_FWD_SMEM, L.stream>>>(T.mods, T.twb_fwd, nullptr, nullptr, J, 0u, keep, T.k, T.np, J.jobs, jb));
+    }
+}
+
 const char *kernels_blk_init() {
     cudaError_t e = cudaSuccess;
 #define SETSM(K) do { if (e == cudaSuccess) e = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BLK_FWD_SMEM); } while (0)
-#define SETS(SS) SETSM(k_blk_intt<SS>); SETSM((k_blk_fwd<SS, 0>)); SETSM((k_blk_fwd<SS, 1>)); SETSM((k_blk_fwd<SS, 2>));
+#define SETS(SS) SETSM(k_blk_intt<SS>); SETSM((k_blk_fwd<SS, 0>)); SETSM((k_blk_fwd<SS, 1>)); SETSM((k_blk_fwd<SS, 2>)); SETSM((k_blk_fwd<SS, 3>)); SETSM(k_rs_chain<SS>);
     SETS(2) SETS(4) SETS(8)
 #undef SETS
 #undef SETSM

@@ -138,7 +138,7 @@ def test_encode_bit_exact(logN, rows, cols, k):
 
 
 @pytest.mark.parametrize("logN,rows,cols,k,batch", [(6, 32, 16, 6, 10), (6, 64, 16, 5, 64), (8, 256, 64, 8, 64),
-                                                    (12, 4096, 8, 3, 6), (14, 16384, 8, 3, 64)])
+                                                    (12, 4096, 8, 3, 6), (12, 2048, 8, 6, 5), (14, 16384, 8, 3, 64)])
 def test_commit_prove_bit_exact(logN, rows, cols, k, batch):
     """TestLigeroE2E shape of flow (fhe/ligero_test.go:70-176): Commit -> Prove, every output ciphertext compared"""
     from lumenos_b200 import fhe

@@ -255,10 +255,142 @@ __global__ void __launch_bounds__(256) k_encode_pass(const EncPassArgs A) {
         A.out[(uint64_t)A.out_pos[slot] * A.ct_words + lane0 + lane] = sm[l * ENC_C + lane];
     }
 }
+// Register-resident variant for tiles of T = 8 V slots (V = 4 .. 32): the CTA's 8 warps split the tile, a warp's 32 threads are the
+// 32 coefficients of the chunk (every global access is one 256 B row), and each thread carries V slots through up to log2 V
+// butterfly levels per stage without touching shared memory; between stages the tile is re-dealt through shared memory so
+// that the next stage's index bits are register-local.  The scalars that follow the butterflies depend on (level, slot) only:
+// the CTA gathers its [levels][T] table of Shoup pairs once and reuses it for all its chunks (same limb).  Results are canonical
+// after every operation, exactly as in the tile kernel above.
+// x - q if x >= q else x, as a branch-free unsigned minimum (x - q wraps above x when x < q)
+__device__ __forceinline__ u64 csub_min(u64 x, u64 q) { const u64 t = x - q; return t < x ? t : x; }
+__device__ __forceinline__ int nth_unused_bit(unsigned used, int nth, int nbits) {
+    int r = 0, c = 0;
+    for (int b = 0; b < nbits; b++)
+        if (!((used >> b) & 1u)) { if (c == nth) r = b; c++; }
+    return r;
+}
+template <int LOGV>
+__global__ void __launch_bounds__(256, (LOGV <= 3 ? 3 : LOGV == 4 ? 2 : 1)) k_encode_pass_r(const EncPassArgs A, int chunks_per_cta) {
+    constexpr int V = 1 << LOGV, LT = LOGV + 3, T = 1 << LT;
+    constexpr int NST = (LT + LOGV - 1) / LOGV;
+    extern __shared__ __align__(16) u64 sm[];
+    ulonglong2 *stab = reinterpret_cast<ulonglong2 *>(sm);     // [LT][T]
+    u64 *xbuf = sm + 2 * LT * T;                                // [T][ENC_C]
+    const unsigned tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const uint32_t slot_base = blockIdx.y * A.tile_mul;
+    uint64_t lane0 = (uint64_t)blockIdx.x * chunks_per_cta * ENC_C;
+    const int limb = (int)((lane0 >> A.logn) % A.k);
+    const u64 q = A.mods[limb].q, q2 = 2 * q, q3 = 3 * q, nq = 0 - q;
+    {
+        const ulonglong2 *scal = A.scal + (size_t)limb * A.nscal;
+        for (int e = tid; e < LT * T; e += 256) {
+            const int lv = e >> LT, l = e & (T - 1);
+            const uint32_t id = A.scale_after[(size_t)(A.s0 + lv) * A.n + slot_base + (uint32_t)l * A.stride];
+            stab[e] = id ? __ldg(&scal[id]) : make_ulonglong2(0, 0);
+        }
+    }
+    // per stage: off[t] = 1 << (local index bit carried by register-index bit t): the stage's level bits first, then filler bits
+    // (lowest unused) when the stage has fewer than log2 V levels; wbase = the warp's 3 remaining bits
+    int off[NST][LOGV], wbase[NST];
+#pragma unroll
+    for (int st = 0; st < NST; st++) {
+        const int m = (LT - st * LOGV) < LOGV ? (LT - st * LOGV) : LOGV;
+        unsigned used = 0;
+#pragma unroll
+        for (int t = 0; t < LOGV; t++) {
+            if (t < m) {
+                const int b = (int)((A.lbits >> (4 * (st * LOGV + t))) & 15);
+                off[st][t] = 1 << b; used |= 1u << b;
+            }
+        }
+#pragma unroll
+        for (int t = 0; t < LOGV; t++)
+            if (t >= m) off[st][t] = 1 << nth_unused_bit(used, t - m, LT);
+        int wb = 0;
+#pragma unroll
+        for (int u = 0; u < 3; u++) wb |= (int)((wid >> u) & 1u) << nth_unused_bit(used, LOGV - m + u, LT);
+        wbase[st] = wb;
+    }
+    __syncthreads();
+#pragma unroll 1
+    for (int ch = 0; ch < chunks_per_cta; ch++, lane0 += ENC_C) {
+        u64 x[V];
+        int ls[V];
+#pragma unroll
+        for (int j = 0; j < V; j++) {
+            int l = wbase[0];
+#pragma unroll
+            for (int t = 0; t < LOGV; t++) if (j & (1 << t)) l += off[0][t];
+            ls[j] = l;
+            const uint32_t slot = slot_base + (uint32_t)l * A.stride;
+            const u64 *src;
+            if (A.in_by_pos) src = A.in + (uint64_t)A.out_pos[slot] * A.ct_words;
+            else src = (slot < A.in_count) ? A.in + (uint64_t)slot * A.ct_words : A.zero;
+            x[j] = src[lane0 + lane];
+        }
+#pragma unroll
+        for (int st = 0; st < NST; st++) {
+            if (st > 0) {
+                if (st > 1 || ch > 0) __syncthreads();     // readers of the previous deal are done
+#pragma unroll
+                for (int j = 0; j < V; j++) xbuf[ls[j] * ENC_C + lane] = x[j];
+                __syncthreads();
+#pragma unroll
+                for (int j = 0; j < V; j++) {
+                    int l = wbase[st];
+#pragma unroll
+                    for (int t = 0; t < LOGV; t++) if (j & (1 << t)) l += off[st][t];
+                    ls[j] = l;
+                    x[j] = xbuf[l * ENC_C + lane];
+                }
+            }
+#pragma unroll
+            for (int t = 0; t < LOGV; t++) {
+                const int lv = st * LOGV + t;
+                if (lv < LT) {
+                    const ulonglong2 *sc = stab + lv * T;
+#pragma unroll
+                    for (int j = 0; j < V; j++) {
+                        if (j & (1 << t)) continue;
+                        const int jj = j | (1 << t);
+                        // values stay in [0, 3q) inside the pass: the 3-product Shoup estimate (ntt_blk.cuh) takes any 64-bit input to
+                        // [0, 3q) by itself, an output without a scalar takes one conditional subtraction of 3q
+                        const u64 a = x[j], b = x[jj];
+                        u64 su = a + b, di = a - b + q3;
+                        const ulonglong2 w0 = sc[ls[j]], w1 = sc[ls[jj]];
+                        if (w0.x) su = mul_shoup_approx(su, w0.x, w0.y, nq); else su = csub_min(su, q3);
+                        if (w1.x) di = mul_shoup_approx(di, w1.x, w1.y, nq); else di = csub_min(di, q3);
+                        x[j] = su; x[jj] = di;
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < V; j++) {
+            const uint32_t slot = slot_base + (uint32_t)ls[j] * A.stride;
+            A.out[(uint64_t)A.out_pos[slot] * A.ct_words + lane0 + lane] = csub_min(csub_min(x[j], q2), q);   // canonical in HBM
+        }
+    }
+}
+static bool enc_tile_kernel_only() { static const bool v = getenv("LMN_ENCODE_TILE_KERNEL") != nullptr; return v; }
 void launch_encode_pass(const Launch &L, const EncPassArgs &A) {
     LaunchScope scope(L, KID_ENCODE);
     const uint64_t chunks = A.ct_words / ENC_C;
     const uint32_t tiles = A.n >> A.log_tile;
+    if (A.log_tile >= 5 && A.log_tile <= 8 && A.s1 - A.s0 == A.log_tile && !enc_tile_kernel_only()) {
+        const int per_limb = 1 << (A.logn - 5);
+        const int cpc = per_limb >= 4 ? 4 : per_limb;
+        const int T = 1 << A.log_tile;
+        const size_t smem = ((size_t)2 * A.log_tile * T + (size_t)T * ENC_C) * 8;
+        const dim3 g((unsigned)(chunks / cpc), tiles);
+        switch (A.log_tile) {
+            case 5: k_encode_pass_r<2><<<g, 256, smem, L.stream>>>(A, cpc); break;
+            case 6: k_encode_pass_r<3><<<g, 256, smem, L.stream>>>(A, cpc); break;
+            case 7: k_encode_pass_r<4><<<g, 256, smem, L.stream>>>(A, cpc); break;
+            default: k_encode_pass_r<5><<<g, 256, smem, L.stream>>>(A, cpc); break;
+        }
+        return;
+    }
     dim3 g((unsigned)chunks, tiles);
     size_t smem = ((size_t)ENC_C << A.log_tile) * 8;
     k_encode_pass<<<g, 256, smem, L.stream>>>(A);
@@ -747,7 +879,7 @@ const char *kernels_init() {
     SETSM(k_rs_intt<LG>); SETSM(k_rs_apply<LG>);
     SET_LOGN(6) SET_LOGN(8) SET_LOGN(10) SET_LOGN(12) SET_LOGN(13) SET_LOGN(14)
     SETSM((k_mac<6, 1>)); SETSM((k_mac<8, 1>)); SETSM((k_mac<10, 1>)); SETSM((k_mac<12, 1>)); SETSM((k_mac<13, 1>));
-    SETSM(k_encode_pass);
+    SETSM(k_encode_pass); SETSM(k_encode_pass_r<2>); SETSM(k_encode_pass_r<3>); SETSM(k_encode_pass_r<4>); SETSM(k_encode_pass_r<5>);
     SETSM((k_ring_decimate<12, 10>)); SETSM((k_ring_decimate<13, 10>)); SETSM((k_ring_decimate<14, 10>));
     SETSM((k_ring_decimate<8, 6>)); SETSM((k_ring_decimate<10, 6>)); SETSM((k_ring_decimate<10, 8>)); SETSM((k_ring_decimate<12, 8>));
 #undef SET_LOGN

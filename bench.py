@@ -32,6 +32,7 @@ sys.path.insert(0, ROOT)
 CONFIGS = {  # rows, cols, logN  (scripts/benchmark_server.sh:34-39, README.md:59-61)
     "A": (2048, 1024, 12), "B": (4096, 2048, 12), "C": (8192, 4096, 13), "D": (16384, 4096, 14),
 }
+NCU_MAC_TRAFFIC_PER_JOB_D = (3.611e9 + 0.924e9) / 256   # bytes per job, profiles/r1d_top_kernels.csv
 PUBLISHED_COMMIT_S = {"A": 1.03, "B": 2.04, "C": 9.17, "D": 18.79}  # "Commit eval": leaf rescale + Merkle (BASELINE.md:23)
 PUBLISHED_S = {"A": 14.77, "B": 36.80, "C": 179.93, "D": 397.85}  # Encode + Prove eval, m7i.8xlarge 32 vCPU
 RHO_INV, SECURITY_BITS = 2, 128
@@ -336,21 +337,27 @@ def main():
     mac_avg_s = mac_ms / max(1, mac_n) * 1e-3
     roofline = {"kernel": "k_mac (ModUp + NTT + gadget MAC; integer-bound, reported against HBM as the contract asks)", "bound": "hbm",
                 "achieved": mac_bytes / mac_avg_s / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": mac_bytes / mac_avg_s / 1e9 / hbm_peak,
-                "traffic": None, "peak_source": hbm_src, "avg_launch_ms": mac_avg_s * 1e3, "launches": mac_n,
+                "traffic": (NCU_MAC_TRAFFIC_PER_JOB_D * jobs if args.config == "D" and not args.cols_override else None),
+                "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of k_mac_rd<8> at 256 jobs per launch (profiles/r1d_top_kernels.csv), scaled per job; includes the base-converted digits written by k_modup_blk (an intermediate of the split pipeline, not in the algorithmic bytes)",
+                "peak_source": hbm_src, "avg_launch_ms": mac_avg_s * 1e3, "launches": mac_n,
                 "share_of_step": mac_ms / total_ms}
     # integer roofline of the same kernel: NTT butterflies per launch / measured register-resident butterfly ceiling
     pk = C.c_double()
     _capi.check(lib.lmn_bench_int_peak(be.ctx, C.byref(pk)))
     ntts = sum((k + np_) - min(np_, k - d * np_) for d in range(beta))   # (digit, target) pairs that need ModUp + NTT
-    mac_bfly = jobs * ntts * (N // 2) * logN
+    mac_levels = 11 if logN >= 12 else logN    # block pipeline: k_mac runs the 2048-point block transforms, the log2(N/2048) coupling levels are in k_modup
+    mac_bfly = jobs * ntts * (N // 2) * mac_levels
     roofline_int = {"kernel": "k_mac", "bound": "int", "achieved": mac_bfly / mac_avg_s / 1e9, "peak": pk.value / 1e9, "unit": "Gbutterfly/s",
                     "frac": mac_bfly / mac_avg_s / pk.value, "peak_source": "k_peak_bfly micro-kernel on this GPU, same run",
-                    "note": "counts only NTT butterflies (ModUp, MAC and reductions are extra integer work in the same kernel)"}
+                    "note": "counts only the NTT butterflies k_mac executes (%d of %d levels; the gadget MACs and reductions are extra integer work in the same kernel); ncu: sm__pipe_fmaheavy_cycles_active 72 %% (profiles/r1d_top_kernels.csv)" % (mac_levels, logN)}
     ctw = 2 * k * (Ns if G > 1 else N) * 8
     enc_bytes = ((cols + 1 + n) + (2 * n if n > 256 else 0)) * ctw   # pass 1 (+ pass 2, in place) per step
     enc_s = enc_ms / args.steps * 1e-3
     roofline_encode = {"kernel": "k_encode_pass (both passes of one Encode)", "bound": "hbm", "achieved": enc_bytes / enc_s / 1e9, "peak": hbm_peak,
-                       "unit": "GB/s", "frac": enc_bytes / enc_s / 1e9 / hbm_peak, "traffic": None, "ms_per_step": enc_s * 1e3,
+                       "unit": "GB/s", "frac": enc_bytes / enc_s / 1e9 / hbm_peak,
+                       "traffic": (91.0e9 if args.config == "D" and G == 1 and not args.cols_override else None),
+                       "traffic_source": "ncu --set full at config D: pass 1 13.3 GB read + 25.9 GB written, pass 2 25.8 + 26.0 GB (profiles/r1f_encode_kernels.csv)",
+                       "ms_per_step": enc_s * 1e3,
                        "algorithmic_min_bytes": (cols + 1 + n) * ctw, "share_of_step": enc_ms / total_ms}
 
     # kernel-class breakdown of one extra (untimed) step

@@ -8,8 +8,11 @@
 //   fhe::LigeroCommitter::Commit   fhe/ligero.go:95-124      fhe::LigeroProver::Prove  fhe/ligero.go:194-291
 //   fhe::matrixInnerSumEval        fhe/ligero.go:299-370     fhe::calculateQueries     fhe/ligero.go:65-71
 //
-// Keys, encryption, the merlin transcript and the Merkle tree stay with the host application (they are Lattigo / Go
-// territory in the reference); they enter here as data (plaintext limbs, Galois keys, the zero column, query indices).
+//   core::MerkleTree / NewTree     core/tree.go:15-21, 76-219  (Commit's "Merkle tree built" span, fhe/ligero.go:105-116)
+//
+// Keys, encryption and the merlin transcript stay with the host application (they are Lattigo / Go territory in the
+// reference); they enter here as data (plaintext limbs, Galois keys, the zero column, query indices, the framing bytes of
+// lattigo's Ciphertext.WriteTo).
 #pragma once
 #include <cmath>
 #include <cstdint>
@@ -202,9 +205,40 @@ inline std::unique_ptr<CiphertextStore> matrixInnerSumEval(CiphertextStore &matr
 
 struct LigeroMetadata { int Rows = 0, Cols = 0, RhoInv = 0, Queries = 0; };
 
-struct EncryptedProof {   // fhe/ligero.go:185-192 without the Merkle material (host)
+typedef std::vector<std::vector<uint8_t>> MerklePath;   // core/tree.go:33
+
+struct EncryptedProof {   // fhe/ligero.go:185-192
     LigeroMetadata Metadata;
     std::unique_ptr<CiphertextStore> MatR, MatZ, QueriedCols;
+    std::vector<MerklePath> MerklePaths;
+    std::vector<uint8_t> Root;
+};
+
+// framing of the leaf byte stream ct.WriteTo(buf) (fhe/ligero.go:157-158); see lmn_leaf_format
+struct LeafFormat {
+    std::vector<uint8_t> header, polyHeader, limbHeader;
+    lmn_leaf_format c() const {
+        return lmn_leaf_format{header.data(), (uint32_t)header.size(), polyHeader.data(), (uint32_t)polyHeader.size(), limbHeader.data(), (uint32_t)limbHeader.size()};
+    }
+};
+// core.MerkleTree (core/tree.go:15-21): built on the GPU by core.NewTree's rule, node hashes on the host
+class MerkleTree {
+  public:
+    MerkleTree(ServerBFV &be, CiphertextStore &leaves, const LeafFormat &f) { lmn_leaf_format c = f.c(); check(lmn_merkle_build(be.ctx(), leaves.handle(), &c, &h_)); }
+    ~MerkleTree() { if (h_) lmn_merkle_destroy(h_); }
+    MerkleTree(const MerkleTree &) = delete;
+    MerkleTree &operator=(const MerkleTree &) = delete;
+    std::vector<uint8_t> MerkleRoot() const { std::vector<uint8_t> r(32); check(lmn_merkle_root(h_, r.data())); return r; }
+    MerklePath GetMerklePath(uint32_t index) const {
+        const uint32_t d = lmn_merkle_depth(h_);
+        std::vector<uint8_t> flat(32 * (size_t)(d ? d : 1));
+        check(lmn_merkle_path(h_, index, flat.data()));     // "index %d out of bounds" -> Error, as tree.go:181-183
+        MerklePath p(d);
+        for (uint32_t i = 0; i < d; i++) p[i].assign(flat.begin() + 32 * i, flat.begin() + 32 * (i + 1));
+        return p;
+    }
+  private:
+    lmn_merkle *h_ = nullptr;
 };
 
 class LigeroCommitter;
@@ -213,6 +247,9 @@ class LigeroProver {   // fhe/ligero.go:32-37
     LigeroMetadata Committer;
     CiphertextStore *Matrix = nullptr;
     std::unique_ptr<CiphertextStore> EncodedMatrix;
+    std::unique_ptr<CiphertextStore> Leaves;     // level-1 leaves of Commit, kept on the device (query stage = gather)
+    std::unique_ptr<MerkleTree> Tree;
+    std::vector<uint8_t> Root;
 
     // Prove (fhe/ligero.go:194-291): rPt, bPt = limbs of backend.Encode(r), backend.Encode(b); queryIndices from the transcript
     EncryptedProof Prove(const uint64_t *rPt, const uint64_t *bPt, const std::vector<uint32_t> &queryIndices, ServerBFV &backend) {
@@ -224,7 +261,9 @@ class LigeroProver {   // fhe/ligero.go:32-37
         proof.MatZ = std::make_unique<CiphertextStore>(backend, Matrix->size(), lout);
         check(lmn_inner_product2(backend.ctx(), Matrix->handle(), rPt, bPt, (uint32_t)Committer.Rows, proof.MatR->handle(), proof.MatZ->handle()));
         proof.QueriedCols = std::make_unique<CiphertextStore>(backend, (uint32_t)queryIndices.size(), lout);
-        check(lmn_query_columns(backend.ctx(), EncodedMatrix->handle(), queryIndices.data(), (uint32_t)queryIndices.size(), proof.QueriedCols->handle()));
+        if (Leaves) check(lmn_store_gather(backend.ctx(), Leaves->handle(), queryIndices.data(), (uint32_t)queryIndices.size(), proof.QueriedCols->handle()));
+        else check(lmn_query_columns(backend.ctx(), EncodedMatrix->handle(), queryIndices.data(), (uint32_t)queryIndices.size(), proof.QueriedCols->handle()));
+        if (Tree) { for (uint32_t ix : queryIndices) proof.MerklePaths.push_back(Tree->GetMerklePath(ix)); proof.Root = Root; }   // ligero.go:275-279
         proof.MatR->Scale = proof.MatZ->Scale = proof.QueriedCols->Scale = backend.RescaleScale(backend.params().MaxLevel(), lout);
         return proof;
     }
@@ -237,13 +276,22 @@ class LigeroCommitter : public LigeroMetadata {   // fhe/ligero.go:26-63
         if (securityBits <= 0) throw std::invalid_argument("securityBits must be positive");
         Rows = rows; Cols = cols; RhoInv = rhoInv; Queries = calculateQueries(securityBits, rhoInv);
     }
-    // Commit (fhe/ligero.go:95-124): the Encode span; the Merkle tree over the leaves stays with the host
-    LigeroProver Commit(CiphertextStore &matrix, ServerBFV &backend, Operand zeroCol) {
+    // Commit (fhe/ligero.go:95-124): the Encode span and, when a leaf framing is given, the "Merkle tree built" span
+    // (processLeafParallel :126-183 + core.NewTree); the reference's second return value is prover.Root
+    LigeroProver Commit(CiphertextStore &matrix, ServerBFV &backend, Operand zeroCol, const LeafFormat *leafFormat = nullptr) {
         if ((int)matrix.size() != Cols) throw std::invalid_argument("matrix must hold one ciphertext per column");
         LigeroProver pr;
         pr.Committer = *this;
         pr.Matrix = &matrix;
         pr.EncodedMatrix = Encode(matrix, Rows, RhoInv, backend, zeroCol);
+        if (leafFormat) {
+            const int lout = std::min(1, backend.params().MaxLevel());
+            pr.Leaves = std::make_unique<CiphertextStore>(backend, pr.EncodedMatrix->size(), lout);
+            check(lmn_commit_leaves(backend.ctx(), pr.EncodedMatrix->handle(), pr.Leaves->handle()));
+            pr.Leaves->Scale = backend.RescaleScale(backend.params().MaxLevel(), lout);
+            pr.Tree = std::make_unique<MerkleTree>(backend, *pr.Leaves, *leafFormat);
+            pr.Root = pr.Tree->MerkleRoot();
+        }
         return pr;
     }
 };

@@ -69,7 +69,11 @@ int main(int argc, char **argv) {
         zeroCol.Upload(zero.data(), 0, 1);
         fhe::LigeroCommitter ligero(128, rows, cols, rhoInv);
         REQUIRE(ligero.Queries == 309, "queries = %d", ligero.Queries);
-        fhe::LigeroProver comm = ligero.Commit(matrix, server, {&zeroCol, 0});
+        fhe::LeafFormat lf;                         // lattigo-like framing: MetaData placeholder + u64 slice-length prefixes
+        lf.header = {'m', 'e', 't', 'a', 0x01, 2, 0, 0, 0, 0, 0, 0, 0};
+        lf.polyHeader.assign(8, 0); lf.polyHeader[0] = 2;
+        lf.limbHeader.assign(8, 0); for (int b = 0; b < 4; b++) lf.limbHeader[b] = (uint8_t)((u64)N >> (8 * b));
+        fhe::LigeroProver comm = ligero.Commit(matrix, server, {&zeroCol, 0}, &lf);
         std::vector<uint32_t> idx(ligero.Queries);
         for (int i = 0; i < ligero.Queries; i++) { seed = seed * 6364136223846793005ull + 1442695040888963407ull; idx[i] = (uint32_t)((seed >> 33) % n); }
         idx[9] = idx[4];
@@ -125,6 +129,33 @@ int main(int argc, char **argv) {
             unsigned __int128 acc = 0;
             for (int i = 0; i < rows; i++) acc = (acc + (unsigned __int128)dec[i] * (r[i] % Modulus)) % Modulus;
             REQUIRE((u64)acc == encR[idx[q]], "well-formedness R check failed for column %u", idx[q]);
+        }
+        // Commit's Merkle span: root and paths against the oracle's core.NewTree over the oracle's leaf buffers
+        {
+            std::vector<u64> leaf(l1w);
+            std::vector<uint8_t> hashes((size_t)n * 32), buf;
+            for (int j = 0; j < n; j++) {
+                orc_rescale_to_level1(P, enc_want.data() + ctw * j, leaf.data());
+                const u64 len = orc_leaf_bytes(leaf.data(), 2, N, lf.header.data(), (uint32_t)lf.header.size(), lf.polyHeader.data(), (uint32_t)lf.polyHeader.size(),
+                                               lf.limbHeader.data(), (uint32_t)lf.limbHeader.size(), nullptr);
+                buf.resize(len);
+                orc_leaf_bytes(leaf.data(), 2, N, lf.header.data(), (uint32_t)lf.header.size(), lf.polyHeader.data(), (uint32_t)lf.polyHeader.size(),
+                               lf.limbHeader.data(), (uint32_t)lf.limbHeader.size(), buf.data());
+                orc_sha256(buf.data(), len, hashes.data() + 32 * (size_t)j);
+            }
+            const uint32_t total = orc_merkle_tree(hashes.data(), (uint32_t)n, nullptr);
+            std::vector<uint8_t> nodes((size_t)total * 32), path(32 * 40);
+            orc_merkle_tree(hashes.data(), (uint32_t)n, nodes.data());
+            REQUIRE(proof.Root.size() == 32 && std::memcmp(proof.Root.data(), nodes.data() + 32 * (size_t)(total - 1), 32) == 0, "Merkle root differs from the oracle");
+            REQUIRE((int)proof.MerklePaths.size() == ligero.Queries, "one Merkle path per query");
+            for (int q = 0; q < 24; q++) {
+                const uint32_t d = orc_merkle_path(nodes.data(), (uint32_t)n, idx[q], path.data());
+                REQUIRE(proof.MerklePaths[q].size() == d, "path length");
+                for (uint32_t l = 0; l < d; l++) REQUIRE(std::memcmp(proof.MerklePaths[q][l].data(), path.data() + 32 * l, 32) == 0, "Merkle path %d level %u", q, l);
+            }
+            bool oob = false;
+            try { comm.Tree->GetMerklePath((uint32_t)n); } catch (const Error &) { oob = true; }
+            REQUIRE(oob, "GetMerklePath out of bounds must fail");
         }
         // error behaviour: missing key / bad shapes raise, they do not abort
         fhe::ServerBFV bare(field, params, 0);

@@ -138,3 +138,38 @@ def test_prove_full_ring_sampled_columns(logN, rows, k):
         assert np.array_equal(got[i], P.rescale_to_level1(Eh[i])[0]), "queried column %d differs from the oracle" % idx[i]
     assert np.array_equal(got[0], got[2])
     be.Close()
+
+
+@pytest.mark.parametrize("logN,n_leaves", [(12, 4096), (14, 8192)])
+def test_merkle_full_size_properties(logN, n_leaves):
+    """Commit's Merkle span at the leaf count and leaf size of configs B / D (8192 x 512 KiB): sampled leaf hashes against hashlib
+    over the downloaded ciphertext bytes, the root recomputed on the host from the GPU's leaf hashes (core.NewTree), and sampled
+    paths accepted by the reference's VerifyMerklePath rule (core/tree.go:223-268)."""
+    import hashlib
+    import torch
+    from lumenos_b200 import fhe
+    dev = torch.device("cuda", 0)
+    P = O.Params(logN, k=3)
+    N = P.N
+    be = _backend(P, O.field_roots_forward(128))
+    g = torch.Generator(device=dev).manual_seed(21)
+    L = torch.randint(0, 2**55, (n_leaves, 2, 2, N), generator=g, dtype=torch.int64, device=dev)
+    leaves = fhe.CiphertextStore(be, n_leaves, 1, wrap_ptr=L.data_ptr())
+    lf = fhe.LeafFormat.lattigo_like(b"\x07" * 45, 1, N)           # odd header length: every coefficient lands unaligned
+    torch.cuda.synchronize()
+    tree = fhe.MerkleTree(be, leaves, lf)
+    le = lambda a: a.cpu().numpy().astype("<u8").tobytes()  # noqa: E731
+    sample = [0, 1, n_leaves // 2 + 3, n_leaves - 1]
+    bufs = {}
+    for j in sample:
+        bufs[j] = lf.header + b"".join(lf.polyHeader + b"".join(lf.limbHeader + le(L[j, p, l]) for l in range(2)) for p in range(2))
+        assert tree.LeafHash(j) == hashlib.sha256(bufs[j]).digest(), "leaf hash %d" % j
+    lv = [tree.LeafHash(j) for j in range(n_leaves)]
+    while len(lv) > 1:
+        lv = [hashlib.sha256(lv[i] + (lv[i + 1] if i + 1 < len(lv) else lv[i])).digest() for i in range(0, len(lv), 2)]
+    assert tree.MerkleRoot() == lv[0]
+    for j in sample:
+        assert fhe.VerifyMerklePath(bufs[j], tree.GetMerklePath(j), tree.MerkleRoot(), j)
+    # a second build reproduces the root
+    assert fhe.MerkleTree(be, leaves, lf).MerkleRoot() == lv[0]
+    be.Close()

@@ -407,6 +407,24 @@ def main():
                          "note": "leaf rescale of all n encoded columns to level 1 + leaf serialisation + SHA-256 Merkle tree on the GPU; root read back to the host"}
         leaves.free(); qsel.free()
 
+    # ---- config E (experimental path, fhe/ring_switch.go): MatR / MatZ ring-switched to LogN = 10, beside the headline ----
+    ring_switch = None
+    if G == 1 and not args.no_commit and logN >= 12:
+        beta_full = (k + len(p) - 1) // len(p)
+        rs_evk = np.stack([rng.integers(0, m, size=(beta_full, 2, N), dtype=np.uint64) for m in list(q) + list(p)], axis=2)   # [beta][2][k+np][N]
+        rs = fhe.RingSwitchServer(be, rs_evk, 10)
+        del rs_evk
+        small_r, small_z = fhe.CiphertextStore(be, cols_loc, small=True), fhe.CiphertextStore(be, cols_loc, small=True)
+
+        def rs_step():
+            _capi.check(lib.lmn_ring_switch(be.ctx, matR.h, small_r.h))
+            _capi.check(lib.lmn_ring_switch(be.ctx, matZ.h, small_z.h))
+        rs_step()
+        rs_ms = timed(rs_step, 1)
+        ring_switch = {"ms": rs_ms, "ciphertexts": 2 * cols_loc, "to_logN": 10, "out_bytes": small_r.nbytes + small_z.nbytes,
+                       "note": "RingSwitchNew (fhe/ring_switch.go:106-113) of every MatR / MatZ ciphertext: level-0 key switch + decimation; config E = the headline step + this"}
+        small_r.free(); small_z.free()
+
     # ---- e2e: host buffers through the C ABI, H2D + D2H inside the timed region ----
     e2e = None
     if not args.no_e2e:
@@ -454,7 +472,7 @@ def main():
                        "sharding": "1 GPU" if G == 1 else "columns/%d for inner products + query rescale, coefficient slices/%d for Encode, all-to-all of queried slices" % (G, G),
                        "batch_jobs": args.batch},
             "e2e": e2e, "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "roofline_int": roofline_int,
-            "roofline_encode": roofline_encode, "kernel_breakdown_one_step": breakdown, "commit_merkle": commit_merkle, "cpu_baseline": cpu,
+            "roofline_encode": roofline_encode, "kernel_breakdown_one_step": breakdown, "commit_merkle": commit_merkle, "ring_switch_E": ring_switch, "cpu_baseline": cpu,
             "published_reference_s": PUBLISHED_S[args.config],
         }
         print(json.dumps(out))

@@ -20,7 +20,7 @@ struct ModDev {
     u64 ninv;   // N^-1 mod q
     u64 ninvs;  // Shoup companion of ninv
     u64 q3;     // 3q (lazy forward butterfly with the 3-product quotient estimate, ntt_r16.cuh)
-    u64 pad[2];
+    u64 pad[2]; // pad[0] stays 0: kernels read it as the "opaque zero" operand of FwdMod::z (ntt_blk.cuh)
 };
 
 __device__ __forceinline__ u64 csub(u64 x, u64 q) { return x >= q ? x - q : x; }

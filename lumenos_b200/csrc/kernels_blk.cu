@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(RA_THREADS, 3) k_blk_intt(const ModDev *mods, 
     const int slot = blockIdx.x / S, h = blockIdx.x % S;
     const int gm = A.mod[slot];
     const ModDev md = mods[gm];
-    const FwdMod fm = {md.q, 0 - md.q, md.q3};
+    const FwdMod fm = {md.q, 0 - md.q, md.q3, (unsigned)md.pad[0]};
     const unsigned u = threadIdx.x;
     const size_t soff = ((size_t)A.src_limb[slot] << LOGN) + (size_t)h * RA_M;
     const size_t doff = ((size_t)A.dst_limb[slot] << LOGN) + (size_t)h * RA_M + u;
@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(256) k_modup_blk(const ModDev *mods, const ulo
         if (a < nd) {
             const int gm = s0 + a;
             const u64 q = mods[gm].q;
-            const FwdMod fm = {q, 0 - q, mods[gm].q3};
+            const FwdMod fm = {q, 0 - q, mods[gm].q3, (unsigned)mods[gm].pad[0]};
             const u64 *src = y + ((size_t)gm << LOGN) + n;
 #pragma unroll
             for (int r = 0; r < S; r++) z[a][r] = src[(size_t)r * M];
@@ -148,7 +148,7 @@ __global__ void __launch_bounds__(256) k_modup_blk(const ModDev *mods, const ulo
         if (tix < nq && tix >= s0 && tix < s0 + nd) continue;   // own limbs are copied from the NTT-domain input
         const int gm = ks_mod_index(tix, nq, k);
         const u64 p = mods[gm].q, pinv = mods[gm].qinv;
-        const FwdMod fm = {p, 0 - p, mods[gm].q3};
+        const FwdMod fm = {p, 0 - p, mods[gm].q3, (unsigned)mods[gm].pad[0]};
         u64 vals[S];
         if (nd == 1) {
             // single-prime digit: centred lift (DecomposeAndSplit, decompLvl < 0), then the key-row scale 2^(e-64)
@@ -224,7 +224,7 @@ __global__ void __launch_bounds__(256) k_down_pre(const ModDev *mods, const ulon
         if (a < np) {
             const int gm = k + a;
             const u64 p = mods[gm].q;
-            const FwdMod fm = {p, 0 - p, mods[gm].q3};
+            const FwdMod fm = {p, 0 - p, mods[gm].q3, (unsigned)mods[gm].pad[0]};
 #pragma unroll
             for (int r = 0; r < S; r++) z[a][r] = accp[((size_t)a << LOGN) + (size_t)r * M];
             couple_inv<S>(z[a], tw_inv + ((size_t)gm << LOGN), fm);
@@ -251,7 +251,7 @@ __global__ void __launch_bounds__(256) k_down_pre(const ModDev *mods, const ulon
 #pragma unroll 1
     for (int i = 0; i < nq; i++) {
         const u64 q = mods[i].q, qinv = mods[i].qinv;
-        const FwdMod fm = {q, 0 - q, mods[i].q3};
+        const FwdMod fm = {q, 0 - q, mods[i].q3, (unsigned)mods[i].pad[0]};
         u64 cm[MAX_P];
 #pragma unroll
         for (int a = 0; a < MAX_P; a++) cm[a] = a < np ? C->md_c[i][a] : 0;
@@ -283,7 +283,7 @@ __global__ void __launch_bounds__(256) k_rs_pre(const ModDev *mods, const ulongl
     const int c = blockIdx.y, job = blockIdx.z;
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     const ModDev ml = mods[level];
-    const FwdMod fl = {ml.q, 0 - ml.q, ml.q3};
+    const FwdMod fl = {ml.q, 0 - ml.q, ml.q3, (unsigned)ml.pad[0]};
     const u64 *raw = J.acc + (size_t)job * J.acc_words + ((size_t)c << LOGN) + n;
     u64 v[S];
 #pragma unroll
@@ -296,7 +296,7 @@ __global__ void __launch_bounds__(256) k_rs_pre(const ModDev *mods, const ulongl
 #pragma unroll 1
     for (int i = 0; i < level; i++) {
         const u64 q = mods[i].q, qmu = mods[i].mu, hm = R->half_mod[i];
-        const FwdMod fm = {q, 0 - q, mods[i].q3};
+        const FwdMod fm = {q, 0 - q, mods[i].q3, (unsigned)mods[i].pad[0]};
         u64 vals[S];
 #pragma unroll
         for (int r = 0; r < S; r++) vals[r] = sub_mod(barrett(v[r], q, qmu), hm, q);
@@ -331,7 +331,7 @@ __global__ void __launch_bounds__(CHAIN_THREADS) k_rs_chain(const ModDev *mods, 
     for (int i = from; i >= 0; i--) {
         const ModDev mi = mods[i];
         const u64 q = mi.q;
-        const FwdMod fm = {q, 0 - q, mi.q3};
+        const FwdMod fm = {q, 0 - q, mi.q3, (unsigned)mi.pad[0]};
         u64 v[S];
 #pragma unroll
         for (int r = 0; r < S; r++) v[r] = raw[((size_t)i << LOGN) + (size_t)r * M];
@@ -391,7 +391,7 @@ __global__ void __launch_bounds__(RA_THREADS, 2) k_blk_fwd(const ModDev *mods, c
     const int i = blockIdx.x / S, h = blockIdx.x % S, c = blockIdx.y;
     const ModDev md = mods[i];
     const u64 q = md.q;
-    const FwdMod fm = {q, 0 - q, md.q3};
+    const FwdMod fm = {q, 0 - q, md.q3, (unsigned)md.pad[0]};
     const unsigned u = threadIdx.x;
     const int KP = k + np;   // k = limb stride of col (Q limbs of the context), KP = limb stride of acc
     const u64 w = MODE == 3 ? 0 : MODE == 2 ? R->qlinv_w[i] : C->pinv_w[i], ws = MODE == 3 ? 0 : MODE == 2 ? R->qlinv_ws[i] : C->pinv_ws[i];

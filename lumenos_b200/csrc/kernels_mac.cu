@@ -44,7 +44,7 @@ __global__ void __launch_bounds__(RA_THREADS, 2) k_mac_rd(const ModDev *mods, co
     const int gm = ks_mod_index(tix, nq, k);
     const ModDev md = mods[gm];
     const u64 p = md.q;
-    const FwdMod fm = {p, 0 - p, md.q3};
+    const FwdMod fm = {p, 0 - p, md.q3, (unsigned)md.pad[0]};
     const unsigned u = threadIdx.x;
     const size_t blk = (size_t)h * M;
     const int beta = C->beta;

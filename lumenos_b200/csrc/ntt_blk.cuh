@@ -36,10 +36,20 @@ __device__ __forceinline__ u64 ld_pin(const u64 *p) {
     return v;
 }
 
-struct FwdMod { u64 q, nq, q3; };   // modulus, 2^64 - q, 3q
+// modulus, 2^64 - q, 3q, and z = a zero that ptxas cannot see (read from ModDev.pad[0]).  ptxas lowers a two-operand add-with-carry
+// to either IADD3.X (ALU pipe) or IMAD.X (fmaheavy pipe) to "balance" the pipes; in these kernels fmaheavy is the saturated pipe
+// (IMAD.WIDE holds it 4 cycles), so the carry adds of the butterflies take z as a third register operand, a form only IADD3.X has.
+struct FwdMod { u64 q, nq, q3; unsigned z; };
+// a + b, the high half as a three-register add-with-carry (always IADD3.X)
+__device__ __forceinline__ u64 add64_alu(u64 a, u64 b, unsigned z) {
+    unsigned lo, hi;
+    asm("add.cc.u32 %0, %2, %3;\n\taddc.u32 %1, %4, %5;" : "=r"(lo), "=r"(hi) : "r"((unsigned)a), "r"((unsigned)b), "r"((unsigned)(a >> 32)), "r"((unsigned)(b >> 32)));
+    hi += z;
+    return ((u64)hi << 32) | lo;
+}
 
 // y * w - hi' * q  with  hi' in { floor(y*ws/2^64) - 1, floor(y*ws/2^64) } : result in [0, 3q) for any y < 2^64
-__device__ __forceinline__ u64 mul_shoup_approx(u64 y, u64 w, u64 ws, u64 nq) {
+__device__ __forceinline__ u64 mul_shoup_approx(u64 y, u64 w, u64 ws, u64 nq, unsigned z = 0) {
     u64 r;
     asm("{\n\t"
         ".reg .u32 yl, yh, wl, wh, sl, sh, nl, nh, alo, ahi, clo, chi, mlo, mhi, mc, hl, hh, tlo, thi;\n\t"
@@ -48,21 +58,21 @@ __device__ __forceinline__ u64 mul_shoup_approx(u64 y, u64 w, u64 ws, u64 nq) {
         "mul.wide.u32 a, yl, sh;\n\t" "mul.wide.u32 c, yh, sl;\n\t"
         "mov.b64 {alo, ahi}, a;\n\t" "mov.b64 {clo, chi}, c;\n\t"
         "add.cc.u32 mlo, alo, clo;\n\t" "addc.cc.u32 mhi, ahi, chi;\n\t" "addc.u32 mc, 0, 0;\n\t"
-        "mov.b64 ad, {mhi, mc};\n\t"
-        "mad.wide.u32 hi, yh, sh, ad;\n\t"
+        "mul.wide.u32 hi, yh, sh;\n\t"
         "mov.b64 {hl, hh}, hi;\n\t"
+        "add.cc.u32 hl, hl, mhi;\n\t" "addc.u32 hh, hh, mc;\n\t" "add.u32 hh, hh, %5;\n\t"
         "mul.wide.u32 t, yl, wl;\n\t" "mad.wide.u32 t, hl, nl, t;\n\t"
         "mov.b64 {tlo, thi}, t;\n\t"
         "mad.lo.u32 thi, yl, wh, thi;\n\t" "mad.lo.u32 thi, yh, wl, thi;\n\t"
         "mad.lo.u32 thi, hl, nh, thi;\n\t" "mad.lo.u32 thi, hh, nl, thi;\n\t"
         "mov.b64 %0, {tlo, thi};\n\t"
-        "}" : "=l"(r) : "l"(y), "l"(w), "l"(ws), "l"(nq));
+        "}" : "=l"(r) : "l"(y), "l"(w), "l"(ws), "l"(nq), "r"(z));
     return r;
 }
 __device__ __forceinline__ void bfly_ct3(u64 &x, u64 &y, const ulonglong2 w, const FwdMod &m) {
-    const u64 t = mul_shoup_approx(y, w.x, w.y, m.nq);
+    const u64 t = mul_shoup_approx(y, w.x, w.y, m.nq, m.z);
     y = x - t + m.q3;
-    x = x + t;
+    x = add64_alu(x, t, m.z);
 }
 
 constexpr int RA_THREADS = 256;
@@ -148,7 +158,7 @@ __device__ __forceinline__ void bfly_gs3(u64 &x, u64 &y, const ulonglong2 w, con
     const u64 s = x + y;
     const u64 d = x - y + q4;
     x = s >= q4 ? s - q4 : s;
-    y = mul_shoup_approx(d, w.x, w.y, m.nq);
+    y = mul_shoup_approx(d, w.x, w.y, m.nq, m.z);
 }
 template <class F>
 __device__ __forceinline__ void r8_inv_f(u64 (&a)[8], F tw_of, const FwdMod &m, u64 q4) {

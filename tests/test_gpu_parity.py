@@ -283,3 +283,28 @@ def test_merkle_odd_leaf_counts(n_leaves):
         assert t.GetMerklePath(j) == want.path(j)
         assert fhe.VerifyMerklePath(bufs[j], t.GetMerklePath(j), t.MerkleRoot(), j)
     be.Close()
+
+
+@pytest.mark.parametrize("logN,logNs,k", [(10, 8, 3), (12, 10, 3), (13, 10, 4), (14, 10, 3)])
+def test_ring_switch_large_rings_bit_exact(logN, logNs, k):
+    """RingSwitchNew (fhe/ring_switch.go:106-113) on level-1 ciphertexts of the rings of configs A-D -> LogN 10 (config E): the
+    level-0 key switch runs through the block pipeline (log N >= 12), then INTT / decimate / small NTT"""
+    from lumenos_b200 import fhe
+    P = O.Params(logN, k=k)
+    Ps = O.Params(logNs, q=P.q[:1], p=P.p)
+    sk, sks = P.keygen_sk(5), Ps.keygen_sk(9)
+    evk = P.keygen_ringswitch(sk, sks, logNs, 11)
+    roots = O.field_roots_forward(32)
+    params = fhe.BGVParameters(logN, P.q, P.p, P.t, P.psi_q, P.psi_p)
+    be = fhe.ServerBFV(fhe.PrimeField(P.t, roots), params)
+    be.SetRingSwitchServer(fhe.RingSwitchServer(be, evk, logNs))
+    rng = np.random.default_rng(logN)
+    n_ct = 5
+    cts = np.stack([np.stack([np.stack([rng.integers(0, int(P.q[l]), size=P.N, dtype=np.uint64) for l in range(2)]) for _ in range(2)]) for _ in range(n_ct)])
+    be.SetBatch(3)
+    st = be.NewStore(n_ct, 1).upload(cts)
+    got = be.RingSwitch().RingSwitchNew(st).download()
+    assert got.shape == (n_ct, 2, 1, 1 << logNs)
+    for j in range(n_ct):
+        assert_same(got[j], P.ringswitch(cts[j], evk, logNs), "ring switch ct %d" % j)
+    be.Close()

@@ -109,6 +109,9 @@ uint32_t lmn_plan_size(const lmn_plan *plan);
  * host); encoded receives cols*rho_inv max-level cts in the order fhe.NTT returns them. */
 int lmn_encode(lmn_ctx *ctx, const lmn_plan *plan, const lmn_store *matrix, const lmn_store *zero_ct,
                uint32_t zero_idx, lmn_store *encoded);
+/* Encode span of Commit with the matrix still in (pinned) host memory, laid out as lmn_store_upload expects: the upload into
+ * `matrix` (kept for Prove) runs limb by limb on the copy stream while the limbs that have landed are encoded */
+int lmn_encode_host(lmn_ctx *ctx, const lmn_plan *plan, const uint64_t *host_matrix, lmn_store *matrix, const lmn_store *zero, uint32_t zero_idx, lmn_store *encoded);
 /* replaces fhe.NTT(values, size, backend) (fhe/ntt.go:12-17) for len(values) == size == plan size:
  * out[i] = i-th ciphertext of the returned slice. in and out must be distinct stores. */
 int lmn_ntt(lmn_ctx *ctx, const lmn_plan *plan, const lmn_store *in, lmn_store *out);
@@ -142,6 +145,10 @@ int lmn_inner_product(lmn_ctx *ctx, const lmn_store *matrix, const uint64_t *pt_
 /* fused pair: InnerProduct(Matrix, r) and InnerProduct(Matrix, b) reading the matrix once (ligero.go:231-242) */
 int lmn_inner_product2(lmn_ctx *ctx, const lmn_store *matrix, const uint64_t *pt_r_host, const uint64_t *pt_b_host,
                        uint32_t rows, lmn_store *out_r, lmn_store *out_b);
+/* the same with the results also copied to caller-owned (pinned, lmn_host_alloc) host buffers batch by batch on the context's copy
+ * stream, behind the kernels of the following batches; complete when the context's stream is synchronised */
+int lmn_inner_product2_host(lmn_ctx *ctx, const lmn_store *matrix, const uint64_t *pt_r, const uint64_t *pt_b, uint32_t rows,
+                            lmn_store *out_r, lmn_store *out_b, uint64_t *host_r, uint64_t *host_b);
 /* optional ring switch of every level-1 ciphertext of `in` (ligero.go:336-342, ring_switch.go:106-113):
  * out is a level-0 store created with lmn_store_create_small */
 int lmn_store_create_small(lmn_ctx *ctx, uint32_t n_ct, lmn_store **out); /* [2][1][N'] per ct */

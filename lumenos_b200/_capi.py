@@ -52,6 +52,8 @@ SIGNATURES = {
     "lmn_plan_size": (C.c_uint32, [vp]),
     "lmn_plan_host_check": (C.c_int, [C.c_uint32, vp, C.c_uint64, vp, vp]),
     "lmn_encode": (C.c_int, [vp, vp, vp, vp, C.c_uint32, vp]),
+    "lmn_encode_host": (C.c_int, [vp, vp, vp, vp, vp, C.c_uint32, vp]),
+    "lmn_inner_product2_host": (C.c_int, [vp, vp, vp, vp, C.c_uint32, vp, vp, vp, vp]),
     "lmn_ntt": (C.c_int, [vp, vp, vp, vp]),
     "lmn_encode_lanes": (C.c_int, [vp, vp, vp, vp, vp, C.c_uint32]),
     "lmn_profile_enable": (C.c_int, [vp, C.c_uint32]),

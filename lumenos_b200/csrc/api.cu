@@ -32,6 +32,8 @@ struct lmn_ctx {
     std::vector<u64> q, p;                  // moduli: mod(i) = i < k ? q[i] : p[i-k]
     bool scalar_centered = true, round_nearest = true, rowswap_last = true;
     cudaStream_t own_stream = nullptr, stream = nullptr;
+    cudaStream_t copy_stream = nullptr;     // host <-> device copies that overlap the kernels (lmn_encode_host, lmn_inner_product2_host)
+    std::vector<cudaEvent_t> copy_events;   // pool, reused call after call
     ModDev *d_mods = nullptr;
     ulonglong2 *d_twf = nullptr, *d_twi = nullptr, *d_twbf = nullptr, *d_twbi = nullptr;
     DeviceTables T{};
@@ -309,6 +311,7 @@ int lmn_ctx_create(const lmn_params *P, int device, lmn_ctx **out) {
         std::copy(iv.begin(), iv.end(), twi.begin() + (size_t)i * N);
     }
     cudaError_t e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaMalloc(&c->d_mods, sizeof(ModDev) * KP);
     if (e == cudaSuccess) e = cudaMalloc(&c->d_twf, sizeof(ulonglong2) * KP * N);
     if (e == cudaSuccess) e = cudaMalloc(&c->d_twi, sizeof(ulonglong2) * KP * N);
@@ -360,6 +363,8 @@ void lmn_ctx_destroy(lmn_ctx *c) {
     cudaFree(c->d_rs_evk); cudaFree(c->d_small_mod); cudaFree(c->d_small_tw); cudaFree(c->d_key_fm); cudaFree(c->ws_mu);
     for (int i = 0; i < KID_COUNT; i++) for (auto &sp : c->prof.spans[i]) { cudaEventDestroy(sp.first); cudaEventDestroy(sp.second); }
     for (auto e : c->prof.pool) cudaEventDestroy(e);
+    for (cudaEvent_t e : c->copy_events) cudaEventDestroy(e);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
@@ -531,13 +536,14 @@ int lmn_plan_host_check(uint32_t n, const uint64_t *roots, uint64_t t, uint64_t 
 }
 
 // ---------------- Encode ----------------
-static int run_plan(lmn_ctx *c, const lmn_plan *p, const u64 *in, uint32_t in_count, const u64 *zero, u64 *out, int lane_logn = -1) {
+static int run_plan(lmn_ctx *c, const lmn_plan *p, const u64 *in, uint32_t in_count, const u64 *zero, u64 *out, int lane_logn = -1,
+                    uint64_t lane_off = 0, uint64_t lane_words = 0) {
     const EncodePlan &pl = p->pl;
     if (lane_logn < 0) lane_logn = c->logn;
     EncPassArgs A; memset(&A, 0, sizeof(A));
     A.mods = c->d_mods; A.scale_after = p->d_scale_after; A.out_pos = p->d_out_pos; A.scal = p->d_scal;
     A.nscal = (uint32_t)pl.scalars.size(); A.n = pl.n; A.k = c->k; A.logn = lane_logn; A.ct_words = 2 * (uint64_t)c->k << lane_logn;
-    A.out = out;
+    A.out = out; A.lane_off = lane_off; A.lane_words = lane_words;
     Launch L = c->L();
     if (pl.split == 0) {
         A.in = in; A.zero = zero; A.in_count = in_count; A.in_by_pos = 0;
@@ -570,6 +576,35 @@ int lmn_encode(lmn_ctx *c, const lmn_plan *p, const lmn_store *matrix, const lmn
     std::lock_guard<std::mutex> g(c->mu);
     cudaSetDevice(c->device);
     return run_plan(c, p, matrix->d, matrix->count, zero->d + zero_idx * zero->words(), enc->d);
+}
+static cudaEvent_t copy_event(lmn_ctx *c, size_t i) {
+    while (c->copy_events.size() <= i) { cudaEvent_t e; cudaEventCreateWithFlags(&e, cudaEventDisableTiming); c->copy_events.push_back(e); }
+    return c->copy_events[i];
+}
+// Encode with the matrix still on the host: the upload runs limb by limb (one strided copy of that limb of every column) on the
+// context's copy stream while the kernels encode the limbs that have landed (Encode is lane-wise, fhe/ntt.go touches one
+// (poly, limb, coefficient) lane at a time), so the span costs max(upload, kernels) instead of their sum.
+int lmn_encode_host(lmn_ctx *c, const lmn_plan *p, const uint64_t *host_matrix, lmn_store *matrix, const lmn_store *zero, uint32_t zero_idx, lmn_store *enc) {
+    if (!c || !p || !host_matrix || !matrix || !zero || !enc) return fail(LMN_ERR_INVALID, "null argument");
+    if (p->ctx != c || matrix->ctx != c || zero->ctx != c || enc->ctx != c) return fail(LMN_ERR_INVALID, "objects belong to different contexts");
+    const uint32_t Lm = (uint32_t)c->k - 1;
+    if (matrix->level != Lm || zero->level != Lm || enc->level != Lm) return fail(LMN_ERR_INVALID, "Encode operates on max-level ciphertexts");
+    if (matrix->count != p->cols || enc->count != p->pl.n || zero_idx >= zero->count) return fail(LMN_ERR_INVALID, "store sizes do not match the plan");
+    if (enc->d == matrix->d) return fail(LMN_ERR_INVALID, "encoded store must be distinct from the matrix");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    const size_t N = c->n, ctb = matrix->words() * 8, limbs = 2 * (size_t)c->k;
+    cudaEvent_t start = copy_event(c, limbs);
+    CK(cudaEventRecord(start, c->stream));
+    CK(cudaStreamWaitEvent(c->copy_stream, start, 0));      // earlier work on the context's stream may still read the matrix store
+    for (size_t l = 0; l < limbs; l++) {
+        CK(cudaMemcpy2DAsync(matrix->d + l * N, ctb, host_matrix + l * N, ctb, N * 8, matrix->count, cudaMemcpyHostToDevice, c->copy_stream));
+        cudaEvent_t ev = copy_event(c, l);
+        CK(cudaEventRecord(ev, c->copy_stream));
+        CK(cudaStreamWaitEvent(c->stream, ev, 0));
+        if (int rc = run_plan(c, p, matrix->d, matrix->count, zero->d + zero_idx * zero->words(), enc->d, -1, l * N, N)) return rc;
+    }
+    return 0;
 }
 int lmn_ntt(lmn_ctx *c, const lmn_plan *p, const lmn_store *in, lmn_store *out) {
     if (!c || !p || !in || !out) return fail(LMN_ERR_INVALID, "null argument");
@@ -748,8 +783,8 @@ static int rescale_jobs_to(lmn_ctx *c, int from_level, int to_level, const KsJob
 }
 
 // ---------------- Inner product eval ----------------
-int lmn_inner_product2(lmn_ctx *c, const lmn_store *matrix, const uint64_t *pt_r, const uint64_t *pt_b, uint32_t rows,
-                       lmn_store *out_r, lmn_store *out_b) {
+static int inner_product2_impl(lmn_ctx *c, const lmn_store *matrix, const uint64_t *pt_r, const uint64_t *pt_b, uint32_t rows,
+                               lmn_store *out_r, lmn_store *out_b, uint64_t *host_r, uint64_t *host_b) {
     if (!c || !matrix || !pt_r || !out_r || (pt_b && !out_b)) return fail(LMN_ERR_INVALID, "null argument");
     const int Lmax = c->k - 1, lout = std::min(1, Lmax);
     if ((int)matrix->level != Lmax) return fail(LMN_ERR_INVALID, "matrix must hold max-level ciphertexts");
@@ -779,9 +814,32 @@ int lmn_inner_product2(lmn_ctx *c, const lmn_store *matrix, const uint64_t *pt_r
         KsJobs Jr = jobs_view(c, 0, nc);
         launch_pack_out(L, c->T, Jr, lout + 1, out_r->d + c0 * out_words);
         if (pt_b) { KsJobs Jb = jobs_view(c, nc, nc); launch_pack_out(L, c->T, Jb, lout + 1, out_b->d + c0 * out_words); }
+        if (host_r) {
+            // this batch's results go home on the copy stream while the next batch computes
+            cudaEvent_t ev = copy_event(c, c0 / bc);
+            CK(cudaEventRecord(ev, c->stream));
+            CK(cudaStreamWaitEvent(c->copy_stream, ev, 0));
+            CK(cudaMemcpyAsync(host_r + c0 * out_words, out_r->d + c0 * out_words, nc * out_words * 8, cudaMemcpyDeviceToHost, c->copy_stream));
+            if (pt_b && host_b) CK(cudaMemcpyAsync(host_b + c0 * out_words, out_b->d + c0 * out_words, nc * out_words * 8, cudaMemcpyDeviceToHost, c->copy_stream));
+        }
+    }
+    if (host_r) {
+        cudaEvent_t done = copy_event(c, (matrix->count + bc - 1) / bc);
+        CK(cudaEventRecord(done, c->copy_stream));
+        CK(cudaStreamWaitEvent(c->stream, done, 0));    // whoever synchronises the context's stream also has the host copies
     }
     CK(cudaGetLastError());
     return 0;
+}
+int lmn_inner_product2(lmn_ctx *c, const lmn_store *matrix, const uint64_t *pt_r, const uint64_t *pt_b, uint32_t rows,
+                       lmn_store *out_r, lmn_store *out_b) {
+    return inner_product2_impl(c, matrix, pt_r, pt_b, rows, out_r, out_b, nullptr, nullptr);
+}
+// the same, with the level-1 results also copied to (pinned) host buffers batch by batch behind the kernels
+int lmn_inner_product2_host(lmn_ctx *c, const lmn_store *matrix, const uint64_t *pt_r, const uint64_t *pt_b, uint32_t rows,
+                            lmn_store *out_r, lmn_store *out_b, uint64_t *host_r, uint64_t *host_b) {
+    if (!host_r || (pt_b && !host_b)) return fail(LMN_ERR_INVALID, "null host buffer");
+    return inner_product2_impl(c, matrix, pt_r, pt_b, rows, out_r, out_b, host_r, host_b);
 }
 int lmn_inner_product(lmn_ctx *c, const lmn_store *matrix, const uint64_t *pt, uint32_t rows, lmn_store *out) {
     return lmn_inner_product2(c, matrix, pt, nullptr, rows, out, nullptr);

@@ -214,7 +214,7 @@ __global__ void __launch_bounds__(256) k_encode_pass(const EncPassArgs A) {
     extern __shared__ u64 sm[];  // [tile][ENC_C]
     const int tile_slots = 1 << A.log_tile;
     const uint32_t tile = blockIdx.y;
-    const uint64_t lane0 = (uint64_t)blockIdx.x * ENC_C;       // first lane (word offset inside a ciphertext)
+    const uint64_t lane0 = A.lane_off + (uint64_t)blockIdx.x * ENC_C;       // first lane (word offset inside a ciphertext)
     const int limb = (int)((lane0 >> A.logn) % A.k);
     const int lane = threadIdx.x & (ENC_C - 1);
     const int row0 = threadIdx.x / ENC_C, rows_per_it = blockDim.x / ENC_C;
@@ -278,7 +278,7 @@ __global__ void __launch_bounds__(256, (LOGV <= 3 ? 3 : LOGV == 4 ? 2 : 1)) k_en
     u64 *xbuf = sm + 2 * LT * T;                                // [T][ENC_C]
     const unsigned tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const uint32_t slot_base = blockIdx.y * A.tile_mul;
-    uint64_t lane0 = (uint64_t)blockIdx.x * chunks_per_cta * ENC_C;
+    uint64_t lane0 = A.lane_off + (uint64_t)blockIdx.x * chunks_per_cta * ENC_C;
     const int limb = (int)((lane0 >> A.logn) % A.k);
     const u64 q = A.mods[limb].q, q2 = 2 * q, q3 = 3 * q, nq = 0 - q;
     {
@@ -375,7 +375,7 @@ __global__ void __launch_bounds__(256, (LOGV <= 3 ? 3 : LOGV == 4 ? 2 : 1)) k_en
 static bool enc_tile_kernel_only() { static const bool v = getenv("LMN_ENCODE_TILE_KERNEL") != nullptr; return v; }
 void launch_encode_pass(const Launch &L, const EncPassArgs &A) {
     LaunchScope scope(L, KID_ENCODE);
-    const uint64_t chunks = A.ct_words / ENC_C;
+    const uint64_t chunks = (A.lane_words ? A.lane_words : A.ct_words) / ENC_C;   // lane ranges are whole limbs (or whole slices)
     const uint32_t tiles = A.n >> A.log_tile;
     if (A.log_tile >= 5 && A.log_tile <= 8 && A.s1 - A.s0 == A.log_tile && !enc_tile_kernel_only()) {
         const int per_limb = 1 << (A.logn - 5);

@@ -81,6 +81,7 @@ struct EncPassArgs {
     int k;                  // Q limbs per poly
     int logn;               // log2 of the coefficients per limb in these buffers (ring degree, or a slice of it)
     uint64_t ct_words;      // words per ciphertext (2*k*N)
+    uint64_t lane_off, lane_words;   // restrict the pass to words [lane_off, lane_off + lane_words) of every ciphertext (0, 0 = all)
 };
 
 // kernel classes (profiling / launch accounting)

@@ -308,3 +308,50 @@ def test_ring_switch_large_rings_bit_exact(logN, logNs, k):
     for j in range(n_ct):
         assert_same(got[j], P.ringswitch(cts[j], evk, logNs), "ring switch ct %d" % j)
     be.Close()
+
+
+@pytest.mark.parametrize("logN,rows,cols,k,batch", [(6, 32, 16, 4, 6), (12, 2048, 16, 3, 8)])
+def test_host_overlapped_entry_points_match(logN, rows, cols, k, batch):
+    """lmn_encode_host (limb-wise upload behind the Encode kernels) and lmn_inner_product2_host (batch-wise download behind the
+    inner-product kernels) give the bits of lmn_store_upload + lmn_encode and lmn_inner_product2 + lmn_store_download"""
+    import ctypes as C
+    from lumenos_b200 import _capi
+    S = scenario(logN, rows, cols, k)
+    be = S.backend()
+    be.SetBatch(batch)
+    lib = _capi.lib()
+    vp = C.c_void_p
+    n = 2 * cols
+    zero = be.NewStore(1).upload(S.zero[None])
+    ref_m = be.NewStore(cols).upload(S.cts)
+    ref_e = be.NewStore(n)
+    plan = be._plan(cols, 2)
+    _capi.check(lib.lmn_encode(be.ctx, plan, ref_m.h, zero.h, 0, ref_e.h))
+    r_r, r_z = be.NewStore(cols, 1), be.NewStore(cols, 1)
+    _capi.check(lib.lmn_inner_product2(be.ctx, ref_m.h, S.rpt.ctypes.data_as(vp), S.bpt.ctypes.data_as(vp), rows, r_r.h, r_z.h))
+    want_e, want_r, want_z = ref_e.download(), r_r.download(), r_z.download()
+
+    def pinned(nbytes):
+        p = vp()
+        _capi.check(lib.lmn_host_alloc(nbytes, C.byref(p)))
+        return p
+    h_m = pinned(S.cts.nbytes)
+    C.memmove(h_m, S.cts.ctypes.data, S.cts.nbytes)
+    h_r, h_z = pinned(want_r.nbytes), pinned(want_z.nbytes)
+    m2, e2 = be.NewStore(cols), be.NewStore(n)
+    o_r, o_z = be.NewStore(cols, 1), be.NewStore(cols, 1)
+    for rep in range(2):
+        C.memset(h_r, 0, want_r.nbytes); C.memset(h_z, 0, want_z.nbytes)
+        _capi.check(lib.lmn_encode_host(be.ctx, plan, h_m, m2.h, zero.h, 0, e2.h))
+        _capi.check(lib.lmn_inner_product2_host(be.ctx, m2.h, S.rpt.ctypes.data_as(vp), S.bpt.ctypes.data_as(vp), rows, o_r.h, o_z.h, h_r, h_z))
+        be.Synchronize()
+        assert_same(m2.download(), S.cts, "uploaded matrix")
+        assert_same(e2.download(), want_e, "EncodedMatrix via lmn_encode_host")
+        got_r = np.frombuffer((C.c_uint8 * want_r.nbytes).from_address(h_r.value), dtype=np.uint64).reshape(want_r.shape)
+        got_z = np.frombuffer((C.c_uint8 * want_z.nbytes).from_address(h_z.value), dtype=np.uint64).reshape(want_z.shape)
+        assert_same(got_r, want_r, "MatR in the host buffer")
+        assert_same(got_z, want_z, "MatZ in the host buffer")
+        assert_same(o_r.download(), want_r, "MatR store")
+    for p in (h_m, h_r, h_z):
+        lib.lmn_host_free(p)
+    be.Close()

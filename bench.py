@@ -378,14 +378,25 @@ def main():
 
     # ---- Commit's "Merkle tree built" span (fhe/ligero.go:105-116), reported beside the headline, not inside it ----
     commit_merkle = None
-    if G == 1 and not args.no_commit:
-        leaves = be.NewStore(n, lout)
+    if not args.no_commit:
+        n_loc = n // G
+        leaves = be.NewStore(n_loc, lout)
         lf = fhe.LeafFormat.lattigo_like(b"\x00" * 48, lout, N)     # 48 placeholder MetaData bytes + lattigo's u64 length prefixes
-        qsel = be.NewStore(len(my_idx), lout)
+        my_leaf_idx = np.ascontiguousarray([int(i) - rank * n_loc for i in qidx if rank * n_loc <= int(i) < (rank + 1) * n_loc] or [0], dtype=np.uint32)
+        qsel = be.NewStore(len(my_leaf_idx), lout)
 
         def commit_tail():
-            _capi.check(lib.lmn_commit_leaves(be.ctx, enc_store.h, leaves.h))
-            t = fhe.MerkleTree(be, leaves, lf)
+            if G == 1:
+                _capi.check(lib.lmn_commit_leaves(be.ctx, enc_store.h, leaves.h))
+                t = fhe.MerkleTree(be, leaves, lf)
+            else:
+                # coefficient slices -> this rank's block of whole encoded columns (all-to-all), local leaves + hashes, gathered tree
+                blk = sharding.exchange_encoded(enc_t, rank, G)
+                st = fhe.CiphertextStore(be, n_loc, k - 1, wrap_ptr=blk.data_ptr())
+                _capi.check(lib.lmn_commit_leaves(be.ctx, st.h, leaves.h))
+                t = sharding.commit_tree(be, leaves, lf, rank, G)
+                torch.cuda.current_stream(dev).synchronize()
+                st.free()
             root = t.MerkleRoot()
             t.free()
             return root
@@ -401,13 +412,14 @@ def main():
             if cnt.value:
                 cm_parts[name] = {"ms": round(ms.value, 3), "launches": cnt.value}
         _capi.check(lib.lmn_profile_enable(be.ctx, 0))
-        gq_ms = timed(lambda: _capi.check(lib.lmn_store_gather(be.ctx, leaves.h, my_idx.ctypes.data_as(vp), len(my_idx), qsel.h)), 1)
+        gq_ms = timed(lambda: _capi.check(lib.lmn_store_gather(be.ctx, leaves.h, my_leaf_idx.ctypes.data_as(vp), len(my_leaf_idx), qsel.h)), 1)
         leaf_len = len(lf.header) + 2 * (len(lf.polyHeader) + (lout + 1) * (len(lf.limbHeader) + 8 * N))
         sha_ms = cm_parts.get("k_sha256_leaves", {}).get("ms", 0.0)
         commit_merkle = {"ms": cm_ms, "leaves": n, "leaf_bytes": leaf_len, "kernels": cm_parts,
-                         "sha256_leaves_GBps": (n * leaf_len / (sha_ms * 1e-3) / 1e9) if sha_ms else None,
+                         "sha256_leaves_GBps": (n_loc * leaf_len / (sha_ms * 1e-3) / 1e9) if sha_ms else None,
                          "query_gather_from_leaves_ms": gq_ms, "published_reference_s": PUBLISHED_COMMIT_S.get(args.config),
-                         "note": "leaf rescale of all n encoded columns to level 1 + leaf serialisation + SHA-256 Merkle tree on the GPU; root read back to the host"}
+                         "note": "leaf rescale of all n encoded columns to level 1 + leaf serialisation + SHA-256 Merkle tree on the GPU; root read back to the host"
+                                 + ("" if G == 1 else "; %d GPUs: all-to-all of the encoded matrix from coefficient slices to column blocks, leaves and leaf hashes per rank, all-gather of the hashes, tree on every rank" % G)}
         leaves.free(); qsel.free()
 
     # ---- config E (experimental path, fhe/ring_switch.go): MatR / MatZ ring-switched to LogN = 10, beside the headline ----

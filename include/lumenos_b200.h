@@ -180,6 +180,10 @@ typedef struct lmn_merkle lmn_merkle;
 /* core.NewTree(leafs) (tree.go:76-163): SHA-256 leaf hashes, parents = SHA-256(left || right), an unpaired last node is paired
  * with itself.  Hashing runs on the GPU; the node hashes (32 B each) are kept on the host for root and paths. */
 int lmn_merkle_build(lmn_ctx *ctx, const lmn_store *leaves, const lmn_leaf_format *fmt, lmn_merkle **out);
+/* multi-GPU Commit (columns sharded by rank): each rank hashes the leaves of its own columns (32 bytes per leaf, to host memory),
+ * the hashes are gathered in column order and the tree is built from them; lmn_merkle_build == the two calls on one GPU */
+int lmn_leaf_hashes(lmn_ctx *ctx, const lmn_store *leaves, const lmn_leaf_format *fmt, uint8_t *out);
+int lmn_merkle_from_leaf_hashes(lmn_ctx *ctx, const uint8_t *hashes, uint32_t n_leaves, lmn_merkle **out);
 void lmn_merkle_destroy(lmn_merkle *tree);
 uint32_t lmn_merkle_leaf_count(const lmn_merkle *tree);
 uint32_t lmn_merkle_depth(const lmn_merkle *tree);                            /* hashes per path */

@@ -70,6 +70,8 @@ SIGNATURES = {
     "lmn_commit_leaves": (C.c_int, [vp, vp, vp]),
     "lmn_store_gather": (C.c_int, [vp, vp, vp, C.c_uint32, vp]),
     "lmn_merkle_build": (C.c_int, [vp, vp, C.POINTER(LmnLeafFormat), C.POINTER(vp)]),
+    "lmn_leaf_hashes": (C.c_int, [vp, vp, C.POINTER(LmnLeafFormat), vp]),
+    "lmn_merkle_from_leaf_hashes": (C.c_int, [vp, vp, C.c_uint32, C.POINTER(vp)]),
     "lmn_merkle_destroy": (None, [vp]),
     "lmn_merkle_leaf_count": (C.c_uint32, [vp]),
     "lmn_merkle_depth": (C.c_uint32, [vp]),

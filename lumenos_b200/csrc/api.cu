@@ -1084,6 +1084,40 @@ int lmn_leaf_bytes(lmn_ctx *c, const lmn_store *leaves, uint32_t index, const lm
     return rc;
 }
 
+// leaf hashes (level 0) computed on the device into d_nodes[0 .. n); caller holds the lock
+static cudaError_t hash_leaves_dev(lmn_ctx *c, const lmn_store *leaves, const LeafFormat &F, uint32_t *d_nodes) {
+    const uint32_t n = leaves->count;
+    u64 *ser = nullptr;
+    cudaError_t e = cudaMalloc(&ser, (size_t)n * F.padded_len);
+    if (e != cudaSuccess) return e;
+    Launch L = c->L();
+    launch_leaf_serialize(L, F, leaves->d, leaves->words(), n, ser);
+    launch_sha256_leaves(L, ser, F.padded_len, n, d_nodes);
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);   // `ser` is freed below
+    cudaFree(ser);
+    return e;
+}
+// parent levels on the device from the n leaf hashes in d_nodes, the whole tree copied to the host object
+static cudaError_t finish_tree(lmn_ctx *c, lmn_merkle *m, uint32_t *d_nodes, uint32_t total_nodes) {
+    Launch L = c->L();
+    for (size_t l = 0; l + 1 < m->level_cnt.size(); l++)
+        launch_sha256_nodes(L, d_nodes + (size_t)m->level_off[l] * 8, m->level_cnt[l], d_nodes + (size_t)m->level_off[l + 1] * 8);
+    cudaError_t e = cudaGetLastError();
+    m->nodes.resize((size_t)total_nodes * 32);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(m->nodes.data(), d_nodes, m->nodes.size(), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    return e;
+}
+static lmn_merkle *new_tree_shape(uint32_t n, uint32_t *total_nodes) {
+    auto *m = new lmn_merkle();
+    m->n_leaves = n;
+    uint32_t total = 0;
+    for (uint32_t cnt = n;; cnt = (cnt + 1) / 2) { m->level_off.push_back(total); m->level_cnt.push_back(cnt); total += cnt; if (cnt == 1) break; }
+    *total_nodes = total;
+    return m;
+}
+
 int lmn_merkle_build(lmn_ctx *c, const lmn_store *leaves, const lmn_leaf_format *fmt, lmn_merkle **out) {
     if (!c || !leaves || !fmt || !out) return fail(LMN_ERR_INVALID, "null argument");
     if (leaves->count == 0) return fail(LMN_ERR_INVALID, "no leaves");
@@ -1091,27 +1125,46 @@ int lmn_merkle_build(lmn_ctx *c, const lmn_store *leaves, const lmn_leaf_format 
     cudaSetDevice(c->device);
     LeafFormat F; uint8_t *d_hdr = nullptr;
     if (int rc = make_leaf_format(c, leaves, fmt, F, &d_hdr)) return rc;
-    const uint32_t n = leaves->count;
-    auto *m = new lmn_merkle();
-    m->n_leaves = n;
     uint32_t total_nodes = 0;
-    for (uint32_t cnt = n;; cnt = (cnt + 1) / 2) { m->level_off.push_back(total_nodes); m->level_cnt.push_back(cnt); total_nodes += cnt; if (cnt == 1) break; }
-    u64 *ser = nullptr; uint32_t *d_nodes = nullptr;
-    cudaError_t e = cudaMalloc(&ser, (size_t)n * F.padded_len);
-    if (e == cudaSuccess) e = cudaMalloc(&d_nodes, (size_t)total_nodes * 32);
-    if (e == cudaSuccess) {
-        Launch L = c->L();
-        launch_leaf_serialize(L, F, leaves->d, leaves->words(), n, ser);
-        launch_sha256_leaves(L, ser, F.padded_len, n, d_nodes);
-        for (size_t l = 0; l + 1 < m->level_cnt.size(); l++)
-            launch_sha256_nodes(L, d_nodes + (size_t)m->level_off[l] * 8, m->level_cnt[l], d_nodes + (size_t)m->level_off[l + 1] * 8);
-        e = cudaGetLastError();
-        m->nodes.resize((size_t)total_nodes * 32);
-        if (e == cudaSuccess) e = cudaMemcpyAsync(m->nodes.data(), d_nodes, m->nodes.size(), cudaMemcpyDeviceToHost, c->stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
-    }
-    cudaFree(ser); cudaFree(d_nodes); cudaFree(d_hdr);
+    lmn_merkle *m = new_tree_shape(leaves->count, &total_nodes);
+    uint32_t *d_nodes = nullptr;
+    cudaError_t e = cudaMalloc(&d_nodes, (size_t)total_nodes * 32);
+    if (e == cudaSuccess) e = hash_leaves_dev(c, leaves, F, d_nodes);
+    if (e == cudaSuccess) e = finish_tree(c, m, d_nodes, total_nodes);
+    cudaFree(d_nodes); cudaFree(d_hdr);
     if (e != cudaSuccess) { delete m; return fail(LMN_ERR_CUDA, std::string("merkle build: ") + cudaGetErrorString(e)); }
+    *out = m;
+    return 0;
+}
+// multi-GPU Commit: every rank hashes the leaves of its own columns ...
+int lmn_leaf_hashes(lmn_ctx *c, const lmn_store *leaves, const lmn_leaf_format *fmt, uint8_t *out) {
+    if (!c || !leaves || !fmt || !out) return fail(LMN_ERR_INVALID, "null argument");
+    if (leaves->count == 0) return fail(LMN_ERR_INVALID, "no leaves");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    LeafFormat F; uint8_t *d_hdr = nullptr;
+    if (int rc = make_leaf_format(c, leaves, fmt, F, &d_hdr)) return rc;
+    uint32_t *d_nodes = nullptr;
+    cudaError_t e = cudaMalloc(&d_nodes, (size_t)leaves->count * 32);
+    if (e == cudaSuccess) e = hash_leaves_dev(c, leaves, F, d_nodes);
+    if (e == cudaSuccess) e = cudaMemcpy(out, d_nodes, (size_t)leaves->count * 32, cudaMemcpyDeviceToHost);
+    cudaFree(d_nodes); cudaFree(d_hdr);
+    if (e != cudaSuccess) return fail(LMN_ERR_CUDA, std::string("leaf hashes: ") + cudaGetErrorString(e));
+    return 0;
+}
+// ... and the tree is built from the gathered leaf hashes (in column order)
+int lmn_merkle_from_leaf_hashes(lmn_ctx *c, const uint8_t *hashes, uint32_t n, lmn_merkle **out) {
+    if (!c || !hashes || !out || n == 0) return fail(LMN_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    uint32_t total_nodes = 0;
+    lmn_merkle *m = new_tree_shape(n, &total_nodes);
+    uint32_t *d_nodes = nullptr;
+    cudaError_t e = cudaMalloc(&d_nodes, (size_t)total_nodes * 32);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_nodes, hashes, (size_t)n * 32, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) e = finish_tree(c, m, d_nodes, total_nodes);
+    cudaFree(d_nodes);
+    if (e != cudaSuccess) { delete m; return fail(LMN_ERR_CUDA, std::string("merkle from hashes: ") + cudaGetErrorString(e)); }
     *out = m;
     return 0;
 }

@@ -369,10 +369,14 @@ class LeafFormat:
 class MerkleTree:
     """ref: core/tree.go:15-21, 76-219.  Built on the GPU (leaf serialisation + SHA-256), node hashes held on the host."""
 
-    def __init__(self, backend, leaves, leafFormat):
+    def __init__(self, backend, leaves, leafFormat, leafHashes=None):
+        """leafHashes: 32*n bytes of leaf hashes gathered from all ranks (multi-GPU Commit) instead of a leaves store"""
         self.h = C.c_void_p()
-        fmt = leafFormat.c_struct()
-        check(_capi.lib().lmn_merkle_build(backend.ctx, leaves.h, C.byref(fmt), C.byref(self.h)))
+        if leafHashes is not None:
+            check(_capi.lib().lmn_merkle_from_leaf_hashes(backend.ctx, bytes(leafHashes), len(leafHashes) // 32, C.byref(self.h)))
+        else:
+            fmt = leafFormat.c_struct()
+            check(_capi.lib().lmn_merkle_build(backend.ctx, leaves.h, C.byref(fmt), C.byref(self.h)))
         self.depth = _capi.lib().lmn_merkle_depth(self.h)
         self.n = _capi.lib().lmn_merkle_leaf_count(self.h)
 
@@ -413,6 +417,14 @@ def VerifyMerklePath(leafBytes, path, root, index):
         cur = hashlib.sha256(cur + sib if index % 2 == 0 else sib + cur).digest()
         index //= 2
     return cur == root
+
+
+def LeafHashes(backend, leaves, leafFormat):
+    """SHA-256 of every leaf of a (rank-local) leaves store: 32*count bytes"""
+    fmt = leafFormat.c_struct()
+    out = C.create_string_buffer(32 * leaves.count)
+    check(_capi.lib().lmn_leaf_hashes(backend.ctx, leaves.h, C.byref(fmt), out))
+    return out.raw
 
 
 def LeafBytes(backend, leaves, index, leafFormat):

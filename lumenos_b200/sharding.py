@@ -3,9 +3,11 @@
 SURVEY 8(e): the inner products, the query rescale and the leaf rescale are independent per column ciphertext
 (fhe/ligero.go:318-345 has no cross-ciphertext reduction), so columns shard by rank with no data-path collective.
 Encode is independent per (poly, limb, coefficient) lane (fhe/ntt.go applies only ct+ct, ct-ct, ct*scalar), so it shards
-by coefficient slice.  The single real exchange is turning the coefficient slices of the few hundred QUERIED encoded
-columns into whole ciphertexts on the rank that rescales them: one all-to-all (NCCL over NVLink on the GPU box,
-gloo in the CPU tests)."""
+by coefficient slice.  The real exchanges of the path are therefore layout changes of the ENCODED matrix from coefficient
+slices to whole ciphertexts: of the few hundred queried columns (exchange_queried, Prove without a leaves store) or of all
+columns (exchange_encoded, Commit's leaf rescale + Merkle span, after which the query stage is a local gather from the
+leaves), plus the gather of 32-byte leaf hashes for the tree (commit_tree).  All-to-all / all-gather over NCCL (NVLink) on
+the GPU box, gloo in the CPU tests."""
 import torch
 import torch.distributed as dist
 
@@ -49,3 +51,42 @@ def exchange_queried(enc_slice, query_idx, rank, world, group=None):
     _, two, k, ns = enc_slice.shape
     # recv is [source rank][my query][poly][limb][slice]; coefficient index = source * ns + c
     return recv.view(world, len(mine), two, k, ns).permute(1, 2, 3, 0, 4).reshape(len(mine), two, k, world * ns).contiguous()
+
+
+def exchange_encoded(enc_slice, rank, world, group=None, chunks=8):
+    """enc_slice: [n, 2, k, N/world], this rank's coefficient slice of the whole encoded matrix.
+    Returns [n/world, 2, k, N]: whole ciphertexts of the encoded columns column_range(n, rank, world), which this rank
+    rescales to leaves, hashes and later serves queries from.  Runs as `chunks` all-to-alls to bound the staging buffers."""
+    n, two, k, ns = enc_slice.shape
+    lo, hi = column_range(n, rank, world)
+    per = hi - lo
+    out = torch.empty((per, two, k, world * ns), dtype=enc_slice.dtype, device=enc_slice.device)
+    if world == 1:
+        out.copy_(enc_slice)
+        return out
+    chunks = max(1, min(chunks, per))
+    while per % chunks:
+        chunks -= 1
+    sub = per // chunks
+    ov = out.view(per, two, k, world, ns)
+    for c in range(chunks):
+        # to rank d: its columns d*per + [c*sub, (c+1)*sub) of my slice; from rank s: slice s of my columns [c*sub, (c+1)*sub)
+        send = torch.stack([enc_slice[d * per + c * sub: d * per + (c + 1) * sub] for d in range(world)])
+        recv = torch.empty_like(send)
+        dist.all_to_all_single(recv, send, group=group)
+        ov[c * sub:(c + 1) * sub].copy_(recv.permute(1, 2, 3, 0, 4))
+    return out
+
+
+def commit_tree(backend, leaves, leaf_format, rank, world, group=None):
+    """Commit's Merkle span on column-sharded leaves (fhe/ligero.go:105-116): every rank hashes its own leaves on its GPU, the
+    32-byte hashes are all-gathered in column order and every rank builds the same tree (root, paths) from them."""
+    from . import fhe
+    mine = fhe.LeafHashes(backend, leaves, leaf_format)
+    if world == 1:
+        return fhe.MerkleTree(backend, None, None, leafHashes=mine)
+    dev = torch.device("cuda", backend.device) if dist.get_backend(group) == "nccl" else torch.device("cpu")
+    local = torch.frombuffer(bytearray(mine), dtype=torch.uint8).to(dev)
+    gathered = [torch.empty_like(local) for _ in range(world)]
+    dist.all_gather(gathered, local, group=group)
+    return fhe.MerkleTree(backend, None, None, leafHashes=b"".join(bytes(t.cpu().numpy().tobytes()) for t in gathered))

@@ -52,6 +52,31 @@ gr, gz = mr.download(), mz.download()
 for j in range(a, b):
     assert np.array_equal(gr[j - a], P.inner_sum_eval_column(S.cts[j], S.rpt, S.rows, S.gal, S.evks)[0])
     assert np.array_equal(gz[j - a], P.inner_sum_eval_column(S.cts[j], S.bpt, S.rows, S.gal, S.evks)[0])
+# Commit's Merkle span, sharded: slices -> column blocks, local leaf rescale + leaf hashes, gathered tree == the 1-GPU tree
+n = 2 * S.cols
+blk = sharding.exchange_encoded(e_sl, rank, world, chunks=2)
+a2, b2 = sharding.column_range(n, rank, world)
+assert np.array_equal(blk.cpu().numpy().astype(np.uint64), want_enc[a2:b2]), "column block of the encoded matrix differs"
+est = fhe.CiphertextStore(be, b2 - a2, P.k - 1, wrap_ptr=blk.data_ptr())
+leaves = be.NewStore(b2 - a2, 1)
+_capi.check(lib.lmn_commit_leaves(be.ctx, est.h, leaves.h))
+lf = fhe.LeafFormat.lattigo_like(b"hdr-bytes", 1, P.N)
+tree = sharding.commit_tree(be, leaves, lf, rank, world)
+from oracle import oracle as O
+bufs = [O.leaf_bytes(P.rescale_to_level1(want_enc[j])[0], lf.header, lf.polyHeader, lf.limbHeader) for j in range(n)]
+want_tree = O.MerkleTree(bufs)
+assert tree.MerkleRoot() == want_tree.root(), "sharded Merkle root differs from the oracle"
+for j in (0, a2, b2 - 1, n - 1):
+    assert tree.GetMerklePath(j) == want_tree.path(j)
+# query stage from the local leaves
+own = [int(q) for q in qidx if a2 <= q < b2]
+if own:
+    sel = be.NewStore(len(own), 1)
+    li = np.array([q - a2 for q in own], dtype=np.uint32)
+    _capi.check(lib.lmn_store_gather(be.ctx, leaves.h, li.ctypes.data_as(vp), len(own), sel.h))
+    gs = sel.download()
+    for t, q in enumerate(own):
+        assert np.array_equal(gs[t], P.rescale_to_level1(want_enc[q])[0])
 be.Close()
 dist.barrier()
 print("rank", rank, "ok")

@@ -25,6 +25,11 @@ full = S.exchange_queried(enc[..., lo:hi].contiguous(), qidx, rank, world)
 mine = S.queries_of(nq, rank, world)
 assert full.shape == (len(mine), 2, k, N)
 assert torch.equal(full, enc[torch.as_tensor(qidx[mine])]), "rank %%d: reassembled ciphertexts differ" %% rank
+# whole encoded matrix: coefficient slices -> column blocks (Commit's leaf span)
+for chunks in (1, 3, 8):
+    blk = S.exchange_encoded(enc[..., lo:hi].contiguous(), rank, world, chunks=chunks)
+    a, b = S.column_range(n, rank, world)
+    assert blk.shape == (b - a, 2, k, N) and torch.equal(blk, enc[a:b]), "rank %%d: column block differs" %% rank
 # partitions
 cols = 32
 owned = torch.zeros(cols, dtype=torch.int64); a, b = S.column_range(cols, rank, world); owned[a:b] += 1

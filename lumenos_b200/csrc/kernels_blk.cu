@@ -16,6 +16,7 @@
 // References: lattigo rlwe.Evaluator.DecomposeNTT / GadgetProductHoisted / ModDownQPtoQNTT / AutomorphismHoisted and
 // ring.DivRoundByLastModulusNTT as called from fhe/ligero.go:325 (InnerSum) and :331-333, :271-273 (Rescale); restated
 // in oracle/lumenos_oracle.c.
+#include <cstdlib>
 #include "kernels.cuh"
 #include "ntt_blk.cuh"
 #include "tma.cuh"
@@ -483,7 +484,8 @@ __global__ void __launch_bounds__(RA_THREADS, 2) k_blk_fwd(const ModDev *mods, c
 // jobs per CTA: as many as keep at least four waves of CTAs in flight (the twiddle table is filled once per CTA)
 static int pick_jb(int ctas_per_job, int jobs) {
     const int want = 4 * 148 * 3;
-    for (int jb = 4; jb > 1; jb >>= 1)
+    static const int jmax = getenv("LMN_BLK_JB") ? atoi(getenv("LMN_BLK_JB")) : 4;   // tuning knob
+    for (int jb = jmax; jb > 1; jb >>= 1)
         if ((long)ctas_per_job * ((jobs + jb - 1) / jb) >= want) return jb;
     return 1;
 }

@@ -440,6 +440,27 @@ def main():
                        "note": "RingSwitchNew (fhe/ring_switch.go:106-113) of every MatR / MatZ ciphertext: level-0 key switch + decimation; config E = the headline step + this"}
         small_r.free(); small_z.free()
 
+    # ---- wire format (EncryptedProof.MarshalBinary, fhe/ligero.go:646-704), beside the headline ----
+    proof_marshal = None
+    if G == 1 and not args.no_commit:
+        lfm = fhe.LeafFormat.lattigo_like(b"\x00" * 48, lout, N)
+        depth = max(1, (n - 1).bit_length())
+        md = _capi.LmnLigeroMetadata(rows, cols, RHO_INV, nq_total)
+        paths_b, root_b = bytes(32 * depth * nq_total), bytes(32)
+        fm = lfm.c_struct()
+        plen = C.c_size_t()
+        margs = (be.ctx, C.byref(md), matR.h, matZ.h, queried.h, C.byref(fm), None, paths_b, len(paths_b), root_b, len(root_b))
+        _capi.check(lib.lmn_proof_marshal(*margs, None, 0, C.byref(plen)))
+        h_proof = vp()
+        _capi.check(lib.lmn_host_alloc(plen.value, C.byref(h_proof)))
+        marshal_once = lambda: _capi.check(lib.lmn_proof_marshal(*margs, h_proof, plen.value, C.byref(plen)))
+        marshal_once()
+        pm_ms = timed(marshal_once, 1)
+        proof_marshal = {"ms": pm_ms, "bytes": plen.value, "GBps_to_pinned_host": plen.value / (pm_ms * 1e-3) / 1e9,
+                         "published_reference_s": {"D": 2.25}.get(args.config),
+                         "note": "MatR || MatZ || QueriedCols serialised on the GPU (k_ct_stream) in 64 MiB chunks, each copied to the pinned proof buffer while the next is produced; metadata, Merkle paths and root written by the host"}
+        lib.lmn_host_free(h_proof)
+
     # ---- e2e: host buffers through the C ABI, H2D + D2H inside the timed region ----
     e2e = None
     if not args.no_e2e:
@@ -491,7 +512,7 @@ def main():
                        "sharding": "1 GPU" if G == 1 else "columns/%d for inner products + query rescale, coefficient slices/%d for Encode, all-to-all of queried slices" % (G, G),
                        "batch_jobs": args.batch},
             "e2e": e2e, "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "roofline_int": roofline_int,
-            "roofline_encode": roofline_encode, "kernel_breakdown_one_step": breakdown, "commit_merkle": commit_merkle, "ring_switch_E": ring_switch, "cpu_baseline": cpu,
+            "roofline_encode": roofline_encode, "kernel_breakdown_one_step": breakdown, "commit_merkle": commit_merkle, "ring_switch_E": ring_switch, "proof_marshal": proof_marshal, "cpu_baseline": cpu,
             "published_reference_s": PUBLISHED_S[args.config],
         }
         print(json.dumps(out))

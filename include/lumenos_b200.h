@@ -190,6 +190,19 @@ uint32_t lmn_merkle_depth(const lmn_merkle *tree);                            /*
 int lmn_merkle_root(const lmn_merkle *tree, uint8_t *out32);                  /* MerkleTree.MerkleRoot, tree.go:165-172 */
 int lmn_merkle_leaf_hash(const lmn_merkle *tree, uint32_t index, uint8_t *out32);
 int lmn_merkle_path(const lmn_merkle *tree, uint32_t index, uint8_t *out);    /* GetMerklePath, tree.go:176-219: 32*depth bytes */
+/* ---------------- Wire format of the proof (fhe/ligero.go:646-704, 757-763; core/tree.go:270-277) ---------------- */
+/* ct.WriteTo(s[first]) || ... || ct.WriteTo(s[first+count-1]) written to host memory `out` (framing as for the leaves; any host
+ * memory, pinned memory overlaps the copy with the serialisation).  out may be NULL to query *len.  Multi-GPU hosts marshal each
+ * rank's columns into its own range of one buffer (every ciphertext stream has the same length). */
+int lmn_store_marshal(lmn_ctx *ctx, const lmn_store *s, uint32_t first, uint32_t count, const lmn_leaf_format *fmt, uint8_t *out, size_t cap, size_t *len);
+typedef struct { uint32_t rows, cols, rho_inv, queries; } lmn_ligero_metadata;   /* fhe.LigeroMetadata, ligero.go:65-70 */
+/* EncryptedProof.WriteTo / MarshalBinary: metadata (u32 rows, u32 cols, u8 rhoInv, u16 queries, little-endian) || MatR || MatZ ||
+ * QueriedCols (each ciphertext as ct.WriteTo) || paths (MerklePath.WriteTo: the 32-byte hashes back to back, `paths_len` bytes as
+ * returned by lmn_merkle_path per query) || root.  fmt_query == NULL: same framing as MatR / MatZ (they differ after a ring switch).
+ * out may be NULL to query *len. */
+int lmn_proof_marshal(lmn_ctx *ctx, const lmn_ligero_metadata *md, const lmn_store *mat_r, const lmn_store *mat_z, const lmn_store *queried,
+                      const lmn_leaf_format *fmt_mat, const lmn_leaf_format *fmt_query, const uint8_t *paths, size_t paths_len,
+                      const uint8_t *root, size_t root_len, uint8_t *out, size_t cap, size_t *len);
 /* test hook: the serialised bytes of leaf `index` (out may be NULL to query *len) */
 int lmn_leaf_bytes(lmn_ctx *ctx, const lmn_store *leaves, uint32_t index, const lmn_leaf_format *fmt, uint8_t *out, size_t cap, size_t *len);
 

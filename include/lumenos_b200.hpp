@@ -207,19 +207,23 @@ struct LigeroMetadata { int Rows = 0, Cols = 0, RhoInv = 0, Queries = 0; };
 
 typedef std::vector<std::vector<uint8_t>> MerklePath;   // core/tree.go:33
 
-struct EncryptedProof {   // fhe/ligero.go:185-192
-    LigeroMetadata Metadata;
-    std::unique_ptr<CiphertextStore> MatR, MatZ, QueriedCols;
-    std::vector<MerklePath> MerklePaths;
-    std::vector<uint8_t> Root;
-};
-
 // framing of the leaf byte stream ct.WriteTo(buf) (fhe/ligero.go:157-158); see lmn_leaf_format
 struct LeafFormat {
     std::vector<uint8_t> header, polyHeader, limbHeader;
     lmn_leaf_format c() const {
         return lmn_leaf_format{header.data(), (uint32_t)header.size(), polyHeader.data(), (uint32_t)polyHeader.size(), limbHeader.data(), (uint32_t)limbHeader.size()};
     }
+};
+
+struct EncryptedProof {   // fhe/ligero.go:185-192
+    LigeroMetadata Metadata;
+    std::unique_ptr<CiphertextStore> MatR, MatZ, QueriedCols;
+    std::vector<MerklePath> MerklePaths;
+    std::vector<uint8_t> Root;
+
+    // MarshalBinary / WriteTo (fhe/ligero.go:646-704): the ciphertext streams are serialised on the GPU straight into the result.
+    // matFormat frames MatR / MatZ, queryFormat (default: the same) the queried columns (they differ after a ring switch).
+    std::vector<uint8_t> MarshalBinary(ServerBFV &backend, const LeafFormat &matFormat, const LeafFormat *queryFormat = nullptr) const;
 };
 // core.MerkleTree (core/tree.go:15-21): built on the GPU by core.NewTree's rule, node hashes on the host
 class MerkleTree {
@@ -240,6 +244,20 @@ class MerkleTree {
   private:
     lmn_merkle *h_ = nullptr;
 };
+
+inline std::vector<uint8_t> EncryptedProof::MarshalBinary(ServerBFV &backend, const LeafFormat &matFormat, const LeafFormat *queryFormat) const {
+    const lmn_ligero_metadata md{(uint32_t)Metadata.Rows, (uint32_t)Metadata.Cols, (uint32_t)Metadata.RhoInv, (uint32_t)Metadata.Queries};
+    const lmn_leaf_format fm = matFormat.c(), fq = queryFormat ? queryFormat->c() : fm;
+    std::vector<uint8_t> paths;
+    for (const MerklePath &p : MerklePaths) for (const auto &hsh : p) paths.insert(paths.end(), hsh.begin(), hsh.end());   // MerklePath.WriteTo, core/tree.go:270-277
+    size_t n = 0;
+    check(lmn_proof_marshal(backend.ctx(), &md, MatR->handle(), MatZ->handle(), QueriedCols->handle(), &fm, &fq, paths.data(), paths.size(),
+                            Root.data(), Root.size(), nullptr, 0, &n));
+    std::vector<uint8_t> out(n);
+    check(lmn_proof_marshal(backend.ctx(), &md, MatR->handle(), MatZ->handle(), QueriedCols->handle(), &fm, &fq, paths.data(), paths.size(),
+                            Root.data(), Root.size(), out.data(), out.size(), &n));
+    return out;
+}
 
 class LigeroCommitter;
 class LigeroProver {   // fhe/ligero.go:32-37

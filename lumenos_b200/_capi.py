@@ -16,6 +16,10 @@ class LmnLeafFormat(C.Structure):
                 ("limb_header", C.c_char_p), ("limb_header_len", C.c_uint32)]
 
 
+class LmnLigeroMetadata(C.Structure):
+    _fields_ = [("rows", C.c_uint32), ("cols", C.c_uint32), ("rho_inv", C.c_uint32), ("queries", C.c_uint32)]
+
+
 class LmnParams(C.Structure):
     _fields_ = [("log_n", C.c_uint32), ("num_q", C.c_uint32), ("num_p", C.c_uint32),
                 ("q", u64p), ("p", u64p), ("psi_q", u64p), ("psi_p", u64p), ("t", C.c_uint64),
@@ -79,6 +83,9 @@ SIGNATURES = {
     "lmn_merkle_leaf_hash": (C.c_int, [vp, C.c_uint32, vp]),
     "lmn_merkle_path": (C.c_int, [vp, C.c_uint32, vp]),
     "lmn_leaf_bytes": (C.c_int, [vp, vp, C.c_uint32, C.POINTER(LmnLeafFormat), vp, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "lmn_store_marshal": (C.c_int, [vp, vp, C.c_uint32, C.c_uint32, C.POINTER(LmnLeafFormat), vp, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "lmn_proof_marshal": (C.c_int, [vp, C.POINTER(LmnLigeroMetadata), vp, vp, vp, C.POINTER(LmnLeafFormat), C.POINTER(LmnLeafFormat),
+                                    C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, vp, C.c_size_t, C.POINTER(C.c_size_t)]),
     "lmn_rescale_scale": (C.c_uint64, [vp, C.c_uint32, C.c_uint32]),
     "lmn_ct_add": (C.c_int, [vp, vp, C.c_uint32, vp, C.c_uint32, vp, C.c_uint32]),
     "lmn_ct_sub": (C.c_int, [vp, vp, C.c_uint32, vp, C.c_uint32, vp, C.c_uint32]),

@@ -1084,6 +1084,92 @@ int lmn_leaf_bytes(lmn_ctx *c, const lmn_store *leaves, uint32_t index, const lm
     return rc;
 }
 
+// ---- wire format: EncryptedProof.WriteTo, fhe/ligero.go:660-704 ----
+// ct.WriteTo(cts[first]) || ... || ct.WriteTo(cts[first + count - 1]) into host memory: the byte streams are produced on the GPU in
+// chunks of two alternating staging buffers, each chunk copied home on the copy stream while the next one is serialised, so the
+// marshalled bytes land in the caller's buffer without an intermediate host copy of the limbs.  Caller holds the lock.
+static int store_marshal_locked(lmn_ctx *c, const lmn_store *s, uint32_t first, uint32_t count, const lmn_leaf_format *fmt, uint8_t *out,
+                                size_t cap, size_t *len) {
+    LeafFormat F; uint8_t *d_hdr = nullptr;
+    if (int rc = make_leaf_format(c, s, fmt, F, &d_hdr)) return rc;
+    const uint64_t total = (uint64_t)count * F.total_len;
+    *len = (size_t)total;
+    int rc = 0;
+    if (out && total) {
+        if (cap < total) rc = fail(LMN_ERR_INVALID, "output buffer too small for the marshalled ciphertexts");
+        else {
+            const uint64_t CH = std::min<uint64_t>((total + 7) / 8 * 8, 64ull << 20);    // bytes per staging buffer (multiple of 8)
+            u64 *stg[2] = {nullptr, nullptr};
+            cudaError_t e = cudaMalloc(&stg[0], CH);
+            if (e == cudaSuccess && total > CH) e = cudaMalloc(&stg[1], CH);
+            const u64 *cts = s->d + (size_t)first * s->words();
+            Launch L = c->L();
+            uint64_t nchunk = 0;
+            for (uint64_t b0 = 0; e == cudaSuccess && b0 < total; b0 += CH, nchunk++) {
+                const int bi = (int)(nchunk & 1);
+                const uint64_t b1 = std::min(total, b0 + CH);
+                cudaEvent_t ser = copy_event(c, bi), copied = copy_event(c, 2 + bi);
+                if (nchunk >= 2) e = cudaStreamWaitEvent(c->stream, copied, 0);          // the buffer's previous chunk has gone home
+                if (e != cudaSuccess) break;
+                launch_ct_stream(L, F, cts, s->words(), b0, b1, stg[bi]);
+                e = cudaGetLastError();
+                if (e == cudaSuccess) e = cudaEventRecord(ser, c->stream);
+                if (e == cudaSuccess) e = cudaStreamWaitEvent(c->copy_stream, ser, 0);
+                if (e == cudaSuccess) e = cudaMemcpyAsync(out + b0, stg[bi], b1 - b0, cudaMemcpyDeviceToHost, c->copy_stream);
+                if (e == cudaSuccess) e = cudaEventRecord(copied, c->copy_stream);
+            }
+            cudaError_t e2 = cudaStreamSynchronize(c->copy_stream);
+            cudaError_t e3 = cudaStreamSynchronize(c->stream);
+            if (e == cudaSuccess) e = e2 != cudaSuccess ? e2 : e3;
+            cudaFree(stg[0]); cudaFree(stg[1]);
+            if (e != cudaSuccess) rc = fail(LMN_ERR_CUDA, cudaGetErrorString(e));
+        }
+    }
+    cudaFree(d_hdr);
+    return rc;
+}
+int lmn_store_marshal(lmn_ctx *c, const lmn_store *s, uint32_t first, uint32_t count, const lmn_leaf_format *fmt, uint8_t *out, size_t cap, size_t *len) {
+    if (!c || !s || !fmt || !len) return fail(LMN_ERR_INVALID, "null argument");
+    if (s->ctx != c) return fail(LMN_ERR_INVALID, "objects belong to different contexts");
+    if ((uint64_t)first + count > s->count) return fail(LMN_ERR_INVALID, "ciphertext range out of bounds");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    return store_marshal_locked(c, s, first, count, fmt, out, cap, len);
+}
+int lmn_proof_marshal(lmn_ctx *c, const lmn_ligero_metadata *md, const lmn_store *mat_r, const lmn_store *mat_z, const lmn_store *queried,
+                      const lmn_leaf_format *fmt_mat, const lmn_leaf_format *fmt_query, const uint8_t *paths, size_t paths_len,
+                      const uint8_t *root, size_t root_len, uint8_t *out, size_t cap, size_t *len) {
+    if (!c || !md || !mat_r || !mat_z || !queried || !fmt_mat || !len) return fail(LMN_ERR_INVALID, "null argument");
+    if ((paths_len && !paths) || (root_len && !root)) return fail(LMN_ERR_INVALID, "null paths / root with non-zero length");
+    if (mat_r->ctx != c || mat_z->ctx != c || queried->ctx != c) return fail(LMN_ERR_INVALID, "objects belong to different contexts");
+    if (mat_r->level != mat_z->level || mat_r->n != mat_z->n) return fail(LMN_ERR_INVALID, "MatR and MatZ must have one shape");
+    if (!fmt_query) fmt_query = fmt_mat;
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    // LigeroMetadata.WriteTo (ligero.go:757-763): u32 rows, u32 cols, u8 rhoInv, u16 queries, little-endian (Go's conversions truncate)
+    constexpr size_t MD = 11;
+    size_t off = MD, n = 0;
+    const lmn_store *parts[3] = {mat_r, mat_z, queried};
+    const lmn_leaf_format *fm[3] = {fmt_mat, fmt_mat, fmt_query};
+    for (int i = 0; i < 3; i++) {
+        uint8_t *dst = out ? out + std::min(off, cap) : nullptr;
+        if (int rc = store_marshal_locked(c, parts[i], 0, parts[i]->count, fm[i], dst, out && cap > off ? cap - off : 0, &n)) return rc;
+        off += n;
+    }
+    const size_t total = off + paths_len + root_len;
+    *len = total;
+    if (!out) return 0;
+    if (cap < total) return fail(LMN_ERR_INVALID, "output buffer too small for the proof");
+    const uint32_t rows = md->rows, cols = md->cols;
+    const uint16_t queries = (uint16_t)md->queries;
+    for (int i = 0; i < 4; i++) { out[i] = (uint8_t)(rows >> (8 * i)); out[4 + i] = (uint8_t)(cols >> (8 * i)); }
+    out[8] = (uint8_t)md->rho_inv;
+    out[9] = (uint8_t)queries; out[10] = (uint8_t)(queries >> 8);
+    if (paths_len) memcpy(out + off, paths, paths_len);                    // MerklePath.WriteTo, core/tree.go:270-277
+    if (root_len) memcpy(out + off + paths_len, root, root_len);           // buf.Write(p.Root), ligero.go:698
+    return 0;
+}
+
 // leaf hashes (level 0) computed on the device into d_nodes[0 .. n); caller holds the lock
 static cudaError_t hash_leaves_dev(lmn_ctx *c, const lmn_store *leaves, const LeafFormat &F, uint32_t *d_nodes) {
     const uint32_t n = leaves->count;

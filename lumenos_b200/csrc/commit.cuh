@@ -18,6 +18,8 @@ struct LeafFormat {
 };
 
 void launch_leaf_serialize(const Launch &L, const LeafFormat &F, const u64 *cts, uint64_t ct_words, uint32_t n_leaves, u64 *out);
+// bytes [byte0, byte_end) of the unpadded concatenation of the ciphertext streams of `cts`, packed into u64 words
+void launch_ct_stream(const Launch &L, const LeafFormat &F, const u64 *cts, uint64_t ct_words, uint64_t byte0, uint64_t byte_end, u64 *out);
 void launch_sha256_leaves(const Launch &L, const u64 *ser, uint32_t padded_len, uint32_t n_leaves, uint32_t *hashes);
 void launch_sha256_nodes(const Launch &L, const uint32_t *children, uint32_t n_children, uint32_t *parents);
 

@@ -105,6 +105,46 @@ __global__ void __launch_bounds__(256) k_leaf_serialize(const LeafFormat F, cons
     out[(size_t)blockIdx.y * (F.padded_len / 8) + w] = v;
 }
 
+// Wire format of the proof (EncryptedProof.WriteTo, fhe/ligero.go:660-691): MatR, MatZ and QueriedCols are written as
+// ct.WriteTo(cts[0]) || ct.WriteTo(cts[1]) || ... without padding.  out[w] = bytes [byte0 + 8w, byte0 + 8w + 8) of that
+// concatenation (little-endian packing), bytes at or beyond byte_end are zero.  A stream need not be a multiple of 8 bytes long, so
+// a word may straddle two ciphertexts: those words (and the ones touching framing bytes) take the byte-wise path.
+__global__ void __launch_bounds__(256) k_ct_stream(const LeafFormat F, const u64 *__restrict__ cts, uint64_t ct_words, uint64_t byte0,
+                                                   uint64_t byte_end, u64 *__restrict__ out) {
+    const uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t p = byte0 + 8 * w;
+    if (p >= byte_end) return;
+    const uint64_t ci = p / F.total_len;
+    const uint32_t pos = (uint32_t)(p - ci * F.total_len);
+    u64 v = 0;
+    bool done = false;
+    if (pos >= F.hdr_len && pos + 8 <= F.total_len) {
+        const uint32_t p0 = pos - F.hdr_len;
+        const uint32_t poly = p0 / F.poly_len, r = p0 - poly * F.poly_len;
+        if (r >= F.poly_hdr_len) {
+            const uint32_t r2 = r - F.poly_hdr_len;
+            const uint32_t limb = r2 / F.limb_len, s = r2 - limb * F.limb_len;
+            if (s >= F.limb_hdr_len && s + 8 <= F.limb_len) {
+                const uint32_t b = s - F.limb_hdr_len, sh = 8 * (b & 7);
+                const u64 *src = cts + ci * ct_words + (((size_t)poly * F.nl + limb) << F.logn) + (b >> 3);
+                v = src[0] >> sh;
+                if (sh) v |= src[1] << (64 - sh);
+                done = true;
+            }
+        }
+    }
+    if (!done) {
+#pragma unroll 1
+        for (int i = 0; i < 8; i++) {
+            const uint64_t pp = p + i;
+            if (pp >= byte_end) break;
+            const uint64_t c2 = pp / F.total_len;
+            v |= (u64)leaf_byte(F, cts + c2 * ct_words, (uint32_t)(pp - c2 * F.total_len)) << (8 * i);
+        }
+    }
+    out[w] = v;
+}
+
 // one thread per leaf; blocks are read one ahead of the compression that consumes them
 __global__ void __launch_bounds__(32) k_sha256_leaves(const uint4 *__restrict__ ser, uint32_t blocks_per_leaf, uint32_t n_leaves,
                                                       uint32_t *__restrict__ hashes) {
@@ -155,6 +195,11 @@ void launch_leaf_serialize(const Launch &L, const LeafFormat &F, const u64 *cts,
     LaunchScope scope(L, KID_LEAF_SER);
     const uint32_t words = F.padded_len / 8;
     k_leaf_serialize<<<dim3((words + 255) / 256, n_leaves), 256, 0, L.stream>>>(F, cts, ct_words, out);
+}
+void launch_ct_stream(const Launch &L, const LeafFormat &F, const u64 *cts, uint64_t ct_words, uint64_t byte0, uint64_t byte_end, u64 *out) {
+    LaunchScope scope(L, KID_LEAF_SER);
+    const uint64_t words = (byte_end - byte0 + 7) / 8;
+    k_ct_stream<<<(unsigned)((words + 255) / 256), 256, 0, L.stream>>>(F, cts, ct_words, byte0, byte_end, out);
 }
 void launch_sha256_leaves(const Launch &L, const u64 *ser, uint32_t padded_len, uint32_t n_leaves, uint32_t *hashes) {
     LaunchScope scope(L, KID_SHA_LEAF);

@@ -342,11 +342,76 @@ class LigeroMetadata:
 
 
 class EncryptedProof:
-    """ref: fhe/ligero.go:185-192"""
+    """ref: fhe/ligero.go:185-192; wire format :646-704"""
 
     def __init__(self, metadata, matR, matZ, queriedCols, merklePaths=None, root=None):
         self.Metadata, self.MatR, self.MatZ, self.QueriedCols = metadata, matR, matZ, queriedCols
         self.MerklePaths, self.Root = merklePaths, root
+
+    def MarshalBinary(self, backend, leafFormat, queryFormat=None, out=None):
+        """EncryptedProof.MarshalBinary / WriteTo (ligero.go:646-704): the ciphertext streams are serialised on the GPU and copied
+        straight into the result.  leafFormat frames MatR / MatZ, queryFormat (default: the same) the queried columns - they differ
+        after a ring switch.  out: optional writable buffer (e.g. pinned memory); returns bytes, or the length written into out."""
+        md = _capi.LmnLigeroMetadata(self.Metadata.Rows & 0xFFFFFFFF, self.Metadata.Cols & 0xFFFFFFFF, self.Metadata.RhoInv & 0xFFFFFFFF,
+                                     self.Metadata.Queries & 0xFFFFFFFF)
+        fm = leafFormat.c_struct()
+        fq = queryFormat.c_struct() if queryFormat is not None else None
+        paths = b"".join(b"".join(p) for p in self.MerklePaths) if self.MerklePaths else b""
+        root = bytes(self.Root) if self.Root else b""
+        lib = _capi.lib()
+        n = C.c_size_t()
+        args = (backend.ctx, C.byref(md), self.MatR.h, self.MatZ.h, self.QueriedCols.h, C.byref(fm), C.byref(fq) if fq is not None else None,
+                paths, len(paths), root, len(root))
+        check(lib.lmn_proof_marshal(*args, None, 0, C.byref(n)))
+        if out is not None:
+            dst = np.frombuffer(out, dtype=np.uint8) if not isinstance(out, np.ndarray) else out
+            check(lib.lmn_proof_marshal(*args, C.c_void_p(dst.ctypes.data), dst.nbytes, C.byref(n)))
+            return n.value
+        buf = np.empty(n.value, dtype=np.uint8)
+        check(lib.lmn_proof_marshal(*args, C.c_void_p(buf.ctypes.data), buf.nbytes, C.byref(n)))
+        return buf.tobytes()
+
+    @staticmethod
+    def UnmarshalBinary(data, params, leafFormat, queryFormat=None, matLevel=1, matN=None):
+        """EncryptedProof.ReadFrom (ligero.go:706-755), host side (numpy): returns (metadata, MatR, MatZ, QueriedCols as uint64 arrays
+        [count][2][level+1][N], paths, root).  Used by the round-trip tests; the verifier is outside this package."""
+        data = memoryview(data)
+        rows, cols = int.from_bytes(data[0:4], "little"), int.from_bytes(data[4:8], "little")
+        rhoInv, queries = data[8], int.from_bytes(data[9:11], "little")
+        off = 11
+        qf = queryFormat or leafFormat
+
+        def read_cts(count, fmt, level, N):
+            nonlocal off
+            out = np.empty((count, 2, level + 1, N), dtype=np.uint64)
+            for i in range(count):
+                if bytes(data[off:off + len(fmt.header)]) != fmt.header:
+                    raise ValueError("ciphertext header mismatch")
+                off += len(fmt.header)
+                for p in range(2):
+                    if bytes(data[off:off + len(fmt.polyHeader)]) != fmt.polyHeader:
+                        raise ValueError("polynomial header mismatch")
+                    off += len(fmt.polyHeader)
+                    for l in range(level + 1):
+                        if bytes(data[off:off + len(fmt.limbHeader)]) != fmt.limbHeader:
+                            raise ValueError("limb header mismatch")
+                        off += len(fmt.limbHeader)
+                        out[i, p, l] = np.frombuffer(data[off:off + 8 * N], dtype="<u8")
+                        off += 8 * N
+            return out
+        N = 1 << params.logN
+        lq = min(1, params.MaxLevel())
+        matR = read_cts(cols, leafFormat, matLevel, matN or N)
+        matZ = read_cts(cols, leafFormat, matLevel, matN or N)
+        qc = read_cts(queries, qf, lq, N)
+        merkleLen = cols * rhoInv
+        depth = max(0, (merkleLen - 1).bit_length())     # ligero.go:737-739: log2 of the next power of two
+        paths = []
+        for _ in range(queries):
+            paths.append([bytes(data[off + 32 * j:off + 32 * j + 32]) for j in range(depth)])
+            off += 32 * depth
+        root = bytes(data[off:off + 32])
+        return LigeroMetadata(rows, cols, rhoInv, queries), matR, matZ, qc, paths, root
 
 
 class LeafFormat:

@@ -144,6 +144,13 @@ uint64_t orc_leaf_bytes(const uint64_t *ct, int nl, int N, const uint8_t *hdr, u
                         const uint8_t *lh, uint32_t lh_len, uint8_t *out);
 uint32_t orc_merkle_tree(const uint8_t *leaf_hashes, uint32_t n, uint8_t *nodes);
 uint32_t orc_merkle_path(const uint8_t *nodes, uint32_t n, uint32_t index, uint8_t *out);
+/* EncryptedProof.WriteTo (fhe/ligero.go:660-704) */
+uint64_t orc_proof_bytes(uint32_t rows, uint32_t cols, uint32_t rho_inv, uint32_t queries,
+                         const uint64_t *mat_r, const uint64_t *mat_z, uint32_t n_mat, int nl_m, int N_m,
+                         const uint8_t *mh, uint32_t mh_len, const uint8_t *mph, uint32_t mph_len, const uint8_t *mlh, uint32_t mlh_len,
+                         const uint64_t *queried, uint32_t n_q, int nl_q, int N_q,
+                         const uint8_t *qh, uint32_t qh_len, const uint8_t *qph, uint32_t qph_len, const uint8_t *qlh, uint32_t qlh_len,
+                         const uint8_t *paths, uint64_t paths_len, const uint8_t *root, uint32_t root_len, uint8_t *out);
 
 #ifdef __cplusplus
 }

@@ -110,3 +110,33 @@ uint32_t orc_merkle_path(const uint8_t *nodes, uint32_t n, uint32_t index, uint8
     }
     return d;
 }
+
+/* EncryptedProof.WriteTo (fhe/ligero.go:660-704) with LigeroMetadata.WriteTo (:757-763) and MerklePath.WriteTo (core/tree.go:270-277):
+   metadata || MatR || MatZ || QueriedCols || paths || root.  mat_r / mat_z: cols ciphertexts [2][nl_m][N_m]; queried: nq ciphertexts
+   [2][nl_q][N_q]; framing (hdr, ph, lh) per group as in orc_leaf_bytes.  Returns the length (out may be NULL). */
+uint64_t orc_proof_bytes(uint32_t rows, uint32_t cols, uint32_t rho_inv, uint32_t queries,
+                         const uint64_t *mat_r, const uint64_t *mat_z, uint32_t n_mat, int nl_m, int N_m,
+                         const uint8_t *mh, uint32_t mh_len, const uint8_t *mph, uint32_t mph_len, const uint8_t *mlh, uint32_t mlh_len,
+                         const uint64_t *queried, uint32_t n_q, int nl_q, int N_q,
+                         const uint8_t *qh, uint32_t qh_len, const uint8_t *qph, uint32_t qph_len, const uint8_t *qlh, uint32_t qlh_len,
+                         const uint8_t *paths, uint64_t paths_len, const uint8_t *root, uint32_t root_len, uint8_t *out) {
+    uint64_t n = 0;
+    if (out) {
+        /* binary.Write(buf, LittleEndian, uint32(Rows) / uint32(Cols) / uint8(RhoInv) / uint16(Queries)) */
+        for (int i = 0; i < 4; i++) { out[i] = (uint8_t)(rows >> (8 * i)); out[4 + i] = (uint8_t)(cols >> (8 * i)); }
+        out[8] = (uint8_t)rho_inv;
+        out[9] = (uint8_t)queries; out[10] = (uint8_t)(queries >> 8);
+    }
+    n = 11;
+    const uint64_t *mats[2] = {mat_r, mat_z};
+    for (int g = 0; g < 2; g++)
+        for (uint32_t i = 0; i < n_mat; i++)
+            n += orc_leaf_bytes(mats[g] + (size_t)i * 2 * nl_m * N_m, nl_m, N_m, mh, mh_len, mph, mph_len, mlh, mlh_len, out ? out + n : NULL);
+    for (uint32_t i = 0; i < n_q; i++)
+        n += orc_leaf_bytes(queried + (size_t)i * 2 * nl_q * N_q, nl_q, N_q, qh, qh_len, qph, qph_len, qlh, qlh_len, out ? out + n : NULL);
+    if (out && paths_len) memcpy(out + n, paths, paths_len);
+    n += paths_len;
+    if (out && root_len) memcpy(out + n, root, root_len);
+    n += root_len;
+    return n;
+}

@@ -45,6 +45,8 @@ def lib():
         "orc_default_switches": (None, [C.POINTER(Switches)]),
         "orc_sha256": (None, [C.c_char_p, u64, C.c_char_p]),
         "orc_leaf_bytes": (u64, [_u64p, i, i, C.c_char_p, C.c_uint32, C.c_char_p, C.c_uint32, C.c_char_p, C.c_uint32, C.c_char_p]),
+        "orc_proof_bytes": (u64, [C.c_uint32] * 4 + [_u64p, _u64p, C.c_uint32, i, i] + [C.c_char_p, C.c_uint32] * 3 + [_u64p, C.c_uint32, i, i]
+                            + [C.c_char_p, C.c_uint32] * 3 + [C.c_char_p, u64, C.c_char_p, C.c_uint32, C.c_char_p]),
         "orc_merkle_tree": (C.c_uint32, [C.c_char_p, C.c_uint32, C.c_char_p]),
         "orc_merkle_path": (C.c_uint32, [C.c_char_p, C.c_uint32, C.c_uint32, C.c_char_p]),
         "orc_params_generate": (vp, [i, i, u64, C.POINTER(Switches)]),
@@ -337,6 +339,23 @@ def leaf_bytes(ct, header=b"", poly_header=b"", limb_header=b""):
     got = lib().orc_leaf_bytes(ct, nl, N, header, len(header), poly_header, len(poly_header), limb_header, len(limb_header), out)
     assert got == n
     return out.raw
+
+
+def proof_bytes(rows, cols, rho_inv, queries, mat_r, mat_z, queried, mat_fmt, query_fmt=None, paths=(), root=b""):
+    """EncryptedProof.WriteTo (fhe/ligero.go:660-704).  mat_r / mat_z: [cols][2][nl][N]; queried: [nq][2][nl'][N']; *_fmt = (header,
+    poly_header, limb_header); paths: list of lists of 32-byte hashes."""
+    mat_r, mat_z = np.ascontiguousarray(mat_r, dtype=np.uint64), np.ascontiguousarray(mat_z, dtype=np.uint64)
+    queried = np.ascontiguousarray(queried, dtype=np.uint64)
+    qf = query_fmt or mat_fmt
+    pb = b"".join(b"".join(p) for p in paths)
+    fm = [x for h in mat_fmt for x in (bytes(h), len(h))]
+    fq = [x for h in qf for x in (bytes(h), len(h))]
+    args = [rows & 0xFFFFFFFF, cols & 0xFFFFFFFF, rho_inv & 0xFFFFFFFF, queries & 0xFFFFFFFF, mat_r, mat_z, mat_r.shape[0], mat_r.shape[2],
+            mat_r.shape[3]] + fm + [queried, queried.shape[0], queried.shape[2], queried.shape[3]] + fq + [pb, len(pb), bytes(root), len(root)]
+    n = lib().orc_proof_bytes(*args, None)
+    out = C.create_string_buffer(max(1, n))
+    assert lib().orc_proof_bytes(*args, out) == n
+    return out.raw[:n]
 
 
 class MerkleTree:

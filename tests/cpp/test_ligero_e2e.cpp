@@ -153,6 +153,16 @@ int main(int argc, char **argv) {
                 REQUIRE(proof.MerklePaths[q].size() == d, "path length");
                 for (uint32_t l = 0; l < d; l++) REQUIRE(std::memcmp(proof.MerklePaths[q][l].data(), path.data() + 32 * l, 32) == 0, "Merkle path %d level %u", q, l);
             }
+            // wire format: EncryptedProof.MarshalBinary against the oracle's WriteTo (fhe/ligero.go:660-704)
+            std::vector<uint8_t> wire = proof.MarshalBinary(server, lf), flat;
+            for (const auto &p : proof.MerklePaths) for (const auto &hsh : p) flat.insert(flat.end(), hsh.begin(), hsh.end());
+            std::vector<uint8_t> wwant(wire.size() + 64);
+            const u64 wl = orc_proof_bytes((uint32_t)rows, (uint32_t)cols, (uint32_t)rhoInv, (uint32_t)ligero.Queries, matR.data(), matZ.data(), (uint32_t)cols, 2, N,
+                                           lf.header.data(), (uint32_t)lf.header.size(), lf.polyHeader.data(), (uint32_t)lf.polyHeader.size(),
+                                           lf.limbHeader.data(), (uint32_t)lf.limbHeader.size(), qc.data(), (uint32_t)ligero.Queries, 2, N,
+                                           lf.header.data(), (uint32_t)lf.header.size(), lf.polyHeader.data(), (uint32_t)lf.polyHeader.size(),
+                                           lf.limbHeader.data(), (uint32_t)lf.limbHeader.size(), flat.data(), flat.size(), proof.Root.data(), 32, wwant.data());
+            REQUIRE(wl == wire.size() && std::memcmp(wire.data(), wwant.data(), wl) == 0, "marshalled proof differs from the oracle (%zu vs %llu bytes)", wire.size(), (unsigned long long)wl);
             bool oob = false;
             try { comm.Tree->GetMerklePath((uint32_t)n); } catch (const Error &) { oob = true; }
             REQUIRE(oob, "GetMerklePath out of bounds must fail");

@@ -355,3 +355,83 @@ def test_host_overlapped_entry_points_match(logN, rows, cols, k, batch):
     for p in (h_m, h_r, h_z):
         lib.lmn_host_free(p)
     be.Close()
+
+
+@pytest.mark.parametrize("fmt_id", range(len(LEAF_FORMATS)))
+@pytest.mark.parametrize("logN,rows,cols,k", [(6, 32, 16, 6), (8, 256, 8, 4)])
+def test_proof_marshal_bit_exact(logN, rows, cols, k, fmt_id):
+    """EncryptedProof.MarshalBinary (fhe/ligero.go:646-704) of a real Commit -> Prove: every byte against the oracle's WriteTo,
+    for aligned / unaligned / empty framings (a ciphertext stream need not be a multiple of 8 bytes), and read back by ReadFrom."""
+    from lumenos_b200 import fhe
+    S = scenario(logN, rows, cols, k)
+    be = S.backend()
+    _, hdr, ph, lh = LEAF_FORMATS[fmt_id]
+    N = 1 << logN
+    lf = fhe.LeafFormat.lattigo_like(hdr, 1, N) if ph is None else fhe.LeafFormat(hdr, ph, lh)
+    matrix = be.NewStore(cols).upload(S.cts)
+    zero = be.NewStore(1).upload(S.zero[None])
+    committer = fhe.LigeroCommitter(128, rows, cols, 2)
+    prover = committer.Commit(matrix, be, (zero, 0), leafFormat=lf)
+    idx = np.random.default_rng(3).integers(0, 2 * cols, size=committer.Queries).astype(np.uint32)
+    proof = prover.Prove(S.rpt, S.bpt, idx, be)
+    got = proof.MarshalBinary(be, lf)
+    matR, matZ, qc = proof.MatR.download(), proof.MatZ.download(), proof.QueriedCols.download()
+    fmt = (lf.header, lf.polyHeader, lf.limbHeader)
+    want = O.proof_bytes(rows, cols, 2, committer.Queries, matR, matZ, qc, fmt, paths=proof.MerklePaths, root=proof.Root)
+    assert len(got) == len(want)
+    assert got == want, "first differing byte %d" % next(i for i in range(len(want)) if got[i] != want[i])
+    md, r2, z2, q2, p2, root2 = fhe.EncryptedProof.UnmarshalBinary(got, be.params, lf)
+    assert (md.Rows, md.Cols, md.RhoInv, md.Queries) == (rows, cols, 2, committer.Queries)
+    assert_same(r2, matR, "MatR"); assert_same(z2, matZ, "MatZ"); assert_same(q2, qc, "QueriedCols")
+    assert p2 == proof.MerklePaths and root2 == proof.Root
+    # a caller-provided buffer that is too small is an error, not a truncated proof
+    with pytest.raises(fhe.LumenosError):
+        proof.MarshalBinary(be, lf, out=np.empty(len(want) - 1, dtype=np.uint8))
+    out = np.zeros(len(want) + 5, dtype=np.uint8)
+    assert proof.MarshalBinary(be, lf, out=out) == len(want) and out[:len(want)].tobytes() == want and not out[len(want):].any()
+    be.Close()
+
+
+def test_store_marshal_ranges_and_chunks():
+    """lmn_store_marshal: any ciphertext range (the multi-GPU host marshals each rank's columns into its own byte range), streams
+    longer than one 64 MiB staging chunk (two alternating buffers), odd stream lengths, and the ring-switched (level-0) shape."""
+    import ctypes as C
+    from lumenos_b200 import fhe, _capi
+    S = scenario(6, 32, 16, 3)
+    be = S.backend()
+    rng = np.random.default_rng(21)
+
+    def marshal(store, first, count, lf):
+        f = lf.c_struct()
+        n = C.c_size_t()
+        fhe.check(_capi.lib().lmn_store_marshal(be.ctx, store.h, first, count, C.byref(f), None, 0, C.byref(n)))
+        buf = np.empty(n.value, dtype=np.uint8)
+        fhe.check(_capi.lib().lmn_store_marshal(be.ctx, store.h, first, count, C.byref(f), C.c_void_p(buf.ctypes.data), buf.nbytes, C.byref(n)))
+        return buf.tobytes()
+    cts = rng.integers(0, 2**58, size=(37, 2, 2, 64), dtype=np.uint64)
+    st = be.NewStore(37, 1).upload(cts)
+    for lf in (fhe.LeafFormat(b"abc", b"\x05", b"\x09\x08\x07"), fhe.LeafFormat(), fhe.LeafFormat.lattigo_like(b"m" * 13, 1, 64)):
+        ser = [O.leaf_bytes(c, lf.header, lf.polyHeader, lf.limbHeader) for c in cts]
+        assert marshal(st, 0, 37, lf) == b"".join(ser)
+        assert marshal(st, 5, 9, lf) == b"".join(ser[5:14])
+        assert marshal(st, 36, 1, lf) == ser[36]
+        assert marshal(st, 3, 0, lf) == b""
+    with pytest.raises(fhe.LumenosError):
+        marshal(st, 30, 8, fhe.LeafFormat())
+    # three staging chunks: 2200 level-1 ciphertexts of N = 4096 -> 144 MB + odd framing
+    if True:
+        S12 = scenario(12, 2048, 8, 3)
+        be12 = S12.backend()
+        big = rng.integers(0, 2**58, size=(2200, 2, 2, 4096), dtype=np.uint64)
+        sb = be12.NewStore(2200, 1).upload(big)
+        lf = fhe.LeafFormat(b"abc", b"\x05", b"\x09\x08\x07")
+        f = lf.c_struct()
+        n = C.c_size_t()
+        fhe.check(_capi.lib().lmn_store_marshal(be12.ctx, sb.h, 0, 2200, C.byref(f), None, 0, C.byref(n)))
+        buf = np.empty(n.value, dtype=np.uint8)
+        fhe.check(_capi.lib().lmn_store_marshal(be12.ctx, sb.h, 0, 2200, C.byref(f), C.c_void_p(buf.ctypes.data), buf.nbytes, C.byref(n)))
+        L = n.value // 2200
+        for j in (0, 1, 511, 512, 1023, 1024, 1025, 2047, 2048, 2199):    # around the 64 MiB chunk boundaries and the ends
+            assert buf[j * L:(j + 1) * L].tobytes() == O.leaf_bytes(big[j], lf.header, lf.polyHeader, lf.limbHeader), "ciphertext %d" % j
+        be12.Close()
+    be.Close()

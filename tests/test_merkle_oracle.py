@@ -71,3 +71,36 @@ def test_leaf_bytes_layout():
     want = hdr + b"".join(ph + b"".join(lh + ct[p, l].astype("<u8").tobytes() for l in range(2)) for p in range(2))
     assert O.leaf_bytes(ct, hdr, ph, lh) == want
     assert O.leaf_bytes(ct) == ct.astype("<u8").tobytes()
+
+
+def test_proof_bytes_layout_and_unmarshal():
+    """EncryptedProof.WriteTo (fhe/ligero.go:660-704): metadata || MatR || MatZ || QueriedCols || paths || root, written by the
+    oracle, spelled out independently here, and read back by the host-side ReadFrom mirror (fhe.EncryptedProof.UnmarshalBinary)."""
+    from lumenos_b200 import fhe
+    rng = np.random.default_rng(9)
+    rows, cols, rho, nq, N = 70000, 4, 2, 5, 16
+    matR = rng.integers(0, 2**58, size=(cols, 2, 2, N), dtype=np.uint64)
+    matZ = rng.integers(0, 2**58, size=(cols, 2, 2, N), dtype=np.uint64)
+    qc = rng.integers(0, 2**58, size=(nq, 2, 2, N), dtype=np.uint64)
+    fmt = (b"meta!", (2).to_bytes(8, "little"), (N).to_bytes(8, "little"))
+    depth = 3   # cols * rho = 8 leaves
+    paths = [[rng.bytes(32) for _ in range(depth)] for _ in range(nq)]
+    root = rng.bytes(32)
+    got = O.proof_bytes(rows, cols, rho, nq, matR, matZ, qc, fmt, paths=paths, root=root)
+    ser = lambda ct: O.leaf_bytes(ct, *fmt)
+    want = (rows.to_bytes(4, "little") + cols.to_bytes(4, "little") + bytes([rho]) + nq.to_bytes(2, "little")
+            + b"".join(ser(c) for c in matR) + b"".join(ser(c) for c in matZ) + b"".join(ser(c) for c in qc)
+            + b"".join(b"".join(p) for p in paths) + root)
+    assert got == want
+
+    class P:   # the two parameters ReadFrom needs
+        logN = 4
+        @staticmethod
+        def MaxLevel():
+            return 1
+    md, r2, z2, q2, p2, root2 = fhe.EncryptedProof.UnmarshalBinary(got, P, fhe.LeafFormat(*fmt))
+    assert (md.Rows, md.Cols, md.RhoInv, md.Queries) == (rows, cols, rho, nq)
+    assert (r2 == matR).all() and (z2 == matZ).all() and (q2 == qc).all() and p2 == paths and root2 == root
+    # Go's uint8(RhoInv) / uint16(Queries) conversions truncate silently (ligero.go:760-761)
+    t = O.proof_bytes(1, 2, 257, 65537, matR[:0], matZ[:0], qc[:0], fmt)
+    assert t == (1).to_bytes(4, "little") + (2).to_bytes(4, "little") + b"\x01" + b"\x01\x00"

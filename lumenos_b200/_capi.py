@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "liblumenos_b200.so")
+SO_PATH = os.environ.get("LUMENOS_B200_SO") or os.path.join(_HERE, "liblumenos_b200.so")   # override: A/B builds of tuning variants
 
 u64p = C.POINTER(C.c_uint64)
 u32p = C.POINTER(C.c_uint32)

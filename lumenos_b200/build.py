@@ -5,7 +5,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-SO = os.path.join(HERE, "liblumenos_b200.so")
+SO = os.environ.get("LUMENOS_B200_SO") or os.path.join(HERE, "liblumenos_b200.so")   # override: A/B builds of tuning variants
 SOURCES = ["api.cu", "kernels.cu", "kernels_blk.cu", "kernels_mac.cu", "kernels_commit.cu", "plan.cpp"]
 HEADERS = ["device.cuh", "ntt_blk.cuh", "tma.cuh", "kernels.cuh", "commit.cuh", "plan.hpp", "hostmath.hpp", os.path.join("..", "..", "include", "lumenos_b200.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
@@ -23,7 +23,7 @@ def needs_build():
 def build(force=False, verbose=False):
     if not force and not needs_build():
         return SO
-    cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO] + [os.path.join(CSRC, f) for f in SOURCES]
+    cmd = [NVCC] + FLAGS + os.environ.get("LUMENOS_B200_NVCC_FLAGS", "").split() + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO] + [os.path.join(CSRC, f) for f in SOURCES]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if verbose or r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)

@@ -23,6 +23,25 @@
 
 namespace lmn {
 
+// resident CTAs per SM each kernel is compiled for (register cap 65536 / (threads * n)).  Measured on B200 at config D with A/B builds:
+// the pointwise base-conversion kernels compiled without a cap were slower than with one (256 jobs per launch: k_modup_blk 27.0 -> 20.1 ms,
+// k_down_pre 10.5 -> 7.8 ms; at the benchmark's 592 jobs per launch 676 -> 637 ms and 248 -> 243 ms per step); the block-transform
+// kernels showed no gain from other values than the ones below, and k_mac_rd with one CTA per SM lost 23 %.
+#ifndef LMN_MODUP_MINB
+#define LMN_MODUP_MINB 4
+#endif
+#ifndef LMN_DOWNPRE_MINB
+#define LMN_DOWNPRE_MINB 3
+#endif
+#ifndef LMN_BLKINTT_MINB
+#define LMN_BLKINTT_MINB 3
+#endif
+#ifndef LMN_BLKFWD_MINB
+#define LMN_BLKFWD_MINB 2
+#endif
+#ifndef LMN_CHAIN_MINB
+#define LMN_CHAIN_MINB 1
+#endif
 constexpr size_t BLK_INTT_SMEM = (2 * (size_t)RA_M + (size_t)RA_WORDS + (size_t)RA_M + 2) * 8;       // twiddles, buffer, one landing block, barriers
 constexpr size_t BLK_FWD_SMEM = (2 * (size_t)RA_M + (size_t)RA_WORDS + 3 * (size_t)RA_M + 4) * 8;    // twiddles, buffer, three landing blocks, barriers
 constexpr unsigned BLK_BYTES = RA_M * 8;
@@ -49,7 +68,7 @@ void launch_build_blk_tables(cudaStream_t stream, const DeviceTables &T, ulonglo
 // before the CTA writes it, and other jobs' blocks are other addresses.
 // ---------------------------------------------------------------------------------------------------
 template <int S>
-__global__ void __launch_bounds__(RA_THREADS, 3) k_blk_intt(const ModDev *mods, const ulonglong2 *twb_inv, const BlkSlots A, int jobs, int jb) {
+__global__ void __launch_bounds__(RA_THREADS, LMN_BLKINTT_MINB) k_blk_intt(const ModDev *mods, const ulonglong2 *twb_inv, const BlkSlots A, int jobs, int jb) {
     extern __shared__ __align__(16) u64 sm[];
     constexpr int LOGN = RA_LOGM + LogS<S>::v;
     ulonglong2 *stw = reinterpret_cast<ulonglong2 *>(sm);
@@ -102,7 +121,7 @@ __global__ void __launch_bounds__(RA_THREADS, 3) k_blk_intt(const ModDev *mods, 
 // grid (M/256, digits, jobs)
 // ---------------------------------------------------------------------------------------------------
 template <int S, int ND>
-__global__ void __launch_bounds__(256) k_modup_blk(const ModDev *mods, const ulonglong2 *tw_fwd, const ulonglong2 *tw_inv,
+__global__ void __launch_bounds__(256, LMN_MODUP_MINB) k_modup_blk(const ModDev *mods, const ulonglong2 *tw_fwd, const ulonglong2 *tw_inv,
                                                     const KsConsts *C, const KsJobs J, int d0) {
     constexpr int LOGN = RA_LOGM + LogS<S>::v;
     constexpr int M = RA_M;
@@ -211,7 +230,7 @@ __global__ void __launch_bounds__(256) k_modup_blk(const ModDev *mods, const ulo
 // convert to every q_i and apply the forward coupling levels.  Output: mu[c][i][N].  grid (M/256, 2, jobs)
 // ---------------------------------------------------------------------------------------------------
 template <int S>
-__global__ void __launch_bounds__(256) k_down_pre(const ModDev *mods, const ulonglong2 *tw_fwd, const ulonglong2 *tw_inv,
+__global__ void __launch_bounds__(256, LMN_DOWNPRE_MINB) k_down_pre(const ModDev *mods, const ulonglong2 *tw_fwd, const ulonglong2 *tw_inv,
                                                    const KsConsts *C, const KsJobs J) {
     constexpr int LOGN = RA_LOGM + LogS<S>::v;
     constexpr int M = RA_M;
@@ -318,7 +337,7 @@ __global__ void __launch_bounds__(256) k_rs_pre(const ModDev *mods, const ulongl
 // ---------------------------------------------------------------------------------------------------
 constexpr int CHAIN_THREADS = 128;
 template <int S>
-__global__ void __launch_bounds__(CHAIN_THREADS) k_rs_chain(const ModDev *mods, const ulonglong2 *tw_fwd, const ulonglong2 *tw_inv,
+__global__ void __launch_bounds__(CHAIN_THREADS, LMN_CHAIN_MINB) k_rs_chain(const ModDev *mods, const ulonglong2 *tw_fwd, const ulonglong2 *tw_inv,
                                                             const RescaleChain *R, const KsJobs J) {
     extern __shared__ __align__(16) u64 sm[];   // rr[l - to - 1][r][thread]
     constexpr int LOGN = RA_LOGM + LogS<S>::v;
@@ -377,7 +396,7 @@ __global__ void __launch_bounds__(CHAIN_THREADS) k_rs_chain(const ModDev *mods, 
 // buffers free, so they land while the CTA transforms.
 // ---------------------------------------------------------------------------------------------------
 template <int S, int MODE>
-__global__ void __launch_bounds__(RA_THREADS, 2) k_blk_fwd(const ModDev *mods, const ulonglong2 *twb_fwd, const KsConsts *C,
+__global__ void __launch_bounds__(RA_THREADS, LMN_BLKFWD_MINB) k_blk_fwd(const ModDev *mods, const ulonglong2 *twb_fwd, const KsConsts *C,
                                                             const RescaleConsts *R, const KsJobs J, uint32_t gal_el, int nlimbs,
                                                             int k, int np, int jobs, int jb) {
     extern __shared__ __align__(16) u64 sm[];

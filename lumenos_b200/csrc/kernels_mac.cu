@@ -25,10 +25,13 @@ template <int S> struct LogS2 { static constexpr int v = S == 8 ? 3 : S == 4 ? 2
 // buffers free; the copies land while the other warps transform.  Shared memory: 32 KB twiddles + 17 KB transposition
 // buffer + 16 KB residues + 32 KB key rows = 97 KB, two CTAs per SM.
 // ---------------------------------------------------------------------------------------------------
+#ifndef LMN_MACRD_MINB
+#define LMN_MACRD_MINB 2
+#endif
 typedef unsigned __int128 u128;
 constexpr size_t MAC_RD_SMEM = (2 * (size_t)RA_M + (size_t)RA_WORDS + (size_t)RA_M + 2 * (size_t)RA_M + 4) * 8;
 template <int S>
-__global__ void __launch_bounds__(RA_THREADS, 2) k_mac_rd(const ModDev *mods, const ulonglong2 *twb_fwd, const KsConsts *C,
+__global__ void __launch_bounds__(RA_THREADS, LMN_MACRD_MINB) k_mac_rd(const ModDev *mods, const ulonglong2 *twb_fwd, const KsConsts *C,
                                                            const KsJobs J, const u64 *__restrict__ evk, int jb) {
     extern __shared__ __align__(16) u64 sm[];
     constexpr int M = RA_M;

@@ -25,6 +25,15 @@ static int fail(int code, const std::string &msg) { g_err = msg; return code; }
         if (e_ != cudaSuccess) return fail(LMN_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
     } while (0)
 
+// device scratch that is released on every exit path of the function that owns it
+struct DevScratch {
+    void *p = nullptr;
+    ~DevScratch() { if (p) cudaFree(p); }
+    cudaError_t alloc(size_t bytes) { return cudaMalloc(&p, bytes); }
+    template <class T> T *as() const { return static_cast<T *>(p); }
+    void *release() { void *r = p; p = nullptr; return r; }
+};
+
 struct lmn_ctx {
     int device = 0;
     int logn = 0, n = 0, k = 0, np = 0;
@@ -240,13 +249,22 @@ static int get_rs(lmn_ctx *c, int level, const RescaleConsts **dev) {
 
 static int ensure_workspace(lmn_ctx *c, uint32_t jobs) {
     if (c->ws_jobs >= jobs) return 0;
-    if (c->ws_col) { cudaFree(c->ws_col); cudaFree(c->ws_col2); cudaFree(c->ws_y); cudaFree(c->ws_acc); cudaFree(c->ws_mu); c->ws_col = c->ws_col2 = c->ws_y = c->ws_acc = c->ws_mu = nullptr; c->ws_jobs = 0; }
+    auto drop = [&]() {
+        cudaFree(c->ws_col); cudaFree(c->ws_col2); cudaFree(c->ws_y); cudaFree(c->ws_acc); cudaFree(c->ws_mu);
+        c->ws_col = c->ws_col2 = c->ws_y = c->ws_acc = c->ws_mu = nullptr; c->ws_jobs = 0;
+    };
+    drop();
     size_t N = c->n, k = c->k, KP = c->k + c->np;
-    CK(cudaMalloc(&c->ws_col, jobs * 2 * k * N * 8));
-    CK(cudaMalloc(&c->ws_col2, jobs * 2 * k * N * 8));   // the block pipeline rotates out of place
-    CK(cudaMalloc(&c->ws_y, jobs * k * N * 8));
-    CK(cudaMalloc(&c->ws_acc, jobs * 2 * KP * N * 8));
-    CK(cudaMalloc(&c->ws_mu, jobs * (size_t)((c->k + c->np - 1) / c->np) * KP * N * 8));
+    cudaError_t e = cudaMalloc(&c->ws_col, jobs * 2 * k * N * 8);
+    if (e == cudaSuccess) e = cudaMalloc(&c->ws_col2, jobs * 2 * k * N * 8);   // the block pipeline rotates out of place
+    if (e == cudaSuccess) e = cudaMalloc(&c->ws_y, jobs * k * N * 8);
+    if (e == cudaSuccess) e = cudaMalloc(&c->ws_acc, jobs * 2 * KP * N * 8);
+    if (e == cudaSuccess) e = cudaMalloc(&c->ws_mu, jobs * (size_t)((c->k + c->np - 1) / c->np) * KP * N * 8);
+    if (e != cudaSuccess) {
+        drop();
+        cudaGetLastError();   // an out-of-memory cudaMalloc leaves a sticky-looking last error behind; the context stays usable
+        return fail(e == cudaErrorMemoryAllocation ? LMN_ERR_NOMEM : LMN_ERR_CUDA, std::string("workspace for ") + std::to_string(jobs) + " jobs: " + cudaGetErrorString(e));
+    }
     c->ws_jobs = jobs;
     return 0;
 }
@@ -671,15 +689,15 @@ int lmn_load_galois_key(lmn_ctx *c, uint64_t gal_el, const uint64_t *evk) {
     if (gal_el == 1) return 0;  // identity: Lattigo's key list may contain it; never used
     const int beta = (c->k + c->np - 1) / c->np;
     size_t bytes = (size_t)beta * 2 * (c->k + c->np) * c->n * 8;
-    u64 *d = nullptr;
     auto it = c->galois.find(gal_el);
-    if (it != c->galois.end()) d = it->second; else CK(cudaMalloc(&d, bytes));
-    u64 *stage = nullptr;
-    CK(cudaMalloc(&stage, bytes));
-    CK(cudaMemcpyAsync(stage, evk, bytes, cudaMemcpyHostToDevice, c->stream));
-    launch_scale_rows(c->L(), c->T, stage, d, c->d_key_fm, beta);   // fold 2^s into the rows the base-converted digits multiply
+    DevScratch fresh, stage;     // a key that is not yet in the map is owned here until the upload has succeeded
+    if (it == c->galois.end()) CK(fresh.alloc(bytes));
+    u64 *d = it != c->galois.end() ? it->second : fresh.as<u64>();
+    CK(stage.alloc(bytes));
+    CK(cudaMemcpyAsync(stage.p, evk, bytes, cudaMemcpyHostToDevice, c->stream));
+    launch_scale_rows(c->L(), c->T, stage.as<u64>(), d, c->d_key_fm, beta);   // fold 2^s into the rows the base-converted digits multiply
     CK(cudaStreamSynchronize(c->stream));
-    cudaFree(stage);
+    fresh.release();
     c->galois[gal_el] = d;
     return 0;
 }
@@ -693,12 +711,11 @@ int lmn_load_ring_switch_key(lmn_ctx *c, uint32_t logns, const uint64_t *evk, ui
     const int beta = (c->k + c->np - 1) / c->np;
     size_t bytes = (size_t)beta * 2 * (c->k + c->np) * c->n * 8;
     if (!c->d_rs_evk) CK(cudaMalloc(&c->d_rs_evk, bytes));
-    u64 *stage = nullptr;
-    CK(cudaMalloc(&stage, bytes));
-    CK(cudaMemcpy(stage, evk, bytes, cudaMemcpyHostToDevice));
-    launch_scale_rows(c->L(), c->T, stage, c->d_rs_evk, c->d_key_fm, beta);
+    DevScratch stage;
+    CK(stage.alloc(bytes));
+    CK(cudaMemcpy(stage.p, evk, bytes, cudaMemcpyHostToDevice));
+    launch_scale_rows(c->L(), c->T, stage.as<u64>(), c->d_rs_evk, c->d_key_fm, beta);
     CK(cudaStreamSynchronize(c->stream));
-    cudaFree(stage);
     u64 q0 = c->q[0];
     if (!psi_small) {
         // psi_small = psi^(N/N'): read psi back from the forward table (entry bitrev(1) = N/2 holds psi)
@@ -1051,7 +1068,8 @@ static int make_leaf_format(lmn_ctx *c, const lmn_store *leaves, const lmn_leaf_
     *d_hdr = nullptr;
     if (F.hdr_len) {
         CK(cudaMalloc(d_hdr, F.hdr_len));
-        CK(cudaMemcpy(*d_hdr, fmt->header, F.hdr_len, cudaMemcpyHostToDevice));
+        const cudaError_t e = cudaMemcpy(*d_hdr, fmt->header, F.hdr_len, cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) { cudaFree(*d_hdr); *d_hdr = nullptr; return fail(LMN_ERR_CUDA, cudaGetErrorString(e)); }
     }
     F.hdr = *d_hdr;
     return 0;

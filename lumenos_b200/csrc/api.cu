@@ -768,6 +768,7 @@ static int get_rs_chain(lmn_ctx *c, int from, int to, const RescaleChain **host,
                 R.half_mod[l][i] = R.half[l] % qi;
                 const u64 inv = h_invmod(ql % qi, qi);
                 R.qlinv_w[l][i] = inv; R.qlinv_ws[l][i] = h_shoup(inv, qi);
+                R.cadd[l][i] = R.half_mod[l][i] + ((ql + qi - 1) / qi) * qi;      // < 2^61: moduli are below 2^59 and within a factor 4 of each other
             }
         }
         RescaleChain *d = nullptr;

@@ -52,6 +52,7 @@ struct RescaleChain {
     u64 half[MAX_LIMBS];                               // (q_l - 1) / 2
     u64 half_mod[MAX_LIMBS][MAX_LIMBS];                // [l][i] half_l mod q_i
     u64 qlinv_w[MAX_LIMBS][MAX_LIMBS], qlinv_ws[MAX_LIMBS][MAX_LIMBS];   // [l][i] q_l^-1 mod q_i (Shoup pair)
+    u64 cadd[MAX_LIMBS][MAX_LIMBS];                    // [l][i] (half_l mod q_i) + ceil(q_l / q_i) q_i: x_i + cadd - r_l > 0 and = x_i - (r_l - half_l) mod q_i
 };
 
 struct DeviceTables {

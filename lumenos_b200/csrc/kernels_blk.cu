@@ -361,13 +361,16 @@ __global__ void __launch_bounds__(CHAIN_THREADS, LMN_CHAIN_MINB) k_rs_chain(cons
         const int lmin = i > to ? i + 1 : to + 1;
 #pragma unroll 1
         for (int l = from; l >= lmin; l--) {
-            const u64 hm = R->half_mod[l][i], w = R->qlinv_w[l][i], ws = R->qlinv_ws[l][i];
+            // x_i <- (x_i - ((r_l mod q_i) - (half_l mod q_i))) q_l^-1 = (x_i + cadd - r_l) q_l^-1 mod q_i: r_l is not reduced first
+            // (the 3-product Shoup estimate takes any 64-bit value to [0, 3q)), and x_i stays lazy in [0, 3q) from step to step
+            const u64 ca = R->cadd[l][i], w = R->qlinv_w[l][i], ws = R->qlinv_ws[l][i];
             const u64 *rr = sm + ((size_t)(l - to - 1) * S) * CHAIN_THREADS + threadIdx.x;
 #pragma unroll
-            for (int r = 0; r < S; r++) {
-                const u64 t = sub_mod(barrett(rr[r * CHAIN_THREADS], q, mi.mu), hm, q);
-                v[r] = mul_shoup(v[r] + q - t, w, ws, q);
-            }
+            for (int r = 0; r < S; r++) v[r] = mul_shoup_approx(v[r] + ca - rr[r * CHAIN_THREADS], w, ws, fm.nq, fm.z);
+        }
+        if (lmin <= from) {
+#pragma unroll
+            for (int r = 0; r < S; r++) v[r] = csub(csub(v[r], 2 * q), q);
         }
         if (i > to) {
             const u64 half = R->half[i];
@@ -416,6 +419,7 @@ __global__ void __launch_bounds__(RA_THREADS, LMN_BLKFWD_MINB) k_blk_fwd(const M
     const int KP = k + np;   // k = limb stride of col (Q limbs of the context), KP = limb stride of acc
     const u64 w = MODE == 3 ? 0 : MODE == 2 ? R->qlinv_w[i] : C->pinv_w[i], ws = MODE == 3 ? 0 : MODE == 2 ? R->qlinv_ws[i] : C->pinv_ws[i];
     const size_t blk = (size_t)h * M;
+    const u64 qK = (u64)(3 * LOGN + 2) * q;
     int hd = 0;   // destination block of the automorphism
     if (MODE == 0) {
 #pragma unroll
@@ -473,9 +477,12 @@ __global__ void __launch_bounds__(RA_THREADS, LMN_BLKFWD_MINB) k_blk_fwd(const M
         const ulonglong2 *av = reinterpret_cast<const ulonglong2 *>(landA) + 4 * u;
 #pragma unroll
         for (int r = 0; r < 4; r++) {
+            // (v - a) w mod q without reducing a first: the transform's input is below 2q (k_down_pre / k_rs_pre reduce before their
+            // coupling levels), every level adds at most 3q, so a < (3 log N + 2) q =: qK and v + qK - a lies in (0, qK + q), below
+            // 2^64 by the modulus check of lmn_ctx_create; the 3-product Shoup estimate takes any 64-bit value to [0, 3q)
             ulonglong2 v = av[r];
-            v.x = mul_shoup(v.x + q - barrett(a[2 * r], q, md.mu), w, ws, q);
-            v.y = mul_shoup(v.y + q - barrett(a[2 * r + 1], q, md.mu), w, ws, q);
+            v.x = csub(csub(mul_shoup_approx(v.x + qK - a[2 * r], w, ws, fm.nq, fm.z), 2 * q), q);
+            v.y = csub(csub(mul_shoup_approx(v.y + qK - a[2 * r + 1], w, ws, fm.nq, fm.z), 2 * q), q);
             if (MODE != 0) reinterpret_cast<ulonglong2 *>(gout + blk + 8 * u)[r] = v;
             else { buf[PAD(8 * u + 2 * r)] = v.x; buf[PAD(8 * u + 2 * r + 1)] = v.y; }   // the thread's own last-pass slots
         }

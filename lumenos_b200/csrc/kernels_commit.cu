@@ -204,9 +204,10 @@ void launch_ct_stream(const Launch &L, const LeafFormat &F, const u64 *cts, uint
 }
 void launch_sha256_leaves(const Launch &L, const u64 *ser, uint32_t padded_len, uint32_t n_leaves, uint32_t *hashes) {
     LaunchScope scope(L, KID_SHA_LEAF);
-    // a leaf is one sequential SHA-256 chain, so the launch has only n_leaves threads: few lanes per warp spread the chains over more
-    // schedulers (8192 leaves = 256 full warps would leave more than half of the 592 schedulers idle)
-    static const int tpb = getenv("LMN_SHA_TPB") ? atoi(getenv("LMN_SHA_TPB")) : 8;   // measured 15.6 (32) / 14.9 (16) / 14.4 (8) / 14.2 ms (4) for 8192 leaves of 512 KiB
+    // a leaf is one sequential SHA-256 chain, so the launch has only n_leaves threads.  Lanes per warp (LMN_SHA_TPB), measured on B200:
+    // 256 leaves of 512 KiB: 15.6 ms (32 lanes) / 14.4 ms (8); 8192 leaves: 15.8 ms (32) / 24.1 ms (8) - full warps win once every
+    // scheduler has a chain to run
+    static const int tpb = getenv("LMN_SHA_TPB") ? atoi(getenv("LMN_SHA_TPB")) : 32;
     k_sha256_leaves<<<(n_leaves + tpb - 1) / tpb, tpb, 0, L.stream>>>(reinterpret_cast<const uint4 *>(ser), padded_len / 64, n_leaves, hashes);
 }
 void launch_sha256_nodes(const Launch &L, const uint32_t *children, uint32_t n_children, uint32_t *parents) {

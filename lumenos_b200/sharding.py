@@ -8,6 +8,7 @@ slices to whole ciphertexts: of the few hundred queried columns (exchange_querie
 columns (exchange_encoded, Commit's leaf rescale + Merkle span, after which the query stage is a local gather from the
 leaves), plus the gather of 32-byte leaf hashes for the tree (commit_tree).  All-to-all / all-gather over NCCL (NVLink) on
 the GPU box, gloo in the CPU tests."""
+import numpy as np
 import torch
 import torch.distributed as dist
 
@@ -90,3 +91,19 @@ def commit_tree(backend, leaves, leaf_format, rank, world, group=None):
     gathered = [torch.empty_like(local) for _ in range(world)]
     dist.all_gather(gathered, local, group=group)
     return fhe.MerkleTree(backend, None, None, leafHashes=b"".join(bytes(t.cpu().numpy().tobytes()) for t in gathered))
+
+
+def marshal_columns(backend, store, leafFormat, first=0, count=None):
+    """Wire format on a column shard (EncryptedProof.WriteTo, fhe/ligero.go:665-679): the ct.WriteTo streams of this rank's
+    ciphertexts.  Every stream has the same length L, so in the proof buffer rank r's MatR block starts at byte
+    11 + column_range(cols, r, world)[0] * L (MatZ: + cols * L); the host concatenates / writes the blocks at those offsets."""
+    import ctypes as C
+    from . import _capi
+    count = store.count - first if count is None else count
+    f = leafFormat.c_struct()
+    n = C.c_size_t()
+    _capi.check(_capi.lib().lmn_store_marshal(backend.ctx, store.h, first, count, C.byref(f), None, 0, C.byref(n)))
+    buf = np.empty(n.value, dtype=np.uint8)
+    if n.value:
+        _capi.check(_capi.lib().lmn_store_marshal(backend.ctx, store.h, first, count, C.byref(f), C.c_void_p(buf.ctypes.data), buf.nbytes, C.byref(n)))
+    return buf.tobytes()

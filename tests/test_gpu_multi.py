@@ -52,6 +52,16 @@ gr, gz = mr.download(), mz.download()
 for j in range(a, b):
     assert np.array_equal(gr[j - a], P.inner_sum_eval_column(S.cts[j], S.rpt, S.rows, S.gal, S.evks)[0])
     assert np.array_equal(gz[j - a], P.inner_sum_eval_column(S.cts[j], S.bpt, S.rows, S.gal, S.evks)[0])
+# wire format on the column shards: every rank marshals its own MatR / MatZ block, the blocks concatenated in rank order are the
+# MatR / MatZ sections of EncryptedProof.WriteTo (fhe/ligero.go:665-679)
+from oracle import oracle as O
+wf = fhe.LeafFormat(b"abc", b"\x05", b"\x09\x08\x07")      # odd lengths: streams are not multiples of 8 bytes
+parts_r, parts_z = [None] * world, [None] * world
+dist.all_gather_object(parts_r, sharding.marshal_columns(be, mr, wf))
+dist.all_gather_object(parts_z, sharding.marshal_columns(be, mz, wf))
+want_r = b"".join(O.leaf_bytes(P.inner_sum_eval_column(S.cts[j], S.rpt, S.rows, S.gal, S.evks)[0], wf.header, wf.polyHeader, wf.limbHeader) for j in range(S.cols))
+want_z = b"".join(O.leaf_bytes(P.inner_sum_eval_column(S.cts[j], S.bpt, S.rows, S.gal, S.evks)[0], wf.header, wf.polyHeader, wf.limbHeader) for j in range(S.cols))
+assert b"".join(parts_r) == want_r and b"".join(parts_z) == want_z, "sharded MatR / MatZ wire sections differ from the oracle"
 # Commit's Merkle span, sharded: slices -> column blocks, local leaf rescale + leaf hashes, gathered tree == the 1-GPU tree
 n = 2 * S.cols
 blk = sharding.exchange_encoded(e_sl, rank, world, chunks=2)
@@ -62,7 +72,6 @@ leaves = be.NewStore(b2 - a2, 1)
 _capi.check(lib.lmn_commit_leaves(be.ctx, est.h, leaves.h))
 lf = fhe.LeafFormat.lattigo_like(b"hdr-bytes", 1, P.N)
 tree = sharding.commit_tree(be, leaves, lf, rank, world)
-from oracle import oracle as O
 bufs = [O.leaf_bytes(P.rescale_to_level1(want_enc[j])[0], lf.header, lf.polyHeader, lf.limbHeader) for j in range(n)]
 want_tree = O.MerkleTree(bufs)
 assert tree.MerkleRoot() == want_tree.root(), "sharded Merkle root differs from the oracle"

@@ -435,3 +435,54 @@ def test_store_marshal_ranges_and_chunks():
             assert buf[j * L:(j + 1) * L].tobytes() == O.leaf_bytes(big[j], lf.header, lf.polyHeader, lf.limbHeader), "ciphertext %d" % j
         be12.Close()
     be.Close()
+
+
+@pytest.mark.parametrize("logN,rows,cols,k", [(8, 256, 16, 6), (8, 128, 16, 6)])
+def test_ligero_e2e_marshal_decrypt_verify(logN, rows, cols, k):
+    """TestLigeroE2E (fhe/ligero_test.go:70-176) end to end: Commit -> Prove -> MarshalBinary -> UnmarshalBinary -> Decrypt -> Verify,
+    then MatR / MatZ against the plaintext prover.  The acceptance test is the reference's own Proof.Verify (fhe/ligero.go:516-571)
+    restated on the decrypted values: Merkle path of every queried leaf, <col, r> == Encode(MatR)[idx], <col, b> == Encode(MatZ)[idx],
+    <MatZ, a> == P(z)."""
+    from lumenos_b200 import fhe
+    S = scenario(logN, rows, cols, k)
+    P = S.P
+    be = S.backend()
+    lf = fhe.LeafFormat.lattigo_like(b"\x01meta", 1, 1 << logN)
+    matrix = be.NewStore(cols).upload(S.cts)
+    zero = be.NewStore(1).upload(S.zero[None])
+    committer = fhe.LigeroCommitter(128, rows, cols, 2)
+    prover = committer.Commit(matrix, be, (zero, 0), leafFormat=lf)
+    idx = np.random.default_rng(17).integers(0, 2 * cols, size=committer.Queries).astype(np.uint32)
+    proof = prover.Prove(S.rpt, S.bpt, idx, be)
+    wire = proof.MarshalBinary(be, lf)                                                   # server -> client (ligero_test.go:118-126)
+    md, matR, matZ, qc, paths, root = fhe.EncryptedProof.UnmarshalBinary(wire, be.params, lf)
+    assert (md.Rows, md.Cols, md.RhoInv, md.Queries) == (rows, cols, 2, committer.Queries)
+    # EncryptedProof.Decrypt (ligero.go:381-502): MatR / MatZ -> slot 0, queried columns -> their `rows` slots
+    sc = proof.MatR.scale
+    dR = np.array([int(P.decrypt(S.sk, matR[j], sc)[0]) for j in range(cols)], dtype=np.uint64)
+    dZ = np.array([int(P.decrypt(S.sk, matZ[j], sc)[0]) for j in range(cols)], dtype=np.uint64)
+    # Proof.Verify (ligero.go:516-571)
+    encR, encZ = O.core_encode(dR, 2, S.roots), O.core_encode(dZ, 2, S.roots)
+    r = [int(x) % T for x in S.r]
+    b = [int(x) for x in S.b]
+    a = [pow(S.z, i, T) for i in range(cols)]
+    assert pow(S.z, cols, T) == (b[1] if rows > 1 else 1)                               # "zPow is not equal to powA"
+    for i, ix in enumerate(idx[:64]):
+        leaf = O.leaf_bytes(qc[i], lf.header, lf.polyHeader, lf.limbHeader)               # QueriedCols[i].Ct.WriteTo
+        assert fhe.VerifyMerklePath(leaf, paths[i], root, int(ix)), "merkle path of column %d" % ix
+        col = [int(v) for v in P.decrypt(S.sk, qc[i], proof.QueriedCols.scale)[:rows]]
+        assert sum(c * x for c, x in zip(col, r)) % T == int(encR[ix]), "well-formedness R check failed for column %d" % ix
+        assert sum(c * x for c, x in zip(col, b)) % T == int(encZ[ix]), "well-formedness B check failed for column %d" % ix
+    value = sum(int(S.M[i, j]) * b[i] % T * a[j] for i in range(rows) for j in range(cols)) % T   # P(z) of the committed polynomial
+    assert sum(int(x) * y for x, y in zip(dZ, a)) % T == value, "claimed value does not match the evaluation of the committed polynomial"
+    # LigeroProveReference (ligero_test.go:164-174)
+    for j in range(cols):
+        assert int(dR[j]) == sum(x * int(m) for x, m in zip(r, S.M[:, j])) % T
+        assert int(dZ[j]) == sum(x * int(m) for x, m in zip(b, S.M[:, j])) % T
+    # a tampered wire byte inside a queried column breaks its Merkle path
+    bad = bytearray(wire)
+    off_q = 11 + 2 * cols * (len(wire) - 11 - 32 - 32 * len(paths) * len(paths[0])) // (2 * cols + committer.Queries)
+    bad[off_q + len(lf.header) + len(lf.polyHeader) + len(lf.limbHeader) + 3] ^= 1
+    _, _, _, qc_bad, _, _ = fhe.EncryptedProof.UnmarshalBinary(bytes(bad), be.params, lf)
+    assert not fhe.VerifyMerklePath(O.leaf_bytes(qc_bad[0], lf.header, lf.polyHeader, lf.limbHeader), paths[0], root, int(idx[0]))
+    be.Close()

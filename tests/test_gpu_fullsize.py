@@ -173,3 +173,54 @@ def test_merkle_full_size_properties(logN, n_leaves):
     # a second build reproduces the root
     assert fhe.MerkleTree(be, leaves, lf).MerkleRoot() == lv[0]
     be.Close()
+
+
+def test_config_A_ligero_e2e_verify():
+    """BASELINE.json configs[0] = the reference's own test, at its own shape: TestLigeroE2E / TestLigeroPPD (fhe/ligero_test.go:13-19,
+    70-176), 2048 x 1024, LogN 12, k = log2(cols) = 10 Q primes (GenerateBGVParamsForNTT), rhoInv 2, 309 queries, REAL keys and
+    pk-encryptions of the ChaCha20 witness (P(1) known answer).  Commit -> Prove -> MarshalBinary -> ReadFrom -> Decrypt -> the checks of
+    Proof.Verify (fhe/ligero.go:516-571) -> MatR / MatZ == LigeroProveReference; two MatR columns also bit-for-bit against the oracle."""
+    from helpers import Scenario
+    from lumenos_b200 import fhe
+    rows, cols, logN, k = 2048, 1024, 12, 10
+    assert O.lib().orc_num_q_primes_for_ntt(cols, T) == k                 # fhe/bfv.go:147-154
+    S = Scenario(logN, rows, cols, k)
+    P = S.P
+    assert int(S.M.astype(object).sum() % T) == 59828798142202325        # results/baseline/client/bench_2048x1024_12.txt:22
+    be = S.backend()
+    lf = fhe.LeafFormat.lattigo_like(b"\x00" * 48, 1, 1 << logN)
+    matrix = be.NewStore(cols).upload(S.cts)
+    zero = be.NewStore(1).upload(S.zero[None])
+    committer = fhe.LigeroCommitter(128, rows, cols, 2)
+    assert committer.Queries == 309
+    prover = committer.Commit(matrix, be, (zero, 0), leafFormat=lf)
+    idx = (np.random.default_rng(5).integers(0, 2**62, size=309) % (2 * cols)).astype(np.uint32)
+    proof = prover.Prove(S.rpt, S.bpt, idx, be)
+    wire = proof.MarshalBinary(be, lf)
+    md, matR, matZ, qc, paths, root = fhe.EncryptedProof.UnmarshalBinary(wire, be.params, lf)
+    assert (md.Rows, md.Cols, md.RhoInv, md.Queries) == (rows, cols, 2, 309) and len(paths[0]) == 11 and root == prover.Root
+    sc = proof.MatR.scale
+    dR = np.array([int(P.decrypt(S.sk, matR[j], sc)[0]) for j in range(cols)], dtype=np.uint64)
+    dZ = np.array([int(P.decrypt(S.sk, matZ[j], sc)[0]) for j in range(cols)], dtype=np.uint64)
+    Mo = S.M.astype(object)
+    r = np.array([int(x) % T for x in S.r], dtype=object)
+    b = np.array([int(x) for x in S.b], dtype=object)
+    a = np.array([pow(S.z, i, T) for i in range(cols)], dtype=object)
+    # LigeroProveReference (ligero_test.go:164-174)
+    assert [int(x) for x in dR] == [int(x) % T for x in r.dot(Mo)], "MatR differs from the plaintext prover"
+    assert [int(x) for x in dZ] == [int(x) % T for x in b.dot(Mo)], "MatZ differs from the plaintext prover"
+    # Proof.Verify
+    encR, encZ = O.core_encode(dR, 2, S.roots), O.core_encode(dZ, 2, S.roots)
+    for i, ix in enumerate(idx):
+        leaf = O.leaf_bytes(qc[i], lf.header, lf.polyHeader, lf.limbHeader)
+        assert fhe.VerifyMerklePath(leaf, paths[i], root, int(ix)), "failed to verify merkle path for column %d" % ix
+        col = P.decrypt(S.sk, qc[i], proof.QueriedCols.scale)[:rows].astype(object)
+        assert int(col.dot(r)) % T == int(encR[ix]), "well-formedness R check failed for column %d" % ix
+        assert int(col.dot(b)) % T == int(encZ[ix]), "well-formedness B check failed for column %d" % ix
+    value = int(b.dot(Mo).dot(a)) % T
+    assert int(dZ.astype(object).dot(a)) % T == value, "claimed value does not match the evaluation of the committed polynomial"
+    # P1 on two columns
+    for j in (0, cols - 1):
+        want, _ = P.inner_sum_eval_column(S.cts[j], S.rpt, rows, S.gal, S.evks)
+        assert (matR[j] == want).all(), "MatR[%d] differs from the oracle" % j
+    be.Close()

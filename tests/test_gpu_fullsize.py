@@ -175,18 +175,19 @@ def test_merkle_full_size_properties(logN, n_leaves):
     be.Close()
 
 
-def test_config_A_ligero_e2e_verify():
+@pytest.mark.parametrize("rows,cols,logN,k,p1", [(2048, 1024, 12, 10, 59828798142202325), (4096, 2048, 12, 11, 78852759954010476)])
+def test_config_A_B_ligero_e2e_verify(rows, cols, logN, k, p1):
     """BASELINE.json configs[0] = the reference's own test, at its own shape: TestLigeroE2E / TestLigeroPPD (fhe/ligero_test.go:13-19,
     70-176), 2048 x 1024, LogN 12, k = log2(cols) = 10 Q primes (GenerateBGVParamsForNTT), rhoInv 2, 309 queries, REAL keys and
-    pk-encryptions of the ChaCha20 witness (P(1) known answer).  Commit -> Prove -> MarshalBinary -> ReadFrom -> Decrypt -> the checks of
-    Proof.Verify (fhe/ligero.go:516-571) -> MatR / MatZ == LigeroProveReference; two MatR columns also bit-for-bit against the oracle."""
+    pk-encryptions of the ChaCha20 witness (P(1) known answer); and configs[1], 4096 x 2048 (rows == N: InnerSum's row-swap step).
+    Commit -> Prove -> MarshalBinary -> ReadFrom -> Decrypt -> the checks of Proof.Verify (fhe/ligero.go:516-571) -> MatR / MatZ ==
+    LigeroProveReference; two MatR columns also bit-for-bit against the oracle."""
     from helpers import Scenario
     from lumenos_b200 import fhe
-    rows, cols, logN, k = 2048, 1024, 12, 10
     assert O.lib().orc_num_q_primes_for_ntt(cols, T) == k                 # fhe/bfv.go:147-154
     S = Scenario(logN, rows, cols, k)
     P = S.P
-    assert int(S.M.astype(object).sum() % T) == 59828798142202325        # results/baseline/client/bench_2048x1024_12.txt:22
+    assert int(S.M.astype(object).sum() % T) == p1        # results/baseline/client/bench_{2048x1024,4096x2048}_12.txt:22
     be = S.backend()
     lf = fhe.LeafFormat.lattigo_like(b"\x00" * 48, 1, 1 << logN)
     matrix = be.NewStore(cols).upload(S.cts)
@@ -198,7 +199,7 @@ def test_config_A_ligero_e2e_verify():
     proof = prover.Prove(S.rpt, S.bpt, idx, be)
     wire = proof.MarshalBinary(be, lf)
     md, matR, matZ, qc, paths, root = fhe.EncryptedProof.UnmarshalBinary(wire, be.params, lf)
-    assert (md.Rows, md.Cols, md.RhoInv, md.Queries) == (rows, cols, 2, 309) and len(paths[0]) == 11 and root == prover.Root
+    assert (md.Rows, md.Cols, md.RhoInv, md.Queries) == (rows, cols, 2, 309) and len(paths[0]) == (2 * cols - 1).bit_length() and root == prover.Root
     sc = proof.MatR.scale
     dR = np.array([int(P.decrypt(S.sk, matR[j], sc)[0]) for j in range(cols)], dtype=np.uint64)
     dZ = np.array([int(P.decrypt(S.sk, matZ[j], sc)[0]) for j in range(cols)], dtype=np.uint64)

@@ -269,8 +269,14 @@ __device__ __forceinline__ int nth_unused_bit(unsigned used, int nth, int nbits)
         if (!((used >> b) & 1u)) { if (c == nth) r = b; c++; }
     return r;
 }
+#ifndef LMN_ENC3_MINB
+#define LMN_ENC3_MINB 4   // measured at config D: 3 -> 54.5 ms per Encode, 4 -> 53.6 ms, 2 -> 59.1 ms (pass kernels, both passes)
+#endif
+#ifndef LMN_ENC4_MINB
+#define LMN_ENC4_MINB 2   // 1 -> 70.2 ms, 3 -> 62.2 ms
+#endif
 template <int LOGV>
-__global__ void __launch_bounds__(256, (LOGV <= 3 ? 3 : LOGV == 4 ? 2 : 1)) k_encode_pass_r(const EncPassArgs A, int chunks_per_cta) {
+__global__ void __launch_bounds__(256, (LOGV <= 2 ? 3 : LOGV == 3 ? LMN_ENC3_MINB : LOGV == 4 ? LMN_ENC4_MINB : 1)) k_encode_pass_r(const EncPassArgs A, int chunks_per_cta) {
     constexpr int V = 1 << LOGV, LT = LOGV + 3, T = 1 << LT;
     constexpr int NST = (LT + LOGV - 1) / LOGV;
     extern __shared__ __align__(16) u64 sm[];
@@ -379,7 +385,8 @@ void launch_encode_pass(const Launch &L, const EncPassArgs &A) {
     const uint32_t tiles = A.n >> A.log_tile;
     if (A.log_tile >= 5 && A.log_tile <= 8 && A.s1 - A.s0 == A.log_tile && !enc_tile_kernel_only()) {
         const int per_limb = 1 << (A.logn - 5);
-        const int cpc = per_limb >= 4 ? 4 : per_limb;
+        static const int cpc_max = getenv("LMN_ENC_CPC") ? atoi(getenv("LMN_ENC_CPC")) : 8;   // chunks per CTA (one scalar-table gather per CTA)
+        const int cpc = per_limb >= cpc_max ? cpc_max : per_limb;
         const int T = 1 << A.log_tile;
         const size_t smem = ((size_t)2 * A.log_tile * T + (size_t)T * ENC_C) * 8;
         const dim3 g((unsigned)(chunks / cpc), tiles);

@@ -351,8 +351,8 @@ def main():
     mac_levels = 11 if logN >= 12 else logN    # block pipeline: k_mac runs the 2048-point block transforms, the log2(N/2048) coupling levels are in k_modup
     mac_bfly = jobs * ntts * (N // 2) * mac_levels
     roofline_int = {"kernel": "k_mac", "bound": "int", "achieved": mac_bfly / mac_avg_s / 1e9, "peak": pk.value / 1e9, "unit": "Gbutterfly/s",
-                    "frac": mac_bfly / mac_avg_s / pk.value, "peak_source": "k_peak_bfly micro-kernel on this GPU, same run",
-                    "note": "counts only the NTT butterflies k_mac executes (%d of %d levels; the gadget MACs and reductions are extra integer work in the same kernel); ncu: sm__pipe_fmaheavy_cycles_active 72 %% (profiles/r1d_top_kernels.csv)" % (mac_levels, logN)}
+                    "frac": mac_bfly / mac_avg_s / pk.value, "peak_source": "k_peak_bfly micro-kernel on this GPU, same run: the product's own 3-product Shoup butterfly (ntt_blk.cuh bfly_ct3), register-resident, no loads or barriers",
+                    "note": "counts only the NTT butterflies k_mac executes (%d of %d levels; the gadget MACs (about 20 %% more multiplier work) and reductions are extra integer work in the same kernel); ncu: sm__pipe_fmaheavy_cycles_active 66 %% (profiles/r1j_top_kernels.csv)" % (mac_levels, logN)}
     ctw = 2 * k * (Ns if G > 1 else N) * 8
     enc_bytes = ((cols + 1 + n) + (2 * n if n > 256 else 0)) * ctw   # pass 1 (+ pass 2, in place) per step
     enc_s = enc_ms / args.steps * 1e-3

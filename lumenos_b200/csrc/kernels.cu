@@ -835,10 +835,12 @@ void launch_ring_decimate(const Launch &L, const DeviceTables &T, const KsJobs &
 }
 
 // =====================================================================================================
-// integer-pipe ceiling: the radix-8 butterfly network of ntt_fwd_smem on register-resident data (no loads, no
-// barriers), all SMs busy.  Denominator of the integer roofline of the NTT-bound kernels.
+// integer-pipe ceiling: the radix-8 butterfly network of the block transforms (ntt_blk.cuh: bfly_ct3, the 3-product Shoup butterfly
+// every NTT kernel of the product uses) on register-resident data (no loads, no barriers), all SMs busy.  Denominator of the
+// integer roofline of the NTT-bound kernels.
 __global__ void __launch_bounds__(256) k_peak_bfly(const ModDev *mods, int rounds, u64 *sink) {
-    const u64 q = mods[0].q, q2 = 2 * q;
+    const u64 q = mods[0].q;
+    const FwdMod fm = {q, 0 - q, mods[0].q3, (unsigned)mods[0].pad[0]};
     u64 a[8];
 #pragma unroll
     for (int r = 0; r < 8; r++) a[r] = (u64)(threadIdx.x * 8 + r + blockIdx.x) % q;
@@ -847,11 +849,11 @@ __global__ void __launch_bounds__(256) k_peak_bfly(const ModDev *mods, int round
     for (int r = 0; r < 7; r++) { w[r].x = (mods[0].ninv + r * 977) % q; w[r].y = mods[0].ninvs + r; }
     for (int it = 0; it < rounds; it++) {
 #pragma unroll
-        for (int r = 0; r < 4; r++) bfly_ct(a[r], a[r + 4], w[0], q, q2);
-        bfly_ct(a[0], a[2], w[1], q, q2); bfly_ct(a[1], a[3], w[1], q, q2);
-        bfly_ct(a[4], a[6], w[2], q, q2); bfly_ct(a[5], a[7], w[2], q, q2);
+        for (int r = 0; r < 4; r++) bfly_ct3(a[r], a[r + 4], w[0], fm);
+        bfly_ct3(a[0], a[2], w[1], fm); bfly_ct3(a[1], a[3], w[1], fm);
+        bfly_ct3(a[4], a[6], w[2], fm); bfly_ct3(a[5], a[7], w[2], fm);
 #pragma unroll
-        for (int r = 0; r < 4; r++) bfly_ct(a[2 * r], a[2 * r + 1], w[3 + r], q, q2);
+        for (int r = 0; r < 4; r++) bfly_ct3(a[2 * r], a[2 * r + 1], w[3 + r], fm);
 #pragma unroll
         for (int r = 0; r < 8; r++) a[r] = csub(a[r] >> 6, q);   // keep values bounded (cheap, ALU pipe)
     }

@@ -779,7 +779,8 @@ static int get_rs_chain(lmn_ctx *c, int from, int to, const RescaleChain **host,
     *host = &it->second.first; *dev = it->second.second;
     return 0;
 }
-static int rescale_jobs_to(lmn_ctx *c, int from_level, int to_level, const KsJobs &J) {
+// src != nullptr: the jobs' input ciphertexts are the consecutive entries of a store starting at src (not yet in J.col)
+static int rescale_jobs_to(lmn_ctx *c, int from_level, int to_level, const KsJobs &J, const u64 *src = nullptr) {
     Launch L = c->L();
     static const bool stepwise = getenv("LMN_RESCALE_STEPWISE") != nullptr;   // the one-limb-at-a-time evaluation, for A/B tests
     // log N >= 12, two or more steps: the whole chain in the coefficient domain (3 launches instead of 3 per step)
@@ -787,10 +788,11 @@ static int rescale_jobs_to(lmn_ctx *c, int from_level, int to_level, const KsJob
         (size_t)(from_level - to_level) * blk_blocks(c->logn) * 128 * 8 <= 96 * 1024 && 2 * (from_level + 1) <= MAX_LIMBS) {
         const RescaleChain *Rh, *Rd;
         if (int rc = get_rs_chain(c, from_level, to_level, &Rh, &Rd)) return rc;
-        launch_rescale_chain(L, c->T, Rd, *Rh, J);
+        launch_rescale_chain(L, c->T, Rd, *Rh, J, src, J.col_words);
         CK(cudaGetLastError());
         return 0;
     }
+    if (src) CK(cudaMemcpyAsync(J.col, src, (size_t)J.jobs * J.col_words * 8, cudaMemcpyDeviceToDevice, c->stream));   // the stepwise path works in place
     for (int l = from_level; l > to_level; l--) {
         const RescaleConsts *Rd;
         if (int rc = get_rs(c, l, &Rd)) return rc;
@@ -875,13 +877,14 @@ uint64_t lmn_rescale_scale(const lmn_ctx *c, uint32_t from_level, uint32_t to_le
 static int rescale_select(lmn_ctx *c, const lmn_store *enc, const uint32_t *idx, uint32_t n_idx, lmn_store *out) {
     const int Lmax = c->k - 1, lout = std::min(1, Lmax);
     if ((int)enc->level != Lmax || (int)out->level != lout || out->count < n_idx) return fail(LMN_ERR_INVALID, "rescale needs max-level input and a level-1 output store with one entry per index");
-    std::vector<uint32_t> iota;
-    if (!idx) { iota.resize(n_idx); for (uint32_t i = 0; i < n_idx; i++) iota[i] = i; idx = iota.data(); }
-    for (uint32_t i = 0; i < n_idx; i++) if (idx[i] >= enc->count) return fail(LMN_ERR_INVALID, "column index out of range");
+    const bool all = idx == nullptr;   // every entry in order (Commit's leaves): the first transform reads the store itself, no gather
+    if (all && n_idx > enc->count) return fail(LMN_ERR_INVALID, "column index out of range");
+    for (uint32_t i = 0; !all && i < n_idx; i++) if (idx[i] >= enc->count) return fail(LMN_ERR_INVALID, "column index out of range");
     cudaSetDevice(c->device);
-    if (c->ws_idx_cap < n_idx) { cudaFree(c->ws_idx); c->ws_idx = nullptr; c->ws_idx_cap = 0; CK(cudaMalloc(&c->ws_idx, n_idx * sizeof(uint32_t))); c->ws_idx_cap = n_idx; }
-    CK(cudaMemcpyAsync(c->ws_idx, idx, n_idx * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
-    if (!iota.empty()) CK(cudaStreamSynchronize(c->stream));   // the pageable source dies with this frame
+    if (!all) {
+        if (c->ws_idx_cap < n_idx) { cudaFree(c->ws_idx); c->ws_idx = nullptr; c->ws_idx_cap = 0; CK(cudaMalloc(&c->ws_idx, n_idx * sizeof(uint32_t))); c->ws_idx_cap = n_idx; }
+        CK(cudaMemcpyAsync(c->ws_idx, idx, n_idx * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+    }
     const uint32_t bc = c->batch;
     if (int rc = ensure_workspace(c, std::min(bc, n_idx))) return rc;
     Launch L = c->L();
@@ -889,8 +892,8 @@ static int rescale_select(lmn_ctx *c, const lmn_store *enc, const uint32_t *idx,
     for (uint32_t j0 = 0; j0 < n_idx; j0 += bc) {
         const uint32_t nj = std::min(bc, n_idx - j0);
         KsJobs J = jobs_view(c, 0, nj);
-        launch_gather_in(L, c->T, enc->d, enc->words(), c->ws_idx + j0, J);
-        if (int rc = rescale_jobs_to(c, Lmax, lout, J)) return rc;
+        if (!all) launch_gather_in(L, c->T, enc->d, enc->words(), c->ws_idx + j0, J);
+        if (int rc = rescale_jobs_to(c, Lmax, lout, J, all ? enc->d + (size_t)j0 * enc->words() : nullptr)) return rc;
         launch_pack_out(L, c->T, J, lout + 1, out->d + j0 * out_words);
     }
     CK(cudaGetLastError());

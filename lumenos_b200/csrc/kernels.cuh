@@ -183,7 +183,9 @@ void launch_rs_blk(const Launch &L, const DeviceTables &T, const RescaleConsts *
 // pointwise in the coefficient domain (k_rs_chain), one block NTT of the surviving limbs.  Bit-identical to the step-by-step
 // evaluation (every step is exact arithmetic mod q_i and the NTT is linear), with 2 (from + to + 2) limb transforms per
 // ciphertext instead of 2 sum_l (l + 1).
-void launch_rescale_chain(const Launch &L, const DeviceTables &T, const RescaleChain *Cd, const RescaleChain &Ch, const KsJobs &J);
+// src != nullptr: job j's input ciphertext ([2][k][N], max level) is read from src + j * src_job_words instead of J.col
+void launch_rescale_chain(const Launch &L, const DeviceTables &T, const RescaleChain *Cd, const RescaleChain &Ch, const KsJobs &J,
+                          const u64 *src = nullptr, uint64_t src_job_words = 0);
 // block NTT + gadget MAC of the block pipeline (kernels_mac.cu)
 void launch_mac_blk(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch, const KsJobs &J, const u64 *evk);
 const char *kernels_mac_init();

@@ -583,11 +583,13 @@ void launch_rs_blk(const Launch &L, const DeviceTables &T, const RescaleConsts *
     LMN_DISPATCH_S(SB, k_blk_fwd<SS, 2><<<g, RA_THREADS, BLK_FWD_SMEM, L.stream>>>(T.mods, T.twb_fwd, nullptr, Rd, J, 0u, level, T.k, T.np, J.jobs, jb));
 }
 
-void launch_rescale_chain(const Launch &L, const DeviceTables &T, const RescaleChain *Cd, const RescaleChain &Ch, const KsJobs &J) {
+void launch_rescale_chain(const Launch &L, const DeviceTables &T, const RescaleChain *Cd, const RescaleChain &Ch, const KsJobs &J,
+                          const u64 *src, uint64_t src_job_words) {
     const int SB = blk_blocks(T.logn);
     const int nl = Ch.from + 1;
     BlkSlots A;
-    A.src = J.col; A.src_job_words = J.col_words; A.dst = J.acc; A.dst_job_words = J.acc_words; A.nslots = 2 * nl;
+    // only the first transform reads the input ciphertexts: they may stay where they are (a store), the results go to J.col
+    A.src = src ? src : J.col; A.src_job_words = src ? src_job_words : J.col_words; A.dst = J.acc; A.dst_job_words = J.acc_words; A.nslots = 2 * nl;
     for (int c = 0; c < 2; c++)
         for (int i = 0; i < nl; i++) { A.mod[c * nl + i] = i; A.src_limb[c * nl + i] = (uint32_t)(c * T.k + i); A.dst_limb[c * nl + i] = (uint32_t)(c * nl + i); }
     launch_blk_intt(L, T, A, J.jobs, KID_RS_INTT);

@@ -66,15 +66,9 @@ __device__ __forceinline__ uint32_t leaf_byte(const LeafFormat &F, const u64 *__
     return (uint32_t)(w >> (8 * (b & 7))) & 0xffu;
 }
 
-// out[leaf][w] = bytes 8w..8w+7 of the padded stream (little-endian packing of the byte sequence into the u64)
-__global__ void __launch_bounds__(256) k_leaf_serialize(const LeafFormat F, const u64 *__restrict__ cts, uint64_t ct_words,
-                                                        u64 *__restrict__ out) {
-    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
-    if (w >= F.padded_len / 8) return;
-    const u64 *ct = cts + (size_t)blockIdx.y * ct_words;
+// word w of the padded stream of one leaf: bytes 8w..8w+7 (little-endian packing of the byte sequence into the u64)
+__device__ __forceinline__ u64 leaf_word(const LeafFormat &F, const u64 *__restrict__ ct, uint32_t w) {
     const uint32_t pos = 8 * w;
-    u64 v = 0;
-    bool done = false;
     if (pos >= F.hdr_len && pos + 8 <= F.total_len) {
         // fast path: the 8 bytes lie inside the coefficients of one limb
         const uint32_t p0 = pos - F.hdr_len;
@@ -85,25 +79,36 @@ __global__ void __launch_bounds__(256) k_leaf_serialize(const LeafFormat F, cons
             if (s >= F.limb_hdr_len && s + 8 <= F.limb_len) {
                 const uint32_t b = s - F.limb_hdr_len, sh = 8 * (b & 7);
                 const u64 *src = ct + (((size_t)poly * F.nl + limb) << F.logn) + (b >> 3);
-                v = src[0] >> sh;
+                u64 v = src[0] >> sh;
                 if (sh) v |= src[1] << (64 - sh);
-                done = true;
+                return v;
             }
         }
     }
-    if (!done) {
+    u64 v = 0;
 #pragma unroll 1
-        for (int i = 0; i < 8; i++) {
-            const uint32_t p = pos + i;
-            uint32_t byte;
-            if (p < F.total_len) byte = leaf_byte(F, ct, p);
-            else if (p == F.total_len) byte = 0x80;
-            else if (p < F.padded_len - 8) byte = 0;
-            else byte = (uint32_t)((8ull * F.total_len) >> (8 * (F.padded_len - 1 - p))) & 0xffu;   // big-endian bit length
-            v |= (u64)byte << (8 * i);
-        }
+    for (int i = 0; i < 8; i++) {
+        const uint32_t p = pos + i;
+        uint32_t byte;
+        if (p < F.total_len) byte = leaf_byte(F, ct, p);
+        else if (p == F.total_len) byte = 0x80;
+        else if (p < F.padded_len - 8) byte = 0;
+        else byte = (uint32_t)((8ull * F.total_len) >> (8 * (F.padded_len - 1 - p))) & 0xffu;   // big-endian bit length
+        v |= (u64)byte << (8 * i);
     }
-    out[(size_t)blockIdx.y * (F.padded_len / 8) + w] = v;
+    return v;
+}
+// out[leaf][2w], out[leaf][2w+1]: two words (one 16-byte store) per thread; the padded length is a multiple of 64 bytes
+__global__ void __launch_bounds__(256) k_leaf_serialize(const LeafFormat F, const u64 *__restrict__ cts, uint64_t ct_words,
+                                                        u64 *__restrict__ out) {
+    const uint32_t w2 = 2 * (blockIdx.x * blockDim.x + threadIdx.x);
+    const uint32_t words = F.padded_len / 8;
+    if (w2 >= words) return;
+    const u64 *ct = cts + (size_t)blockIdx.y * ct_words;
+    ulonglong2 v;
+    v.x = leaf_word(F, ct, w2);
+    v.y = leaf_word(F, ct, w2 + 1);
+    reinterpret_cast<ulonglong2 *>(out + (size_t)blockIdx.y * words)[w2 >> 1] = v;
 }
 
 // Wire format of the proof (EncryptedProof.WriteTo, fhe/ligero.go:660-691): MatR, MatZ and QueriedCols are written as
@@ -195,7 +200,7 @@ __global__ void k_sha256_nodes(const uint32_t *__restrict__ children, uint32_t n
 void launch_leaf_serialize(const Launch &L, const LeafFormat &F, const u64 *cts, uint64_t ct_words, uint32_t n_leaves, u64 *out) {
     LaunchScope scope(L, KID_LEAF_SER);
     const uint32_t words = F.padded_len / 8;
-    k_leaf_serialize<<<dim3((words + 255) / 256, n_leaves), 256, 0, L.stream>>>(F, cts, ct_words, out);
+    k_leaf_serialize<<<dim3((words / 2 + 255) / 256, n_leaves), 256, 0, L.stream>>>(F, cts, ct_words, out);
 }
 void launch_ct_stream(const Launch &L, const LeafFormat &F, const u64 *cts, uint64_t ct_words, uint64_t byte0, uint64_t byte_end, u64 *out) {
     LaunchScope scope(L, KID_LEAF_SER);

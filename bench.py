@@ -32,7 +32,12 @@ sys.path.insert(0, ROOT)
 CONFIGS = {  # rows, cols, logN  (scripts/benchmark_server.sh:34-39, README.md:59-61)
     "A": (2048, 1024, 12), "B": (4096, 2048, 12), "C": (8192, 4096, 13), "D": (16384, 4096, 14),
 }
-NCU_MAC_TRAFFIC_PER_JOB_D = (3.611e9 + 0.924e9) / 256   # bytes per job, profiles/r1d_top_kernels.csv
+NCU_MAC_TRAFFIC_PER_JOB_D = (3.611e9 + 0.924e9) / 256   # bytes per job, profiles/r1d_top_kernels.csv (r1j: 10.49 GB per 592-job launch, the same per job)
+NCU_ENCODE_TRAFFIC_D = 92.6e9                           # both passes, profiles/r1k_encode_kernels.csv
+# sm__pipe_fmaheavy_cycles_active (% of peak) of each hot kernel class from the committed ncu captures (profiles/r1j_top_kernels.csv,
+# r1k_commit_kernels.csv): the hardware's own reading of how busy the multiplier pipe is, next to the modelled fractions below
+NCU_FMAHEAVY = {"k_mac": 66.0, "k_modup": 76.0, "k_down_pre": 79.0, "k_intt_c1": 65.0, "k_pintt": 65.0, "k_down": 51.0, "k_rs_pre": 57.0,
+                "k_rs_intt": 65.0}
 PUBLISHED_COMMIT_S = {"A": 1.03, "B": 2.04, "C": 9.17, "D": 18.79}  # "Commit eval": leaf rescale + Merkle (BASELINE.md:23)
 PUBLISHED_S = {"A": 14.77, "B": 36.80, "C": 179.93, "D": 397.85}  # Encode + Prove eval, m7i.8xlarge 32 vCPU
 RHO_INV, SECURITY_BITS = 2, 128
@@ -91,8 +96,8 @@ def cpu_reference_sample(cfg, threads, enc_lanes=2048, ip_cols=None, q_cols=None
     P = O.Params(logN, k=k)
     N, n = P.N, cols * RHO_INV
     rng = np.random.default_rng(5)
-    ip_cols = ip_cols or threads
-    q_cols = q_cols or threads
+    ip_cols = ip_cols or 4 * threads       # >= 64 column-vectors on 16 cores, 4 per thread: the sample stops moving +-5 % run to run
+    q_cols = q_cols or 2 * threads
     # Encode: the reference runs it on ONE goroutine (fhe/code.go, fhe/ntt.go have no worker pool)
     roots = O.field_roots_forward(n)
     limb_of_lane = (np.arange(enc_lanes) * k // enc_lanes).astype(np.int32)
@@ -135,6 +140,45 @@ def fheq(cfg):
     return fhe.calculateQueries(SECURITY_BITS, RHO_INV)
 
 
+def work_per_job(k, np_, logN):
+    """Integer work of one column-job (one ciphertext) in one launch of each block-pipeline kernel class at the top level:
+    `butterflies` = NTT butterflies (one Shoup modmul + two additions each), `modmuls` = butterflies + every other 64-bit modular
+    multiplication the class performs (scalings, base-conversion products, epilogues, rescale steps), `macs` = gadget
+    multiply-accumulates (k_mac only; NOT in modmuls).  N = 2048 S; a block transform has 11 levels, the log2 S coupling levels
+    live in the pointwise kernels."""
+    N = 1 << logN
+    c = max(0, logN - 11)                       # coupling levels
+    KP, beta = k + np_, (k + np_ - 1) // np_
+    dig = [min(np_, k - d * np_) for d in range(beta)]
+    blk = N // 2 * min(11, logN)                # butterflies of the block levels of one limb
+    w = {}
+    w["k_intt_c1"] = {"butterflies": k * blk, "other": 0}
+    w["k_modup"] = {"butterflies": sum(c * nd * N // 2 + c * (KP - nd) * N // 2 for nd in dig),
+                    "other": sum(nd * N + (KP - nd) * nd * N for nd in dig)}
+    w["k_mac"] = {"butterflies": sum(KP - nd for nd in dig) * blk, "other": 0, "macs": beta * 2 * KP * N}
+    w["k_pintt"] = {"butterflies": 2 * np_ * blk, "other": 0}
+    w["k_down_pre"] = {"butterflies": 2 * (c * np_ * N // 2 + c * k * N // 2), "other": 2 * (np_ * N + k * np_ * N)}
+    w["k_down"] = {"butterflies": 2 * k * blk, "other": 2 * k * N}
+    # chained rescale from level k-1 to 1 (fhe/ligero.go:331-333): limb i takes part in the steps that drop the limbs above it
+    steps = sum(l for l in range(2, k))         # sum over dropped limbs l = k-1 .. 2 of the l limbs below: (x_i - r_l) q_l^-1
+    w["k_rs_intt"] = {"butterflies": 2 * k * blk, "other": 0}
+    w["k_rs_pre"] = {"butterflies": 2 * (c * k * N // 2 + c * min(2, k) * N // 2), "other": 2 * (k * N + steps * N)}
+    w["k_rs_apply"] = {"butterflies": 2 * min(2, k) * blk, "other": 0}
+    for v in w.values():
+        v["modmuls"] = v["butterflies"] + v["other"]
+        v.setdefault("macs", 0)
+    return w
+
+
+def workload_string(cfg, cols_override=0):
+    """config.workload, identical in both arms (the driver compares the strings)"""
+    from lumenos_b200 import hostutil as H
+    rows, cols, logN = CONFIGS[cfg]
+    k = H.num_q_primes_for_ntt(cols, H.T_DEFAULT)
+    return "%s%s: %dx%d LogN=%d k=%d encode + prove eval (inner products r,b + %d query columns)" % (
+        cfg, " (PROFILING SUBSET of %d columns)" % cols_override if cols_override else "", rows, cols, logN, k, fheq(cfg))
+
+
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -142,7 +186,7 @@ def run_reference_arm(args):
     threads = os.cpu_count() or 1
     vals, desc, parts = [], "", {}
     for i in range(args.warmup + args.steps):
-        v, desc, parts = cpu_reference_sample(args.config, threads, enc_lanes=1024, ip_cols=threads, q_cols=threads)
+        v, desc, parts = cpu_reference_sample(args.config, threads, enc_lanes=1024)
         if i >= args.warmup:
             vals.append(v)
     rows, cols, logN = CONFIGS[args.config]
@@ -151,7 +195,7 @@ def run_reference_arm(args):
         "impl": "reference", "metric": "ligero_server_prove_eval_s", "value": value, "unit": "s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": value * 1e3, "higher_is_better": False, "scaling": "strong",
         "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-        "config": {"workload": "%s: %dx%d LogN=%d encode + prove eval (inner products r,b + %d query columns)" % (args.config, rows, cols, logN, fheq(args.config))},
+        "config": {"workload": workload_string(args.config)},
         "cpu_baseline": {"value": value, "unit": "s", "cores": threads, "kind": "port", "sample": desc, "parts": parts},
         "e2e": {"value": value, "unit": "s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "reference = Go + un-vendored Lattigo; no Go toolchain here, so the CPU arm is the C port (oracle/); published m7i.8xlarge number: %.2f s" % PUBLISHED_S[args.config],
@@ -170,6 +214,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-commit", action="store_true", help="skip the Commit Merkle span (reported beside the headline)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the untimed oracle self-check of one seeded step")
     ap.add_argument("--cols-override", type=int, default=0, help="profiling only: shrink the matrix to this many columns, keeping the named config's k, N and rows")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -210,12 +255,16 @@ def main():
     beta = (k + len(p) - 1) // len(p)
 
     # Galois keys: random canonical residues in the evk layout [beta][2][k+np][N]
-    for g in params.GaloisElementsForInnerSum(1, rows):
+    gal_els, evks_host = params.GaloisElementsForInnerSum(1, rows), []
+    for g in gal_els:
         evk = np.empty((beta, 2, k + len(p), N), np.uint64)
         for i, m in enumerate(mods):
             evk[:, :, i, :] = rng.integers(0, m, size=(beta, 2, N), dtype=np.uint64)
         be.LoadGaloisKey(g, evk)
+        if not args.no_parity:
+            evks_host.append(evk)      # the oracle self-check evaluates sampled columns with the same keys
     del evk
+    torch.manual_seed(1234 + rank)
 
     def rand_cts(count, coeffs):
         t = torch.empty((count, 2, k, coeffs), dtype=torch.int64, device=dev)
@@ -283,6 +332,55 @@ def main():
             dist.barrier()
         torch.cuda.synchronize(dev)
 
+    def parity_check():
+        """One untimed step on this rank's seeded inputs; sampled outputs are compared bit for bit with the CPU oracle (the checker,
+        never the thing measured): a lane sample of the encoded matrix, 3 MatR columns, 1 MatZ column and 2 queried columns per rank.
+        At N > 1 the whole encoded ciphertext of a queried column is assembled for the oracle by a plain all_gather of its slices,
+        independently of the product's own exchange."""
+        from oracle import oracle as O
+        t0 = time.perf_counter()
+        P = O.Params(logN, q=np.array(q, np.uint64), p=np.array(p, np.uint64), t=T)
+        step()
+        torch.cuda.synchronize(dev)
+        u = lambda t: t.cpu().numpy().astype(np.uint64)  # noqa: E731
+        bad = []
+        coeffs = Ns if G > 1 else N
+        rs = np.random.default_rng(4242 + rank)
+        lanes = np.sort(rs.choice(2 * k * coeffs, size=256, replace=False))
+        lt = torch.as_tensor(lanes, device=dev)
+        want = P.fhe_encode_lanes(u(mat_enc_t.view(cols, -1)[:, lt]), RHO_INV, u(zero_t.view(1, -1)[0, lt]),
+                                  ((lanes // coeffs) % k).astype(np.int32), field.roots)
+        if not np.array_equal(u(enc_t.view(n, -1)[:, lt]), want):
+            bad.append("EncodedMatrix lane sample")
+        gr, gz = matR.download(), matZ.download()
+        for j in sorted({0, cols_loc // 2, cols_loc - 1}):
+            ct = u(mat_cols_t[j])
+            if not np.array_equal(gr[j], P.inner_sum_eval_column(ct, rpt, rows, gal_els, evks_host)[0]):
+                bad.append("MatR[%d]" % j)
+            if j == 0 and not np.array_equal(gz[j], P.inner_sum_eval_column(ct, bpt, rows, gal_els, evks_host)[0]):
+                bad.append("MatZ[%d]" % j)
+        gq = queried.download()
+        for r in range(G):
+            qs = sharding.queries_of(nq_total, r, G)
+            for pos in sorted({0, len(qs) - 1}):
+                col = int(qidx[qs[pos]])
+                if G == 1:
+                    full = enc_t[col]
+                else:
+                    parts = [torch.empty_like(enc_t[col]) for _ in range(G)]
+                    dist.all_gather(parts, enc_t[col].contiguous())
+                    full = torch.cat(parts, dim=-1)
+                if r == rank and not np.array_equal(gq[pos], P.rescale_to_level1(u(full))[0]):
+                    bad.append("QueriedCols[%d] (column %d)" % (qs[pos], col))
+        flag = torch.tensor([len(bad)], device=dev)
+        if G > 1:
+            dist.all_reduce(flag)
+        if bad:
+            log("[rank %d] PARITY FAILURE against the oracle: %s" % (rank, ", ".join(bad)))
+        if int(flag.item()):
+            raise SystemExit("parity check against the oracle failed on %d sampled outputs" % int(flag.item()))
+        return "ok: per rank 256 encoded lanes x %d, 3 MatR + 1 MatZ columns, 2 queried columns bit-identical to the oracle (%.0f s, untimed)" % (n, time.perf_counter() - t0)
+
     def timed(fn, steps):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -303,13 +401,22 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
+    parity = parity_check() if not args.no_parity else "skipped (--no-parity)"
     for _ in range(args.warmup):
         step()
     # device-resident timing; the dominant kernel (k_mac) and the HBM-bound Encode kernel are bracketed with event pairs
     KID = {lib.lmn_kernel_name(i).decode(): i for i in range(lib.lmn_kernel_count())}
+
+    def prof_reset():
+        for i in range(lib.lmn_kernel_count()):
+            lib.lmn_profile_read(be.ctx, i, None, None, None, 1)
+
+    def prof(name):
+        ms, cnt, jb = C.c_double(), C.c_uint64(), C.c_uint64()
+        _capi.check(lib.lmn_profile_read(be.ctx, KID[name], C.byref(ms), C.byref(cnt), C.byref(jb), 1))
+        return ms.value, cnt.value, jb.value
     _capi.check(lib.lmn_profile_enable(be.ctx, (1 << KID["k_mac"]) | (1 << KID["k_encode_pass"])))
-    for i in range(lib.lmn_kernel_count()):
-        lib.lmn_profile_read(be.ctx, i, None, None, 1)
+    prof_reset()
     launches0 = be.LaunchCount()
     sampler = ClockSampler(local)
     sampler.start()
@@ -317,13 +424,8 @@ def main():
     clocks = sampler.stop()
     gpu_launches = be.LaunchCount() - launches0
     ms_per_step = total_ms / args.steps
-
-    def prof(name):
-        ms, cnt = C.c_double(), C.c_uint64()
-        _capi.check(lib.lmn_profile_read(be.ctx, KID[name], C.byref(ms), C.byref(cnt), 1))
-        return ms.value, cnt.value
-    mac_ms, mac_n = prof("k_mac")
-    enc_ms, enc_n = prof("k_encode_pass")
+    mac_ms, mac_n, mac_jobs = prof("k_mac")
+    enc_ms, enc_n, _ = prof("k_encode_pass")
     _capi.check(lib.lmn_profile_enable(be.ctx, 0))
 
     peaks = {}
@@ -333,47 +435,62 @@ def main():
         pass
     hbm_peak, hbm_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback (B200_PROFILING.md)")
     np_ = len(p)
-    jobs = min(args.batch, 2 * cols_loc)
     limb_b = N * 8
-    # k_mac algorithmic bytes per launch: per job read y (k limbs) + c1 (k limbs), write 2(k+np) accumulator limbs; evk once per launch
-    mac_bytes = jobs * (2 * k + 2 * (k + np_)) * limb_b + beta * 2 * (k + np_) * limb_b
-    mac_avg_s = mac_ms / max(1, mac_n) * 1e-3
-    roofline = {"kernel": "k_mac (ModUp + NTT + gadget MAC; integer-bound, reported against HBM as the contract asks)", "bound": "hbm",
-                "achieved": mac_bytes / mac_avg_s / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": mac_bytes / mac_avg_s / 1e9 / hbm_peak,
-                "traffic": (NCU_MAC_TRAFFIC_PER_JOB_D * jobs if args.config == "D" and not args.cols_override else None),
-                "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of k_mac_rd<8> at 256 jobs per launch (profiles/r1d_top_kernels.csv), scaled per job; includes the base-converted digits written by k_modup_blk (an intermediate of the split pipeline, not in the algorithmic bytes)",
-                "peak_source": hbm_src, "avg_launch_ms": mac_avg_s * 1e3, "launches": mac_n,
-                "share_of_step": mac_ms / total_ms}
-    # integer roofline of the same kernel: NTT butterflies per launch / measured register-resident butterfly ceiling
+    # integer ceiling: the product's own 3-product Shoup butterfly, register-resident, on every SM (lmn_bench_int_peak), this run
     pk = C.c_double()
     _capi.check(lib.lmn_bench_int_peak(be.ctx, C.byref(pk)))
-    ntts = sum((k + np_) - min(np_, k - d * np_) for d in range(beta))   # (digit, target) pairs that need ModUp + NTT
-    mac_levels = 11 if logN >= 12 else logN    # block pipeline: k_mac runs the 2048-point block transforms, the log2(N/2048) coupling levels are in k_modup
-    mac_bfly = jobs * ntts * (N // 2) * mac_levels
-    roofline_int = {"kernel": "k_mac", "bound": "int", "achieved": mac_bfly / mac_avg_s / 1e9, "peak": pk.value / 1e9, "unit": "Gbutterfly/s",
-                    "frac": mac_bfly / mac_avg_s / pk.value, "peak_source": "k_peak_bfly micro-kernel on this GPU, same run: the product's own 3-product Shoup butterfly (ntt_blk.cuh bfly_ct3), register-resident, no loads or barriers",
-                    "note": "counts only the NTT butterflies k_mac executes (%d of %d levels; the gadget MACs (about 20 %% more multiplier work) and reductions are extra integer work in the same kernel); ncu: sm__pipe_fmaheavy_cycles_active 66 %% (profiles/r1j_top_kernels.csv)" % (mac_levels, logN)}
+    sm_mhz = clocks.get("sm_mhz") or 1965.0
+    fma_bound = 148 * 4 * 32 * sm_mhz * 1e6 / 24.0     # butterflies/s if the fmaheavy pipe did nothing but the butterfly's multiplies
+    work = work_per_job(k, np_, logN)
+    mac_avg_s = mac_ms / max(1, mac_n) * 1e-3
+    jobs_avg = mac_jobs / max(1, mac_n)                 # from the library's own launch accounting (the last batch of a rank is shorter)
+    mac_bfly = jobs_avg * work["k_mac"]["butterflies"]
+    roofline = {"kernel": "k_mac (k_mac_rd: block NTT of the base-converted digits + gadget MAC; the dominant kernel)", "bound": "int",
+                "achieved": mac_bfly / mac_avg_s / 1e9, "peak": pk.value / 1e9, "unit": "Gbutterfly/s", "frac": mac_bfly / mac_avg_s / pk.value,
+                "peak_source": "lmn_bench_int_peak, this run: the product's own 3-product Shoup butterfly (ntt_blk.cuh bfly_ct3), register-resident on all SMs, no loads or barriers",
+                "peak_fmaheavy_only": fma_bound / 1e9,
+                "peak_fmaheavy_only_note": "148 SMs x 4 sub-partitions x 32 lanes x %.0f MHz / 24 fmaheavy pipe-cycles per butterfly (6 wide multiplies of 4 cycles, tools/int_pipe_probe.cu): the butterfly ceiling above is %.0f %% of it because the ALU and issue slots of the same butterfly are not free" % (sm_mhz, 100 * pk.value / fma_bound),
+                "frac_of_fmaheavy_only": mac_bfly / mac_avg_s / fma_bound,
+                "work_per_launch": {"jobs": jobs_avg, "butterflies_per_job": work["k_mac"]["butterflies"], "gadget_macs_per_job": work["k_mac"]["macs"],
+                                    "note": "butterflies = (digit, target modulus) pairs x N/2 x 11 block levels; the gadget MACs and Montgomery reductions (not counted in achieved) are extra integer work of the same kernel"},
+                "avg_launch_ms": mac_avg_s * 1e3, "launches": mac_n, "share_of_step": mac_ms / total_ms,
+                "traffic": (NCU_MAC_TRAFFIC_PER_JOB_D * jobs_avg if args.config == "D" else None),
+                "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of k_mac_rd<8> (profiles/, see NCU_MAC_TRAFFIC_PER_JOB_D), scaled per job",
+                "ncu_fmaheavy_pct": NCU_FMAHEAVY.get("k_mac")}
+    # the same kernel against HBM (it is not HBM-bound: kept so the reader sees both ceilings)
+    mac_bytes = jobs_avg * (2 * k + 2 * (k + np_)) * limb_b + beta * 2 * (k + np_) * limb_b
+    roofline_hbm = {"kernel": "k_mac", "bound": "hbm", "achieved": mac_bytes / mac_avg_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                    "frac": mac_bytes / mac_avg_s / 1e9 / hbm_peak, "peak_source": hbm_src,
+                    "algorithmic_bytes_per_launch": mac_bytes,
+                    "note": "per job read y (k limbs) + c1 (k limbs), write 2(k+np) accumulator limbs; evk once per launch"}
     ctw = 2 * k * (Ns if G > 1 else N) * 8
-    enc_bytes = ((cols + 1 + n) + (2 * n if n > 256 else 0)) * ctw   # pass 1 (+ pass 2, in place) per step
+    enc_alg = (cols + 1 + n) * ctw                       # matrix + zero column read once, encoded matrix written once
+    enc_two_pass = enc_alg + (2 * n * ctw if n > 256 else 0)
     enc_s = enc_ms / args.steps * 1e-3
-    roofline_encode = {"kernel": "k_encode_pass (both passes of one Encode)", "bound": "hbm", "achieved": enc_bytes / enc_s / 1e9, "peak": hbm_peak,
-                       "unit": "GB/s", "frac": enc_bytes / enc_s / 1e9 / hbm_peak,
-                       "traffic": (91.0e9 if args.config == "D" and G == 1 and not args.cols_override else None),
-                       "traffic_source": "ncu --set full at config D: pass 1 13.3 GB read + 25.9 GB written, pass 2 25.8 + 26.0 GB (profiles/r1f_encode_kernels.csv)",
-                       "ms_per_step": enc_s * 1e3,
-                       "algorithmic_min_bytes": (cols + 1 + n) * ctw, "share_of_step": enc_ms / total_ms}
+    roofline_encode = {"kernel": "k_encode_pass (both passes of one Encode)", "bound": "hbm", "achieved": enc_alg / enc_s / 1e9, "peak": hbm_peak,
+                       "unit": "GB/s", "frac": enc_alg / enc_s / 1e9 / hbm_peak, "peak_source": hbm_src,
+                       "algorithmic_bytes": enc_alg, "frac_two_pass": enc_two_pass / enc_s / 1e9 / hbm_peak, "two_pass_bytes": enc_two_pass,
+                       "traffic": (NCU_ENCODE_TRAFFIC_D if args.config == "D" and G == 1 and not args.cols_override else None),
+                       "traffic_source": "ncu --set full at config D, both passes (profiles/, see NCU_ENCODE_TRAFFIC_D)",
+                       "ms_per_step": enc_s * 1e3, "share_of_step": enc_ms / total_ms}
 
-    # kernel-class breakdown of one extra (untimed) step
-    for i in range(lib.lmn_kernel_count()):
-        lib.lmn_profile_read(be.ctx, i, None, None, 1)
+    # kernel-class breakdown of one extra (untimed) step with every class bracketed by event pairs, and one integer-roofline object per
+    # hot class: units of work per job from work_per_job(), jobs from the library's launch accounting
+    prof_reset()
     _capi.check(lib.lmn_profile_enable(be.ctx, 0xFFFFFFFF))
     step()
-    breakdown = {}
-    for name, i in KID.items():
-        ms, cnt = C.c_double(), C.c_uint64()
-        _capi.check(lib.lmn_profile_read(be.ctx, i, C.byref(ms), C.byref(cnt), 1))
-        if cnt.value:
-            breakdown[name] = {"ms": round(ms.value, 3), "launches": cnt.value}
+    breakdown, kernel_rooflines = {}, {}
+    for name in KID:
+        ms, cnt, jb = prof(name)
+        if not cnt:
+            continue
+        breakdown[name] = {"ms": round(ms, 3), "launches": cnt, "jobs": jb}
+        if name in work and jb and ms > 0:
+            units = jb * work[name]["modmuls"]
+            kernel_rooflines[name] = {"bound": "int", "unit": "Gmodmul/s", "achieved": units / (ms * 1e-3) / 1e9, "peak": pk.value / 1e9,
+                                      "frac": units / (ms * 1e-3) / pk.value, "modmuls_per_job": work[name]["modmuls"],
+                                      "butterflies_per_job": work[name]["butterflies"], "jobs": jb, "ms": round(ms, 3),
+                                      "share_of_step": ms / ms_per_step, "ncu_fmaheavy_pct": NCU_FMAHEAVY.get(name)}
     _capi.check(lib.lmn_profile_enable(be.ctx, 0))
 
     # ---- Commit's "Merkle tree built" span (fhe/ligero.go:105-116), reported beside the headline, not inside it ----
@@ -381,7 +498,7 @@ def main():
     if not args.no_commit:
         n_loc = n // G
         leaves = be.NewStore(n_loc, lout)
-        lf = fhe.LeafFormat.lattigo_like(b"\x00" * 48, lout, N)     # 48 placeholder MetaData bytes + lattigo's u64 length prefixes
+        lf = fhe.LeafFormat.placeholder(lout, N)     # right size (pinned by the reference's logged sizes), not lattigo's MetaData bytes
         my_leaf_idx = np.ascontiguousarray([int(i) - rank * n_loc for i in qidx if rank * n_loc <= int(i) < (rank + 1) * n_loc] or [0], dtype=np.uint32)
         qsel = be.NewStore(len(my_leaf_idx), lout)
 
@@ -401,16 +518,14 @@ def main():
             t.free()
             return root
         commit_tail()
-        for i in range(lib.lmn_kernel_count()):
-            lib.lmn_profile_read(be.ctx, i, None, None, 1)
+        prof_reset()
         _capi.check(lib.lmn_profile_enable(be.ctx, 0xFFFFFFFF))
         cm_ms = timed(commit_tail, 1)
         cm_parts = {}
-        for name, i in KID.items():
-            ms, cnt = C.c_double(), C.c_uint64()
-            _capi.check(lib.lmn_profile_read(be.ctx, i, C.byref(ms), C.byref(cnt), 1))
-            if cnt.value:
-                cm_parts[name] = {"ms": round(ms.value, 3), "launches": cnt.value}
+        for name in KID:
+            ms, cnt, jb = prof(name)
+            if cnt:
+                cm_parts[name] = {"ms": round(ms, 3), "launches": cnt}
         _capi.check(lib.lmn_profile_enable(be.ctx, 0))
         gq_ms = timed(lambda: _capi.check(lib.lmn_store_gather(be.ctx, leaves.h, my_leaf_idx.ctypes.data_as(vp), len(my_leaf_idx), qsel.h)), 1)
         leaf_len = len(lf.header) + 2 * (len(lf.polyHeader) + (lout + 1) * (len(lf.limbHeader) + 8 * N))
@@ -443,7 +558,7 @@ def main():
     # ---- wire format (EncryptedProof.MarshalBinary, fhe/ligero.go:646-704), beside the headline ----
     proof_marshal = None
     if G == 1 and not args.no_commit:
-        lfm = fhe.LeafFormat.lattigo_like(b"\x00" * 48, lout, N)
+        lfm = fhe.LeafFormat.placeholder(lout, N)
         depth = max(1, (n - 1).bit_length())
         md = _capi.LmnLigeroMetadata(rows, cols, RHO_INV, nq_total)
         paths_b, root_b = bytes(32 * depth * nq_total), bytes(32)
@@ -507,12 +622,13 @@ def main():
         out = {
             "metric": "ligero_server_prove_eval_s", "value": ms_per_step / 1e3, "unit": "s", "n_gpus": G, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-            "config": {"workload": "%s%s: %dx%d LogN=%d k=%d encode + prove eval (inner products r,b + %d query columns)" % (args.config, " (PROFILING SUBSET of columns)" if args.cols_override else "", rows, cols, logN, k, nq_total),
+            "config": {"workload": workload_string(args.config, args.cols_override),
                        "l2": "inputs (%.1f GiB matrix per GPU) far exceed the 126 MB L2; no flush needed" % (mat_cols.nbytes / 2**30),
                        "sharding": "1 GPU" if G == 1 else "columns/%d for inner products + query rescale, coefficient slices/%d for Encode, all-to-all of queried slices" % (G, G),
                        "batch_jobs": args.batch},
-            "e2e": e2e, "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "roofline_int": roofline_int,
-            "roofline_encode": roofline_encode, "kernel_breakdown_one_step": breakdown, "commit_merkle": commit_merkle, "ring_switch_E": ring_switch, "proof_marshal": proof_marshal, "cpu_baseline": cpu,
+            "parity_check": parity,
+            "e2e": e2e, "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "roofline_hbm": roofline_hbm,
+            "roofline_encode": roofline_encode, "kernel_rooflines": kernel_rooflines, "kernel_breakdown_one_step": breakdown, "commit_merkle": commit_merkle, "ring_switch_E": ring_switch, "proof_marshal": proof_marshal, "cpu_baseline": cpu,
             "published_reference_s": PUBLISHED_S[args.config],
         }
         print(json.dumps(out))

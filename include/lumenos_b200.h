@@ -19,6 +19,13 @@
  * Threading: a context may be used from several host threads for DISTINCT stores; calls on one context
  * are serialised internally (the reference runs R and Z inner products from two goroutines,
  * fhe/ligero.go:231-242 -- use lmn_inner_product2 to fuse them instead).
+ *
+ * Lifetime of host buffers: work is queued on the context's stream and most calls return before it has run.
+ * Small host inputs (plaintexts, index lists, scalars, framing bytes) are copied into library-owned pinned
+ * staging before the call returns, so the caller may reuse or free them at once, pinned or not.  The BULK
+ * host buffers of lmn_encode_host (host_matrix) and lmn_inner_product2_host (host_r, host_b) are read /
+ * written by asynchronous copies and must stay valid and untouched until lmn_ctx_synchronize returns.
+ * lmn_store_upload / download and the key loaders synchronise before returning.
  */
 #ifndef LUMENOS_B200_H
 #define LUMENOS_B200_H
@@ -96,10 +103,13 @@ int lmn_host_alloc(size_t bytes, void **out);
 void lmn_host_free(void *p);
 
 /* ---------------- Encode eval (fhe/code.go + fhe/ntt.go) ---------------- */
-/* compile the butterfly/twiddle/permutation plan of nttInner(size = cols*rho_inv) for
- * core.NewPrimeField(t, cols*rho_inv): roots_forward[i] = backend.Field().RootForwardUint64(i)
- * (core/field.go:45-47), cols*rho_inv entries. */
-int lmn_plan_create(lmn_ctx *ctx, uint32_t cols, uint32_t rho_inv, const uint64_t *roots_forward, lmn_plan **out);
+/* compile the butterfly/twiddle/permutation plan of nttInner(size = cols*rho_inv) over the plaintext field the
+ * backend was built with: roots_forward[i] = backend.Field().RootForwardUint64(i) (core/field.go:45-47), field_n =
+ * backend.Field().N() entries.  The reference builds the field as core.NewPrimeField(t, cols*2) (cmd/server/main.go:57,
+ * fhe/ligero_test.go:58) and nttInner reads `step = Field().N()/size` and `idx %= Field().N()` from it (fhe/ntt.go:249-266),
+ * so field_n is a parameter of its own, equal to cols*rho_inv only for rho_inv == 2; every table index the walk produces is
+ * checked against field_n. */
+int lmn_plan_create(lmn_ctx *ctx, uint32_t cols, uint32_t rho_inv, const uint64_t *roots_forward, uint32_t field_n, lmn_plan **out);
 void lmn_plan_destroy(lmn_plan *plan);
 /* ciphertext-level op counts the plan stands for (ServerBFV.MulCounter analogue, fhe/bfv.go:20,34-46) */
 int lmn_plan_counts(const lmn_plan *plan, uint64_t *adds, uint64_t *subs, uint64_t *muls);
@@ -132,9 +142,13 @@ int lmn_plan_host_check(uint32_t n, const uint64_t *roots_forward, uint64_t t, u
 /* replaces rlwe.MemEvaluationKeySet lookup by Galois element (fhe/ligero_test.go:53-56,
  * cmd/server/main.go:66-122): evk = gk.Value[d][0][c] Q then P limbs, Montgomery + NTT form */
 int lmn_load_galois_key(lmn_ctx *ctx, uint64_t gal_el, const uint64_t *evk_host);
-/* ring-switch key (fhe/ring_switch.go:16-57, 98-104): evk sk -> embed(sk_small); psi_small = primitive
- * 2N'-th root of q[0] used by the small ring (0 = derive as psi_q[0]^(N/N')) */
-int lmn_load_ring_switch_key(lmn_ctx *ctx, uint32_t log_n_small, const uint64_t *evk_host, uint64_t psi_small);
+/* ring-switch key (fhe/ring_switch.go:16-57, 98-104): evk sk -> embed(sk_small), laid out [rns_digits][base2_digits][2][k+np][N]
+ * = evk.Value[d][b][c].  The reference asks for BaseTwoDecomposition = 13 (ring_switch.go:47-55); whether Lattigo honours it
+ * when P is present is unpinned, so the digit shape is an argument: rns_digits must equal ceil(k/np) and
+ * base2_digits must be 1 (LMN_ERR_UNSUPPORTED otherwise - a key with base-2 sub-digits is rejected instead of being misread).
+ * psi_small = primitive 2N'-th root of q[0] used by the small ring (0 = derive as psi_q[0]^(N/N')) */
+int lmn_load_ring_switch_key(lmn_ctx *ctx, uint32_t log_n_small, const uint64_t *evk_host, uint32_t rns_digits, uint32_t base2_digits,
+                             uint64_t psi_small);
 
 /* ---------------- Inner product eval (fhe/ligero.go:299-370 matrixInnerSumEval) ---------------- */
 /* pt_host: plaintext at max level as bgv.Encoder.Encode produced it: [num_q][N], NTT domain (ligero.go:204-205).
@@ -221,7 +235,9 @@ int lmn_limb_ntt(lmn_ctx *ctx, lmn_store *a, uint32_t ai, uint32_t poly, uint32_
 /* ---------------- measurement hooks (bench.py) ---------------- */
 /* per-kernel-class device timing with CUDA event pairs on the launch stream; mask bit i = class i */
 int lmn_profile_enable(lmn_ctx *ctx, uint32_t mask);
-int lmn_profile_read(lmn_ctx *ctx, int kernel_id, double *ms, uint64_t *launches, int reset);
+/* ms: summed device time of the timed launches of the class; launches / jobs: launches since the last reset and the column-jobs
+ * (ciphertexts) they processed (block-pipeline classes; 0 for the others) */
+int lmn_profile_read(lmn_ctx *ctx, int kernel_id, double *ms, uint64_t *launches, uint64_t *jobs, int reset);
 int lmn_kernel_count(void);
 const char *lmn_kernel_name(int kernel_id);
 /* measured ceiling of the NTT butterfly instruction mix on the integer pipes (register-resident, all SMs) */

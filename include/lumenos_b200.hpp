@@ -157,7 +157,7 @@ class ServerBFV {
         for (auto &pl : plans_) if (pl.first == key) return pl.second;
         if ((uint32_t)ptField_.N() != cols * rhoInv) throw std::invalid_argument("plaintext field degree does not match the codeword length");
         lmn_plan *p = nullptr;
-        check(lmn_plan_create(ctx_, cols, rhoInv, ptField_.roots.data(), &p));
+        check(lmn_plan_create(ctx_, cols, rhoInv, ptField_.roots.data(), (uint32_t)ptField_.roots.size(), &p));
         plans_.emplace_back(key, p);
         return p;
     }

@@ -50,7 +50,7 @@ SIGNATURES = {
     "lmn_store_download_limb": (C.c_int, [vp, C.c_uint32, C.c_uint32, C.c_uint32, vp]),
     "lmn_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(vp)]),
     "lmn_host_free": (None, [vp]),
-    "lmn_plan_create": (C.c_int, [vp, C.c_uint32, C.c_uint32, vp, C.POINTER(vp)]),
+    "lmn_plan_create": (C.c_int, [vp, C.c_uint32, C.c_uint32, vp, C.c_uint32, C.POINTER(vp)]),
     "lmn_plan_destroy": (None, [vp]),
     "lmn_plan_counts": (C.c_int, [vp, u64p, u64p, u64p]),
     "lmn_plan_size": (C.c_uint32, [vp]),
@@ -61,12 +61,12 @@ SIGNATURES = {
     "lmn_ntt": (C.c_int, [vp, vp, vp, vp]),
     "lmn_encode_lanes": (C.c_int, [vp, vp, vp, vp, vp, C.c_uint32]),
     "lmn_profile_enable": (C.c_int, [vp, C.c_uint32]),
-    "lmn_profile_read": (C.c_int, [vp, C.c_int, C.POINTER(C.c_double), u64p, C.c_int]),
+    "lmn_profile_read": (C.c_int, [vp, C.c_int, C.POINTER(C.c_double), u64p, u64p, C.c_int]),
     "lmn_kernel_count": (C.c_int, []),
     "lmn_kernel_name": (C.c_char_p, [C.c_int]),
     "lmn_bench_int_peak": (C.c_int, [vp, C.POINTER(C.c_double)]),
     "lmn_load_galois_key": (C.c_int, [vp, C.c_uint64, vp]),
-    "lmn_load_ring_switch_key": (C.c_int, [vp, C.c_uint32, vp, C.c_uint64]),
+    "lmn_load_ring_switch_key": (C.c_int, [vp, C.c_uint32, vp, C.c_uint32, C.c_uint32, C.c_uint64]),
     "lmn_inner_product": (C.c_int, [vp, vp, vp, C.c_uint32, vp]),
     "lmn_inner_product2": (C.c_int, [vp, vp, vp, vp, C.c_uint32, vp, vp]),
     "lmn_ring_switch": (C.c_int, [vp, vp, vp]),

@@ -43,6 +43,9 @@ struct lmn_ctx {
     cudaStream_t own_stream = nullptr, stream = nullptr;
     cudaStream_t copy_stream = nullptr;     // host <-> device copies that overlap the kernels (lmn_encode_host, lmn_inner_product2_host)
     std::vector<cudaEvent_t> copy_events;   // pool, reused call after call
+    // small host inputs (plaintexts, index lists) go through this pinned buffer, so the caller's memory is free to be reused or
+    // released the moment a call returns even when it is pinned (an async copy from pinned memory runs behind the queued kernels)
+    uint8_t *h_stage = nullptr; size_t h_stage_cap = 0, h_stage_cur = 0; cudaEvent_t stage_ev = nullptr; bool stage_pending = false;
     ModDev *d_mods = nullptr;
     ulonglong2 *d_twf = nullptr, *d_twi = nullptr, *d_twbf = nullptr, *d_twbi = nullptr;
     DeviceTables T{};
@@ -214,6 +217,34 @@ static void build_ks_consts(const lmn_ctx *c, int level, KsConsts &K) {
     }
 }
 
+// staged host -> device copies on the context's stream: stage_begin (waits until the previous user of the staging buffer has been
+// copied out, grows it), any number of stage_copy, stage_end.  Caller holds the context lock.
+static int stage_begin(lmn_ctx *c, size_t total) {
+    if (c->stage_pending) { CK(cudaEventSynchronize(c->stage_ev)); c->stage_pending = false; }
+    if (!c->stage_ev) CK(cudaEventCreateWithFlags(&c->stage_ev, cudaEventDisableTiming));
+    if (c->h_stage_cap < total) {
+        if (c->h_stage) cudaFreeHost(c->h_stage);
+        c->h_stage = nullptr; c->h_stage_cap = 0;
+        CK(cudaHostAlloc((void **)&c->h_stage, total, cudaHostAllocDefault));
+        c->h_stage_cap = total;
+    }
+    c->h_stage_cur = 0;
+    return 0;
+}
+static int stage_copy(lmn_ctx *c, void *dst, const void *src, size_t bytes) {
+    if (c->h_stage_cur + bytes > c->h_stage_cap) return fail(LMN_ERR_INVALID, "staging buffer overflow");
+    uint8_t *s = c->h_stage + c->h_stage_cur;
+    memcpy(s, src, bytes);
+    c->h_stage_cur += (bytes + 15) & ~(size_t)15;
+    CK(cudaMemcpyAsync(dst, s, bytes, cudaMemcpyHostToDevice, c->stream));
+    return 0;
+}
+static int stage_end(lmn_ctx *c) {
+    CK(cudaEventRecord(c->stage_ev, c->stream));
+    c->stage_pending = true;
+    return 0;
+}
+
 static int get_ks(lmn_ctx *c, int level, const KsConsts **host, const KsConsts **dev) {
     auto it = c->ks.find(level);
     if (it == c->ks.end()) {
@@ -382,6 +413,8 @@ void lmn_ctx_destroy(lmn_ctx *c) {
     for (int i = 0; i < KID_COUNT; i++) for (auto &sp : c->prof.spans[i]) { cudaEventDestroy(sp.first); cudaEventDestroy(sp.second); }
     for (auto e : c->prof.pool) cudaEventDestroy(e);
     for (cudaEvent_t e : c->copy_events) cudaEventDestroy(e);
+    if (c->stage_ev) cudaEventDestroy(c->stage_ev);
+    if (c->h_stage) cudaFreeHost(c->h_stage);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
@@ -483,8 +516,9 @@ static u64 scalar_mod_q(const lmn_ctx *c, u64 w, u64 q) {
     if (c->scalar_centered && w > (t >> 1)) { u64 neg = (t - w) % q; return neg ? q - neg : 0; }
     return w % q;
 }
-int lmn_plan_create(lmn_ctx *c, uint32_t cols, uint32_t rho_inv, const uint64_t *roots, lmn_plan **out) {
+int lmn_plan_create(lmn_ctx *c, uint32_t cols, uint32_t rho_inv, const uint64_t *roots, uint32_t field_n, lmn_plan **out) {
     if (!roots || !out || cols == 0 || rho_inv == 0) return fail(LMN_ERR_INVALID, "bad plan arguments");
+    if (field_n == 0 || (field_n & (field_n - 1))) return fail(LMN_ERR_INVALID, "field_n (PrimeField.N()) must be a power of two");
     uint64_t n64 = (uint64_t)cols * rho_inv;
     if (n64 > (1u << 16)) return fail(LMN_ERR_UNSUPPORTED, "codeword length above 65536");
     uint32_t n = (uint32_t)n64;
@@ -492,7 +526,7 @@ int lmn_plan_create(lmn_ctx *c, uint32_t cols, uint32_t rho_inv, const uint64_t 
     p->ctx = c; p->cols = cols; p->rho_inv = rho_inv;
     if (!c) { delete p; return fail(LMN_ERR_INVALID, "null context"); }
     uint64_t t = c->t;
-    std::string err = compile_encode_plan(n, n, roots, t, ENC_MAX_TILE, p->pl);
+    std::string err = compile_encode_plan(n, field_n, roots, t, ENC_MAX_TILE, p->pl);
     if (!err.empty()) { delete p; return fail(LMN_ERR_INVALID, err); }
     std::lock_guard<std::mutex> g(c->mu);
     cudaSetDevice(c->device);
@@ -650,7 +684,7 @@ int lmn_profile_enable(lmn_ctx *c, uint32_t mask) {
     c->prof.mask = mask;
     return 0;
 }
-int lmn_profile_read(lmn_ctx *c, int kernel_id, double *ms, uint64_t *launches, int reset) {
+int lmn_profile_read(lmn_ctx *c, int kernel_id, double *ms, uint64_t *launches, uint64_t *jobs, int reset) {
     if (!c || kernel_id < 0 || kernel_id >= KID_COUNT) return fail(LMN_ERR_INVALID, "bad kernel id");
     std::lock_guard<std::mutex> g(c->mu);
     CK(cudaStreamSynchronize(c->stream));
@@ -661,10 +695,12 @@ int lmn_profile_read(lmn_ctx *c, int kernel_id, double *ms, uint64_t *launches, 
     }
     if (ms) *ms = total;
     if (launches) *launches = c->prof.launches[kernel_id];
+    if (jobs) *jobs = c->prof.jobs[kernel_id];
     if (reset) {
         for (auto &sp : c->prof.spans[kernel_id]) { c->prof.pool.push_back(sp.first); c->prof.pool.push_back(sp.second); }
         c->prof.spans[kernel_id].clear();
         c->prof.launches[kernel_id] = 0;
+        c->prof.jobs[kernel_id] = 0;
     }
     return 0;
 }
@@ -701,8 +737,10 @@ int lmn_load_galois_key(lmn_ctx *c, uint64_t gal_el, const uint64_t *evk) {
     c->galois[gal_el] = d;
     return 0;
 }
-int lmn_load_ring_switch_key(lmn_ctx *c, uint32_t logns, const uint64_t *evk, uint64_t psi_small) {
+int lmn_load_ring_switch_key(lmn_ctx *c, uint32_t logns, const uint64_t *evk, uint32_t rns_digits, uint32_t base2_digits, uint64_t psi_small) {
     if (!c || !evk) return fail(LMN_ERR_INVALID, "null argument");
+    if (rns_digits != (uint32_t)((c->k + c->np - 1) / c->np)) return fail(LMN_ERR_INVALID, "ring-switch key must have ceil(k / np) RNS digits");
+    if (base2_digits != 1) return fail(LMN_ERR_UNSUPPORTED, "ring-switch keys with base-2 sub-digits (BaseTwoDecomposition) are not supported: evk.Value[d] must have one entry");
     if ((int)logns >= c->logn) return fail(LMN_ERR_INVALID, "small ring must be smaller than the ciphertext ring");
     bool ok = (logns == 10 && c->logn >= 12) || (logns == 6 && (c->logn == 8 || c->logn == 10)) || (logns == 8 && (c->logn == 10 || c->logn == 12));
     if (!ok) return fail(LMN_ERR_UNSUPPORTED, "ring switch is instantiated for N' = 1024 (N >= 4096) and the small test rings");
@@ -819,8 +857,10 @@ static int inner_product2_impl(lmn_ctx *c, const lmn_store *matrix, const uint64
     Launch L = c->L();
     // plaintexts: upload, fold T and the Montgomery factor (tensorStandard's T * pt)
     u64 *d_pt = c->ws_pt, *d_ptm = c->ws_pt + 2 * k * N;
-    CK(cudaMemcpyAsync(d_pt, pt_r, k * N * 8, cudaMemcpyHostToDevice, c->stream));
-    if (pt_b) CK(cudaMemcpyAsync(d_pt + k * N, pt_b, k * N * 8, cudaMemcpyHostToDevice, c->stream));
+    if (int rc = stage_begin(c, 2 * k * N * 8 + 32)) return rc;
+    if (int rc = stage_copy(c, d_pt, pt_r, k * N * 8)) return rc;
+    if (pt_b) if (int rc = stage_copy(c, d_pt + k * N, pt_b, k * N * 8)) return rc;
+    if (int rc = stage_end(c)) return rc;
     launch_prep_pt(L, c->T, Lmax, d_pt, c->t, d_ptm);
     if (pt_b) launch_prep_pt(L, c->T, Lmax, d_pt + k * N, c->t, d_ptm + k * N);
     const size_t out_words = 2 * (size_t)(lout + 1) * N;
@@ -883,7 +923,9 @@ static int rescale_select(lmn_ctx *c, const lmn_store *enc, const uint32_t *idx,
     cudaSetDevice(c->device);
     if (!all) {
         if (c->ws_idx_cap < n_idx) { cudaFree(c->ws_idx); c->ws_idx = nullptr; c->ws_idx_cap = 0; CK(cudaMalloc(&c->ws_idx, n_idx * sizeof(uint32_t))); c->ws_idx_cap = n_idx; }
-        CK(cudaMemcpyAsync(c->ws_idx, idx, n_idx * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+        if (int rc = stage_begin(c, n_idx * sizeof(uint32_t) + 16)) return rc;
+        if (int rc = stage_copy(c, c->ws_idx, idx, n_idx * sizeof(uint32_t))) return rc;
+        if (int rc = stage_end(c)) return rc;
     }
     const uint32_t bc = c->batch;
     if (int rc = ensure_workspace(c, std::min(bc, n_idx))) return rc;
@@ -969,7 +1011,9 @@ int lmn_ct_mul_pt(lmn_ctx *c, const lmn_store *a, uint32_t ai, const uint64_t *p
     cudaSetDevice(c->device);
     const size_t N = c->n, nl = a->level + 1;
     u64 *d_pt = c->ws_pt, *d_ptm = c->ws_pt + 2 * (size_t)c->k * N;
-    CK(cudaMemcpyAsync(d_pt, pt, nl * N * 8, cudaMemcpyHostToDevice, c->stream));
+    if (int rc = stage_begin(c, nl * N * 8 + 16)) return rc;
+    if (int rc = stage_copy(c, d_pt, pt, nl * N * 8)) return rc;
+    if (int rc = stage_end(c)) return rc;
     Launch L = c->L();
     launch_prep_pt(L, c->T, (int)a->level, d_pt, c->t, d_ptm);
     launch_mul_pt(L, c->T, (int)a->level, a->d + ai * a->words(), a->words(), 1, d_ptm, nullptr, o->d + oi * o->words(), nullptr, o->words());

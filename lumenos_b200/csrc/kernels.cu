@@ -34,10 +34,11 @@ cudaEvent_t Profiler::get() {
     if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
     cudaEvent_t e; cudaEventCreate(&e); return e;
 }
-LaunchScope::LaunchScope(const Launch &l, int kid) : L(l), id(kid) {
+LaunchScope::LaunchScope(const Launch &l, int kid, uint64_t jobs) : L(l), id(kid) {
     if (L.counter) (*L.counter)++;
     if (L.prof) {
         L.prof->launches[id]++;
+        L.prof->jobs[id] += jobs;
         if (L.prof->mask & (1u << id)) {
             cudaEvent_t e0 = L.prof->get(); e1 = L.prof->get();
             cudaEventRecord(e0, L.stream);
@@ -683,27 +684,27 @@ void launch_rotate_accumulate(const Launch &L, const DeviceTables &T, const KsCo
     const int N = T.n, nq = Ch.nq, np = Ch.np, jobs = J.jobs;
     const size_t sm_full = (size_t)padded_words(N) * 8;
     const int nt_full = ntt_threads(N);
-    { LaunchScope scope(L, KID_INTT_C1);
+    { LaunchScope scope(L, KID_INTT_C1, (uint64_t)jobs);
     LMN_DISPATCH_LOGN(T.logn, k_intt_c1<LG><<<dim3(nq, jobs), nt_full, sm_full, L.stream>>>(T.mods, T.tw_inv, Cd, J, Ch.k)); }
     {
-        LaunchScope scope(L, KID_VFIX);
+        LaunchScope scope(L, KID_VFIX, (uint64_t)jobs);
         const int bs = N < 256 ? N : 256;
         const int beta_max = (Ch.k + np - 1) / np;
         k_modup<1><<<dim3((N + bs - 1) / bs, Ch.beta, jobs), bs, 0, L.stream>>>(T.mods, T.tw_fwd, Cd, J, T.logn, beta_max);
     }
     {
-        LaunchScope scope(L, KID_MAC);
+        LaunchScope scope(L, KID_MAC, (uint64_t)jobs);
         const size_t smm = ((size_t)padded_words(N) + 2 * (size_t)N) * 8;
         LMN_DISPATCH_LOGN(T.logn, k_mac<(LG <= 13 ? LG : 13), 1><<<dim3(nq + np, jobs), nt_full, smm, L.stream>>>(T.mods, T.tw_fwd, Cd, J, evk));
     }
-    { LaunchScope scope(L, KID_PINTT);
+    { LaunchScope scope(L, KID_PINTT, (uint64_t)jobs);
     LMN_DISPATCH_LOGN(T.logn, k_pintt<LG><<<dim3(np, 2, jobs), nt_full, sm_full, L.stream>>>(T.mods, T.tw_inv, Cd, J)); }
     if (np > 1) {
         int bs = N < 256 ? N : 256;
-        LaunchScope scope(L, KID_VPFIX);
+        LaunchScope scope(L, KID_VPFIX, (uint64_t)jobs);
         k_vpfix<<<dim3((N + bs - 1) / bs, 2, jobs), bs, 0, L.stream>>>(T.mods, Cd, J, T.logn);
         }
-    { LaunchScope scope(L, KID_DOWN);
+    { LaunchScope scope(L, KID_DOWN, (uint64_t)jobs);
     LMN_DISPATCH_LOGN(T.logn, k_down<LG><<<dim3(nq, 2, jobs), nt_full, sm_full, L.stream>>>(T.mods, T.tw_fwd, Cd, J, gal_el,
                                                                                         gal_el == 0 ? 1 : 0)); }
 }

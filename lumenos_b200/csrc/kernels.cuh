@@ -96,6 +96,7 @@ struct Profiler {
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> spans[KID_COUNT];
     std::vector<cudaEvent_t> pool;
     uint64_t launches[KID_COUNT] = {0};
+    uint64_t jobs[KID_COUNT] = {0};                       // column-jobs (ciphertexts) those launches processed
     cudaEvent_t get();
 };
 
@@ -106,7 +107,7 @@ struct Launch {
 };
 struct LaunchScope {        // RAII: counts the launch and brackets it with events when its class is being profiled
     const Launch &L; int id; cudaEvent_t e1 = nullptr;
-    LaunchScope(const Launch &l, int kid);
+    LaunchScope(const Launch &l, int kid, uint64_t jobs = 0);
     ~LaunchScope();
 };
 // peak rate of the NTT butterfly instruction mix on the integer pipes, register-resident (no memory traffic)

@@ -524,7 +524,7 @@ static int pick_jb(int ctas_per_job, int jobs) {
     }
 
 void launch_blk_intt(const Launch &L, const DeviceTables &T, const BlkSlots &A, int jobs, int kid) {
-    LaunchScope scope(L, kid);
+    LaunchScope scope(L, kid, (uint64_t)jobs);
     const int SB = blk_blocks(T.logn);
     const int jb = pick_jb(SB * A.nslots, jobs);
     const dim3 g(SB * A.nslots, (jobs + jb - 1) / jb);
@@ -532,7 +532,7 @@ void launch_blk_intt(const Launch &L, const DeviceTables &T, const BlkSlots &A, 
 }
 
 void launch_modup_blk(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch, const KsJobs &J) {
-    LaunchScope scope(L, KID_VFIX);
+    LaunchScope scope(L, KID_VFIX, (uint64_t)J.jobs);
     const int SB = blk_blocks(T.logn);
     // digits of the common size np run with the digit size as a template parameter; a shorter last digit separately
     int full = 0;
@@ -552,7 +552,7 @@ void launch_modup_blk(const Launch &L, const DeviceTables &T, const KsConsts *Cd
 }
 
 void launch_down_pre(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch, const KsJobs &J) {
-    LaunchScope scope(L, KID_VPFIX);
+    LaunchScope scope(L, KID_VPFIX, (uint64_t)J.jobs);
     const int SB = blk_blocks(T.logn);
     const dim3 g(RA_M / 256, 2, J.jobs);
     LMN_DISPATCH_S(SB, k_down_pre<SS><<<g, 256, 0, L.stream>>>(T.mods, T.tw_fwd, T.tw_inv, Cd, J));
@@ -560,7 +560,7 @@ void launch_down_pre(const Launch &L, const DeviceTables &T, const KsConsts *Cd,
 
 void launch_down_blk(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch, const KsJobs &J,
                      uint32_t gal_el, int mode) {
-    LaunchScope scope(L, KID_DOWN);
+    LaunchScope scope(L, KID_DOWN, (uint64_t)J.jobs);
     const int SB = blk_blocks(T.logn);
     const int jb = pick_jb(SB * Ch.nq * 2, J.jobs);
     const dim3 g(SB * Ch.nq, 2, (J.jobs + jb - 1) / jb);
@@ -569,14 +569,14 @@ void launch_down_blk(const Launch &L, const DeviceTables &T, const KsConsts *Cd,
 }
 
 void launch_rs_pre(const Launch &L, const DeviceTables &T, const RescaleConsts *Rd, int level, const KsJobs &J) {
-    LaunchScope scope(L, KID_RS_PRE);
+    LaunchScope scope(L, KID_RS_PRE, (uint64_t)J.jobs);
     const int SB = blk_blocks(T.logn);
     const dim3 g(RA_M / 256, 2, J.jobs);
     LMN_DISPATCH_S(SB, k_rs_pre<SS><<<g, 256, 0, L.stream>>>(T.mods, T.tw_fwd, T.tw_inv, Rd, J, level));
 }
 
 void launch_rs_blk(const Launch &L, const DeviceTables &T, const RescaleConsts *Rd, int level, const KsJobs &J) {
-    LaunchScope scope(L, KID_RS_APPLY);
+    LaunchScope scope(L, KID_RS_APPLY, (uint64_t)J.jobs);
     const int SB = blk_blocks(T.logn);
     const int jb = pick_jb(SB * level * 2, J.jobs);
     const dim3 g(SB * level, 2, (J.jobs + jb - 1) / jb);
@@ -594,13 +594,13 @@ void launch_rescale_chain(const Launch &L, const DeviceTables &T, const RescaleC
         for (int i = 0; i < nl; i++) { A.mod[c * nl + i] = i; A.src_limb[c * nl + i] = (uint32_t)(c * T.k + i); A.dst_limb[c * nl + i] = (uint32_t)(c * nl + i); }
     launch_blk_intt(L, T, A, J.jobs, KID_RS_INTT);
     {
-        LaunchScope scope(L, KID_RS_PRE);
+        LaunchScope scope(L, KID_RS_PRE, (uint64_t)J.jobs);
         const dim3 g(RA_M / CHAIN_THREADS, 2, J.jobs);
         const size_t smem = (size_t)(Ch.from - Ch.to) * SB * CHAIN_THREADS * 8;
         LMN_DISPATCH_S(SB, k_rs_chain<SS><<<g, CHAIN_THREADS, smem, L.stream>>>(T.mods, T.tw_fwd, T.tw_inv, Cd, J));
     }
     {
-        LaunchScope scope(L, KID_RS_APPLY);
+        LaunchScope scope(L, KID_RS_APPLY, (uint64_t)J.jobs);
         const int keep = Ch.to + 1;
         const int jb = pick_jb(SB * keep * 2, J.jobs);
         const dim3 g(SB * keep, 2, (J.jobs + jb - 1) / jb);

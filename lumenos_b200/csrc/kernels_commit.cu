@@ -99,16 +99,18 @@ __device__ __forceinline__ u64 leaf_word(const LeafFormat &F, const u64 *__restr
     return v;
 }
 // out[leaf][2w], out[leaf][2w+1]: two words (one 16-byte store) per thread; the padded length is a multiple of 64 bytes
+// (the leaf index is folded into blockIdx.x - bx blocks per leaf - so that any leaf count lmn_plan_create admits fits the grid)
 __global__ void __launch_bounds__(256) k_leaf_serialize(const LeafFormat F, const u64 *__restrict__ cts, uint64_t ct_words,
-                                                        u64 *__restrict__ out) {
-    const uint32_t w2 = 2 * (blockIdx.x * blockDim.x + threadIdx.x);
+                                                        u64 *__restrict__ out, uint32_t bx) {
+    const uint32_t leaf = blockIdx.x / bx;
+    const uint32_t w2 = 2 * ((blockIdx.x - leaf * bx) * blockDim.x + threadIdx.x);
     const uint32_t words = F.padded_len / 8;
     if (w2 >= words) return;
-    const u64 *ct = cts + (size_t)blockIdx.y * ct_words;
+    const u64 *ct = cts + (size_t)leaf * ct_words;
     ulonglong2 v;
     v.x = leaf_word(F, ct, w2);
     v.y = leaf_word(F, ct, w2 + 1);
-    reinterpret_cast<ulonglong2 *>(out + (size_t)blockIdx.y * words)[w2 >> 1] = v;
+    reinterpret_cast<ulonglong2 *>(out + (size_t)leaf * words)[w2 >> 1] = v;
 }
 
 // Wire format of the proof (EncryptedProof.WriteTo, fhe/ligero.go:660-691): MatR, MatZ and QueriedCols are written as
@@ -200,7 +202,8 @@ __global__ void k_sha256_nodes(const uint32_t *__restrict__ children, uint32_t n
 void launch_leaf_serialize(const Launch &L, const LeafFormat &F, const u64 *cts, uint64_t ct_words, uint32_t n_leaves, u64 *out) {
     LaunchScope scope(L, KID_LEAF_SER);
     const uint32_t words = F.padded_len / 8;
-    k_leaf_serialize<<<dim3((words / 2 + 255) / 256, n_leaves), 256, 0, L.stream>>>(F, cts, ct_words, out);
+    const uint32_t bx = (words / 2 + 255) / 256;
+    k_leaf_serialize<<<bx * n_leaves, 256, 0, L.stream>>>(F, cts, ct_words, out, bx);
 }
 void launch_ct_stream(const Launch &L, const LeafFormat &F, const u64 *cts, uint64_t ct_words, uint64_t byte0, uint64_t byte_end, u64 *out) {
     LaunchScope scope(L, KID_LEAF_SER);
@@ -209,10 +212,10 @@ void launch_ct_stream(const Launch &L, const LeafFormat &F, const u64 *cts, uint
 }
 void launch_sha256_leaves(const Launch &L, const u64 *ser, uint32_t padded_len, uint32_t n_leaves, uint32_t *hashes) {
     LaunchScope scope(L, KID_SHA_LEAF);
-    // a leaf is one sequential SHA-256 chain, so the launch has only n_leaves threads.  Lanes per warp (LMN_SHA_TPB), measured on B200:
+    // a leaf is one sequential SHA-256 chain, so the launch has only n_leaves threads.  Lanes per warp, measured on B200:
     // 256 leaves of 512 KiB: 15.6 ms (32 lanes) / 14.4 ms (8); 8192 leaves: 15.8 ms (32) / 24.1 ms (8) - full warps win once every
     // scheduler has a chain to run
-    static const int tpb = getenv("LMN_SHA_TPB") ? atoi(getenv("LMN_SHA_TPB")) : 32;
+    constexpr int tpb = 32;   // == the kernel's __launch_bounds__
     k_sha256_leaves<<<(n_leaves + tpb - 1) / tpb, tpb, 0, L.stream>>>(reinterpret_cast<const uint4 *>(ser), padded_len / 64, n_leaves, hashes);
 }
 void launch_sha256_nodes(const Launch &L, const uint32_t *children, uint32_t n_children, uint32_t *parents) {

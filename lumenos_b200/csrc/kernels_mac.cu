@@ -160,7 +160,7 @@ __global__ void __launch_bounds__(RA_THREADS, LMN_MACRD_MINB) k_mac_rd(const Mod
 
 // =====================================================================================================
 void launch_mac_blk(const Launch &L, const DeviceTables &T, const KsConsts *Cd, const KsConsts &Ch, const KsJobs &J, const u64 *evk) {
-    LaunchScope scope(L, KID_MAC);
+    LaunchScope scope(L, KID_MAC, (uint64_t)J.jobs);
     const int SB = blk_blocks(T.logn);
     static const int jbe = getenv("LMN_MAC_JB") ? atoi(getenv("LMN_MAC_JB")) : 0;
     const int ctas = (Ch.nq + Ch.np) * SB;

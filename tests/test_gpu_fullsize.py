@@ -155,7 +155,7 @@ def test_merkle_full_size_properties(logN, n_leaves):
     g = torch.Generator(device=dev).manual_seed(21)
     L = torch.randint(0, 2**55, (n_leaves, 2, 2, N), generator=g, dtype=torch.int64, device=dev)
     leaves = fhe.CiphertextStore(be, n_leaves, 1, wrap_ptr=L.data_ptr())
-    lf = fhe.LeafFormat.lattigo_like(b"\x07" * 45, 1, N)           # odd header length: every coefficient lands unaligned
+    lf = fhe.LeafFormat.with_prefixes(b"\x07" * 45, 1, N)           # odd header length: every coefficient lands unaligned
     torch.cuda.synchronize()
     tree = fhe.MerkleTree(be, leaves, lf)
     le = lambda a: a.cpu().numpy().astype("<u8").tobytes()  # noqa: E731
@@ -189,7 +189,7 @@ def test_config_A_B_ligero_e2e_verify(rows, cols, logN, k, p1):
     P = S.P
     assert int(S.M.astype(object).sum() % T) == p1        # results/baseline/client/bench_{2048x1024,4096x2048}_12.txt:22
     be = S.backend()
-    lf = fhe.LeafFormat.lattigo_like(b"\x00" * 48, 1, 1 << logN)
+    lf = fhe.LeafFormat.with_prefixes(b"\x00" * 48, 1, 1 << logN)
     matrix = be.NewStore(cols).upload(S.cts)
     zero = be.NewStore(1).upload(S.zero[None])
     committer = fhe.LigeroCommitter(128, rows, cols, 2)

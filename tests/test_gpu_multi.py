@@ -1,5 +1,7 @@
-"""2-GPU equivalence (-m gpu, skipped with fewer than 2 devices): the sharded path (coefficient-sliced Encode,
-column-sharded inner products, all-to-all of queried slices) produces byte-identical outputs to the 1-GPU path."""
+"""Multi-GPU equivalence (-m gpu; a case is skipped when the box has fewer devices than its world size): the sharded path
+(coefficient-sliced Encode, column-sharded inner products, all-to-all of queried / encoded slices, gathered Merkle tree, sharded
+wire sections) produces byte-identical outputs to the oracle's single-process evaluation, at world sizes 2 / 4 / 8, on a small
+ring (whole-limb kernels) and on a logN-12 ring with rows == N (the block pipeline of the benchmark, InnerSum's row-swap step)."""
 import os
 import subprocess
 import sys
@@ -19,7 +21,7 @@ from lumenos_b200 import fhe, sharding, _capi
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(local); dev = torch.device("cuda", local)
 dist.init_process_group("nccl", device_id=dev)
-S = Scenario(logN=8, rows=256, cols=16, k=5)
+S = Scenario(logN=int(os.environ["LMN_T_LOGN"]), rows=int(os.environ["LMN_T_ROWS"]), cols=int(os.environ["LMN_T_COLS"]), k=int(os.environ["LMN_T_K"]))
 P, lib = S.P, _capi.lib()
 be = S.backend(device=local, stream=torch.cuda.current_stream(dev).cuda_stream)
 want_enc = P.fhe_encode(S.cts, 2, S.zero, S.roots)
@@ -33,7 +35,7 @@ _capi.check(lib.lmn_encode_lanes(be.ctx, be._plan(S.cols, 2), vp(m_sl.data_ptr()
 be.Synchronize()
 assert np.array_equal(e_sl.cpu().numpy().astype(np.uint64), want_enc[..., lo:hi]), "sliced Encode differs"
 # query columns via the all-to-all
-qidx = np.random.default_rng(3).integers(0, 2 * S.cols, size=21); qidx[4] = qidx[1]
+qidx = np.random.default_rng(3).integers(0, 2 * S.cols, size=37); qidx[4] = qidx[1]
 full = sharding.exchange_queried(e_sl, qidx, rank, world)
 mine = sharding.queries_of(len(qidx), rank, world)
 st = fhe.CiphertextStore(be, len(mine), P.k - 1, wrap_ptr=full.data_ptr())
@@ -70,7 +72,7 @@ assert np.array_equal(blk.cpu().numpy().astype(np.uint64), want_enc[a2:b2]), "co
 est = fhe.CiphertextStore(be, b2 - a2, P.k - 1, wrap_ptr=blk.data_ptr())
 leaves = be.NewStore(b2 - a2, 1)
 _capi.check(lib.lmn_commit_leaves(be.ctx, est.h, leaves.h))
-lf = fhe.LeafFormat.lattigo_like(b"hdr-bytes", 1, P.N)
+lf = fhe.LeafFormat.with_prefixes(b"hdr-bytes", 1, P.N)
 tree = sharding.commit_tree(be, leaves, lf, rank, world)
 bufs = [O.leaf_bytes(P.rescale_to_level1(want_enc[j])[0], lf.header, lf.polyHeader, lf.limbHeader) for j in range(n)]
 want_tree = O.MerkleTree(bufs)
@@ -93,14 +95,19 @@ dist.destroy_process_group()
 '''
 
 
-def test_two_gpu_equivalence(tmp_path):
+CASES = [(2, 8, 256, 16, 5), (2, 12, 4096, 16, 5), (4, 12, 4096, 16, 5), (8, 12, 4096, 16, 4), (8, 8, 128, 16, 5)]
+
+
+@pytest.mark.parametrize("world,logN,rows,cols,k", CASES)
+def test_multi_gpu_equivalence(tmp_path, world, logN, rows, cols, k):
     import torch
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs")
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs" % world)
     script = tmp_path / "worker.py"
     script.write_text(WORKER % (ROOT, ROOT))
-    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
-                        "--master-addr", "127.0.0.1", "--master-port", "29655", str(script)],
-                       capture_output=True, text=True, timeout=600)
+    env = dict(os.environ, LMN_T_LOGN=str(logN), LMN_T_ROWS=str(rows), LMN_T_COLS=str(cols), LMN_T_K=str(k))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
+                        "--master-addr", "127.0.0.1", "--master-port", str(29655 + world), str(script)],
+                       capture_output=True, text=True, timeout=900, env=env)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
-    assert r.stdout.count("ok") == 2
+    assert r.stdout.count("ok") == world

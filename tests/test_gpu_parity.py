@@ -231,7 +231,7 @@ def test_commit_merkle_bit_exact(logN, rows, cols, k, batch, fmt_id):
     be.SetBatch(batch)
     _, hdr, ph, lh = LEAF_FORMATS[fmt_id]
     N = 1 << logN
-    lf = fhe.LeafFormat.lattigo_like(hdr, 1, N) if ph is None else fhe.LeafFormat(hdr, ph, lh)
+    lf = fhe.LeafFormat.with_prefixes(hdr, 1, N) if ph is None else fhe.LeafFormat(hdr, ph, lh)
     matrix = be.NewStore(cols).upload(S.cts)
     zero = be.NewStore(1).upload(S.zero[None])
     committer = fhe.LigeroCommitter(128, rows, cols, 2)
@@ -274,7 +274,7 @@ def test_merkle_odd_leaf_counts(n_leaves):
     rng = np.random.default_rng(n_leaves)
     cts = rng.integers(0, 2**55, size=(n_leaves, 2, 2, 64), dtype=np.uint64)
     leaves = be.NewStore(n_leaves, 1).upload(cts)
-    lf = fhe.LeafFormat.lattigo_like(b"hdr", 1, 64)
+    lf = fhe.LeafFormat.with_prefixes(b"hdr", 1, 64)
     t = fhe.MerkleTree(be, leaves, lf)
     bufs = [O.leaf_bytes(cts[j], lf.header, lf.polyHeader, lf.limbHeader) for j in range(n_leaves)]
     want = O.MerkleTree(bufs)
@@ -367,7 +367,7 @@ def test_proof_marshal_bit_exact(logN, rows, cols, k, fmt_id):
     be = S.backend()
     _, hdr, ph, lh = LEAF_FORMATS[fmt_id]
     N = 1 << logN
-    lf = fhe.LeafFormat.lattigo_like(hdr, 1, N) if ph is None else fhe.LeafFormat(hdr, ph, lh)
+    lf = fhe.LeafFormat.with_prefixes(hdr, 1, N) if ph is None else fhe.LeafFormat(hdr, ph, lh)
     matrix = be.NewStore(cols).upload(S.cts)
     zero = be.NewStore(1).upload(S.zero[None])
     committer = fhe.LigeroCommitter(128, rows, cols, 2)
@@ -410,7 +410,7 @@ def test_store_marshal_ranges_and_chunks():
         return buf.tobytes()
     cts = rng.integers(0, 2**58, size=(37, 2, 2, 64), dtype=np.uint64)
     st = be.NewStore(37, 1).upload(cts)
-    for lf in (fhe.LeafFormat(b"abc", b"\x05", b"\x09\x08\x07"), fhe.LeafFormat(), fhe.LeafFormat.lattigo_like(b"m" * 13, 1, 64)):
+    for lf in (fhe.LeafFormat(b"abc", b"\x05", b"\x09\x08\x07"), fhe.LeafFormat(), fhe.LeafFormat.with_prefixes(b"m" * 13, 1, 64)):
         ser = [O.leaf_bytes(c, lf.header, lf.polyHeader, lf.limbHeader) for c in cts]
         assert marshal(st, 0, 37, lf) == b"".join(ser)
         assert marshal(st, 5, 9, lf) == b"".join(ser[5:14])
@@ -447,7 +447,7 @@ def test_ligero_e2e_marshal_decrypt_verify(logN, rows, cols, k):
     S = scenario(logN, rows, cols, k)
     P = S.P
     be = S.backend()
-    lf = fhe.LeafFormat.lattigo_like(b"\x01meta", 1, 1 << logN)
+    lf = fhe.LeafFormat.with_prefixes(b"\x01meta", 1, 1 << logN)
     matrix = be.NewStore(cols).upload(S.cts)
     zero = be.NewStore(1).upload(S.zero[None])
     committer = fhe.LigeroCommitter(128, rows, cols, 2)
@@ -485,4 +485,75 @@ def test_ligero_e2e_marshal_decrypt_verify(logN, rows, cols, k):
     bad[off_q + len(lf.header) + len(lf.polyHeader) + len(lf.limbHeader) + 3] ^= 1
     _, _, _, qc_bad, _, _ = fhe.EncryptedProof.UnmarshalBinary(bytes(bad), be.params, lf)
     assert not fhe.VerifyMerklePath(O.leaf_bytes(qc_bad[0], lf.header, lf.polyHeader, lf.limbHeader), paths[0], root, int(idx[0]))
+    be.Close()
+
+
+@pytest.mark.parametrize("logN,rows,cols,k", [(8, 256, 16, 5), (12, 4096, 8, 4)])
+def test_two_host_threads_one_context(logN, rows, cols, k):
+    """The reference issues InnerProduct(Matrix, r) and InnerProduct(Matrix, b) from two goroutines on shallow copies of one
+    evaluator (fhe/ligero.go:231-242, fhe/bfv.go:56-58).  include/lumenos_b200.h promises the same for one context and distinct
+    stores, and a per-thread lmn_last_error: two host threads call the ABI concurrently (ctypes releases the GIL), repeatedly,
+    while a third keeps provoking errors; every result must equal the oracle's and every thread must read its own error text."""
+    import ctypes as C
+    import threading
+    from lumenos_b200 import _capi
+    S = scenario(logN, rows, cols, k)
+    P, lib = S.P, _capi.lib()
+    be = S.backend()
+    be.SetBatch(6)
+    matrix = be.NewStore(cols).upload(S.cts)
+    vp = C.c_void_p
+    want = {"r": np.stack([P.inner_sum_eval_column(S.cts[j], S.rpt, rows, S.gal, S.evks)[0] for j in range(cols)]),
+            "b": np.stack([P.inner_sum_eval_column(S.cts[j], S.bpt, rows, S.gal, S.evks)[0] for j in range(cols)])}
+    errors, stop = [], threading.Event()
+
+    def worker(tag, pt):
+        try:
+            for _ in range(3):
+                out = be.NewStore(cols, 1)
+                _capi.check(lib.lmn_inner_product(be.ctx, matrix.h, pt.ctypes.data_as(vp), rows, out.h))
+                got = out.download()
+                if not np.array_equal(got, want[tag]):
+                    errors.append("%s: result differs from the oracle under concurrency" % tag)
+                # this thread's own failure: an out-of-range download; the message must be this one, not the other thread's
+                rc = lib.lmn_store_download(out.h, cols, 1, got.ctypes.data_as(vp))
+                msg = lib.lmn_last_error().decode()
+                if rc == 0 or "download range" not in msg:
+                    errors.append("%s: expected its own download error, got rc=%d %r" % (tag, rc, msg))
+                out.free()
+        except Exception as e:  # noqa: BLE001
+            errors.append("%s: %r" % (tag, e))
+
+    def heckler():
+        bad = be.NewStore(1, 0)
+        while not stop.is_set():
+            rc = lib.lmn_ct_rescale(be.ctx, bad.h, 0, bad.h, 0)          # level-0 input: always invalid
+            msg = lib.lmn_last_error().decode()
+            if rc == 0 or "Rescale output" not in msg:
+                errors.append("heckler: rc=%d %r" % (rc, msg))
+                break
+        bad.free()
+
+    ts = [threading.Thread(target=worker, args=("r", S.rpt)), threading.Thread(target=worker, args=("b", S.bpt)), threading.Thread(target=heckler)]
+    for t in ts:
+        t.start()
+    ts[0].join(); ts[1].join()
+    stop.set(); ts[2].join()
+    assert not errors, errors
+    be.Close()
+
+
+def test_ring_switch_key_with_base2_digits_is_rejected():
+    """fhe/ring_switch.go:47-55 asks Lattigo for BaseTwoDecomposition = 13; if Lattigo honoured it the key would carry base-2
+    sub-digits (evk.Value[d] of length > 1).  The ABI takes the digit shape and refuses such a key instead of misreading it."""
+    from lumenos_b200 import fhe
+    S = scenario(8, 128, 16, 4)
+    be = S.backend()
+    P = S.P
+    good = np.zeros((P.beta, 2, P.k + P.np, P.N), np.uint64)
+    with pytest.raises(fhe.LumenosError, match="base-2"):
+        fhe.RingSwitchServer(be, np.zeros((P.beta, 2) + good.shape[1:], np.uint64), 6)
+    with pytest.raises(fhe.LumenosError, match="RNS digits"):
+        fhe.RingSwitchServer(be, good[:1], 6)
+    fhe.RingSwitchServer(be, good, 6)
     be.Close()

@@ -125,3 +125,82 @@ def test_ring_switch_decrypts_under_small_key():
     assert out.shape == (2, 1, Ps.N)
     # an encryption of zero stays an encryption of zero (small noise) under the small key
     assert Ps.noise_bits(sks, out) < 45
+
+
+def test_ring_switch_preserves_a_message_at_stride_positions():
+    """P0 pin of the oracle's ring switch (VERDICT r1 #2c): a plaintext polynomial whose non-zero coefficients sit at multiples of
+    N/N' survives RingSwitchNew (fhe/ring_switch.go:106-113) as the small-ring polynomial with those coefficients, so decrypting
+    the level-0 LogN' ciphertext under sk' returns the small-ring slot vector it encodes.  Plaintext modulus 0x3ee0001 as in the
+    reference's own TestRingSwitch (fhe/ring_switch_test.go:18): with the 57-bit t of the benchmarks a level-0 ciphertext
+    (Q = [q0], 58 bits) has no noise budget left, which is why the reference calls this path experimental."""
+    logN, logNs, k = 8, 6, 4
+    T = 0x3ee0001
+    P = O.Params(logN, k=k, t=T)
+    Ps = O.Params(logNs, q=P.q[:1], p=P.p, t=T)
+    sk = P.keygen_sk(2); pk = P.keygen_pk(sk, 3)
+    sks = Ps.keygen_sk(9)
+    evk = P.keygen_ringswitch(sk, sks, logNs, 11)
+    rng = np.random.default_rng(4)
+    want = rng.integers(0, T, size=Ps.N, dtype=np.uint64)
+    q0 = int(P.q[0])
+    # coefficients of the small-ring plaintext: Ps.encode gives NTT(m' t^-1 mod q0); m' < t < q0, so INTT and * t recovers m'
+    mp = [(int(c) * (T % q0)) % q0 for c in Ps.intt(Ps.encode(want, 0)[0], 0)]
+    assert max(mp) < T
+    stride = P.N // Ps.N
+    pt = np.zeros((k, P.N), np.uint64)
+    for i in range(k):
+        qi = int(P.q[i])
+        tinv = pow(T % qi, -1, qi)
+        big = np.zeros(P.N, np.uint64)
+        big[::stride] = np.array([m * tinv % qi for m in mp], dtype=np.uint64)
+        pt[i] = P.ntt(big, i)
+    ct = P.encrypt(pk, pt, 5)
+    lvl1, scale = P.rescale_to_level1(ct)
+    out = P.ringswitch(lvl1, evk, logNs)
+    assert out.shape == (2, 1, Ps.N)
+    assert (Ps.decrypt(sks, out, scale) == want).all()
+    # and a message off the stride positions does not survive as such (the decimation drops it): sanity of the test itself
+    pt2 = np.zeros((k, P.N), np.uint64)
+    for i in range(k):
+        qi = int(P.q[i]); tinv = pow(T % qi, -1, qi)
+        big = np.zeros(P.N, np.uint64)
+        big[1::stride] = np.array([m * tinv % qi for m in mp], dtype=np.uint64)
+        pt2[i] = P.ntt(big, i)
+    out2 = P.ringswitch(P.rescale_to_level1(P.encrypt(pk, pt2, 6))[0], evk, logNs)
+    assert (Ps.decrypt(sks, out2, scale) != want).any()
+
+
+FLIPS = [("primroot_start", 2), ("scalar_centered", 0), ("digit_centered", 1), ("moddown_round_nearest", 0), ("innersum_rowswap_last", 0)]
+
+
+@pytest.mark.parametrize("name,value", FLIPS)
+def test_switch_flips_are_invisible_at_P0(name, value):
+    """VERDICT r1 #2d: every Lattigo-recollection switch flipped away from its default still passes the P0
+    equalities the reference's tests assert (TestEncode, TestLigeroE2E slot 0, rows == N) while CHANGING ciphertext limbs - i.e.
+    these five behaviours are exactly what decrypted-plaintext parity cannot pin (DESIGN.md section 5 lists them)."""
+    logN, rows, cols, k = 6, 64, 8, 6
+    outs = {}
+    for tag, sw in (("default", O.default_switches()), ("flipped", O.default_switches(**{name: value}))):
+        P = O.Params(logN, k=k, switches=sw)
+        sk = P.keygen_sk(2); pk = P.keygen_pk(sk, 3)
+        M = O.witness_matrix(rows, cols)
+        cts = np.stack([P.encrypt(pk, P.encode(M[:, j]), 100 + j) for j in range(cols)])
+        roots = O.field_roots_forward(2 * cols)
+        enc = P.fhe_encode(cts, 2, P.encrypt(pk, None, 4), roots)
+        exp = np.stack([O.core_encode(M[i], 2, roots) for i in range(rows)])
+        for j in range(2 * cols):
+            assert (P.decrypt(sk, enc[j])[:rows] == exp[:, j]).all(), (tag, j)
+        gal = P.galois_elements_for_innersum(rows)             # rows == N: includes the row swap
+        evks = [P.keygen_galois(sk, g, 5) for g in gal]
+        r = np.random.default_rng(1).integers(0, 2**63, size=rows, dtype=np.uint64)
+        rpt = P.encode(r)
+        ip, scale = P.inner_sum_eval_column(cts[1], rpt, rows, gal, evks)
+        assert int(P.decrypt(sk, ip, scale)[0]) == sum((int(a) % T) * int(b) % T for a, b in zip(r, M[:, 1])) % T, tag
+        outs[tag] = (enc, ip)
+    differs = not np.array_equal(outs["default"][0], outs["flipped"][0]) or not np.array_equal(outs["default"][1], outs["flipped"][1])
+    if name == "primroot_start":
+        # 2 is a quadratic residue modulo every prime = 1 (mod 8), hence never a generator of an NTT-friendly prime's group: the
+        # search finds the same root whether it starts at 2 or at 3, so this recollection cannot matter (closed, not unpinned)
+        assert not differs
+    else:
+        assert differs, "flipping %s does not change any limb: the switch is dead" % name

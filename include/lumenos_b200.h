@@ -232,6 +232,39 @@ int lmn_ct_copy(lmn_ctx *ctx, const lmn_store *a, uint32_t ai, lmn_store *o, uin
 /* ring.SubRing NTT / INTT of one limb of one polynomial, in place (test hook for the limb kernels) */
 int lmn_limb_ntt(lmn_ctx *ctx, lmn_store *a, uint32_t ai, uint32_t poly, uint32_t limb, int inverse);
 
+/* ---------------- the stages either side of the path ---------------- */
+/* Keys and the plaintext ring arrive as Lattigo holds them: psi_t = the primitive 2N-th root of unity of the encoder's ring T
+ * (ring.SubRing of t, as psi_q above); pk = pk.Value[0].Q, pk.Value[1].Q as [2][num_q][N] and sk = sk.Value.Q as [num_q][N],
+ * both NTT + MONTGOMERY form (rlwe.PublicKey / rlwe.SecretKey in memory). */
+int lmn_load_plaintext_ring(lmn_ctx *ctx, uint64_t psi_t);
+int lmn_load_public_key(lmn_ctx *ctx, const uint64_t *pk_host);
+int lmn_load_secret_key(lmn_ctx *ctx, const uint64_t *sk_host);
+/* core.RandomMatrixRowMajor's witness (core/utils.go:46-82) generated on the device: ChaCha20 (IETF; key = chacha_key32, zero nonce,
+ * counter 0) keystream as little-endian u64 words mod t, row-major rows x cols; host_out receives columns [first_col,
+ * first_col + n_cols) column-major, [n_cols][rows].  The reference's key is LE64(1) followed by 24 zero bytes. */
+int lmn_witness_columns(lmn_ctx *ctx, const uint8_t *chacha_key32, uint32_t rows, uint32_t cols, uint32_t first_col, uint32_t n_cols,
+                        uint64_t *host_out);
+/* "Encrypt matrix" span of the demo server (cmd/server/main.go:187-207) on the device.  For j in [0, count):
+ *   values = column first_col + j of the witness (values_colmajor_host [count][rows] when given, any u64, reduced mod t like
+ *            ringT.Reduce; else generated on the device from chacha_key32 as lmn_witness_columns does, rows x cols_total);
+ *   matrix[j] = EncryptNew(Encode(values)) at max level: ct = (u pk0 + e0 + pt, u pk1 + e1), u uniform ternary, e0 / e1 rounded
+ *            Gaussians (sigma 3.2, bound 19 = lattigo DefaultXe).
+ * All randomness comes from the ChaCha20 stream keyed by enc_seed32 with nonce (column index, stream), so a column's ciphertext
+ * does not depend on which rank or batch produced it.  Lattigo's own sampler stream cannot be reproduced (not vendored): the
+ * contract is that the client decrypts every column to the witness, with Lattigo-sized noise - not ciphertext bits. */
+int lmn_encrypt_columns(lmn_ctx *ctx, const uint64_t *values_colmajor_host, const uint8_t *chacha_key32, uint32_t rows, uint32_t cols_total,
+                        uint32_t first_col, uint32_t count, const uint8_t *enc_seed32, lmn_store *matrix);
+/* zeroCol of fhe.Encode (fhe/code.go:15-22): EncryptNew of the all-zero plaintext into out[out_idx]; stream_id plays the column
+ * index in the nonce (use one outside [0, cols)) */
+int lmn_encrypt_zero(lmn_ctx *ctx, const uint8_t *enc_seed32, uint32_t stream_id, lmn_store *out, uint32_t out_idx);
+/* backend.Encode(values, pt) at max level (fhe/ligero.go:204-205, 218-219: the r and b plaintexts of Prove): pt_host [num_q][N] */
+int lmn_encode_plaintext(lmn_ctx *ctx, const uint64_t *values, uint32_t n_values, uint64_t *pt_host);
+/* client side: EncryptedProof.Decrypt's decryptBatchedParallel (fhe/ligero.go:381-502, 577-636) = rlwe.Decryptor.DecryptNew +
+ * bgv.Encoder.Decode of ciphertexts [first, first + count) of a store of the context ring (any level); values_host receives the
+ * first n_values slots of each, [count][n_values].  scale = the ciphertexts' rlwe.MetaData.Scale (mod t). */
+int lmn_decrypt_decode(lmn_ctx *ctx, const lmn_store *s, uint32_t first, uint32_t count, uint64_t scale, uint32_t n_values,
+                       uint64_t *values_host);
+
 /* ---------------- measurement hooks (bench.py) ---------------- */
 /* per-kernel-class device timing with CUDA event pairs on the launch stream; mask bit i = class i */
 int lmn_profile_enable(lmn_ctx *ctx, uint32_t mask);

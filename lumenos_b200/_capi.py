@@ -65,6 +65,14 @@ SIGNATURES = {
     "lmn_kernel_count": (C.c_int, []),
     "lmn_kernel_name": (C.c_char_p, [C.c_int]),
     "lmn_bench_int_peak": (C.c_int, [vp, C.POINTER(C.c_double)]),
+    "lmn_load_plaintext_ring": (C.c_int, [vp, C.c_uint64]),
+    "lmn_load_public_key": (C.c_int, [vp, vp]),
+    "lmn_load_secret_key": (C.c_int, [vp, vp]),
+    "lmn_witness_columns": (C.c_int, [vp, C.c_char_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, vp]),
+    "lmn_encrypt_columns": (C.c_int, [vp, vp, C.c_char_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_char_p, vp]),
+    "lmn_encrypt_zero": (C.c_int, [vp, C.c_char_p, C.c_uint32, vp, C.c_uint32]),
+    "lmn_encode_plaintext": (C.c_int, [vp, vp, C.c_uint32, vp]),
+    "lmn_decrypt_decode": (C.c_int, [vp, vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, vp]),
     "lmn_load_galois_key": (C.c_int, [vp, C.c_uint64, vp]),
     "lmn_load_ring_switch_key": (C.c_int, [vp, C.c_uint32, vp, C.c_uint32, C.c_uint32, C.c_uint64]),
     "lmn_inner_product": (C.c_int, [vp, vp, vp, C.c_uint32, vp]),

@@ -335,6 +335,7 @@ void lmn_ctx_destroy(lmn_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    client_state_free(c->client);
     for (auto &kv : c->ks) cudaFree(kv.second.second);
     for (auto &kv : c->rs) cudaFree(kv.second);
     for (auto &kv : c->rs_chain) cudaFree(kv.second.second);

@@ -55,10 +55,11 @@ def calculateQueries(securityBits, rhoInv):
 class BGVParameters:
     """bgv.Parameters as the host holds them: moduli and the primitive 2N-th roots its rings use."""
 
-    def __init__(self, logN, Q, P, T, psi_q, psi_p):
+    def __init__(self, logN, Q, P, T, psi_q, psi_p, psi_t=None):
         self.logN, self.N, self.T = int(logN), 1 << int(logN), int(T)
         self.Q, self.P = _u64(Q), _u64(P)
         self.psi_q, self.psi_p = _u64(psi_q), _u64(psi_p)
+        self.psi_t = None if psi_t is None else int(psi_t)   # primitive 2N-th root of the encoder's ring T (Encode / Decode / Encrypt only)
 
     def MaxLevel(self):
         return len(self.Q) - 1
@@ -304,6 +305,92 @@ class ServerBFV:
     def RescaleScale(self, from_level, to_level):
         return _capi.lib().lmn_rescale_scale(self.ctx, from_level, to_level)
 
+    # -- bgv.Encoder / rlwe.Encryptor halves of ServerBFV (fhe/bfv.go:13-27), on the device --
+    def LoadPlaintextRing(self, psi_t=None):
+        psi_t = self.params.psi_t if psi_t is None else psi_t
+        if psi_t is None:
+            raise ValueError("the encoder needs psi_t, the primitive 2N-th root of unity of the plaintext ring")
+        check(_capi.lib().lmn_load_plaintext_ring(self.ctx, int(psi_t)))
+        self._ringT = True
+
+    def _need_ringT(self):
+        if not getattr(self, "_ringT", False):
+            self.LoadPlaintextRing()
+
+    def LoadPublicKey(self, pk):
+        """pk: [2][k][N] = pk.Value[0].Q, pk.Value[1].Q in NTT + Montgomery form (rlwe.PublicKey as Lattigo holds it)"""
+        self._need_ringT()
+        check(_capi.lib().lmn_load_public_key(self.ctx, _ptr(_u64(pk))))
+
+    def Encode(self, values):
+        """bgv.Encoder.Encode(values, pt) at max level (fhe/ligero.go:204-205): returns the plaintext limbs [k][N]"""
+        self._need_ringT()
+        v = _u64(values)
+        pt = np.empty((len(self.params.Q), self.params.N), np.uint64)
+        check(_capi.lib().lmn_encode_plaintext(self.ctx, _ptr(v), len(v), _ptr(pt)))
+        return pt
+
+    def EncryptColumns(self, rows, cols, encSeed, firstCol=0, count=None, values=None, witnessKey=None, out=None):
+        """"Encrypt matrix" of the demo server (cmd/server/main.go:187-207): EncryptNew(Encode(column)) for `count` columns from
+        firstCol.  values: [count][rows] column-major witness values, or None to generate core.RandomMatrixRowMajor's ChaCha20
+        witness on the device (witnessKey: 32 bytes, default the reference's LE64(1) key).  Returns the matrix store."""
+        count = cols - firstCol if count is None else count
+        out = self.NewStore(count) if out is None else out
+        key = None
+        vals = None
+        if values is None:
+            key = bytes(witnessKey) if witnessKey is not None else REFERENCE_WITNESS_KEY
+        else:
+            vals = _u64(values)
+            if vals.shape != (count, rows):
+                raise ValueError("values must be [count][rows]")
+        check(_capi.lib().lmn_encrypt_columns(self.ctx, None if vals is None else _ptr(vals), key, rows, cols, firstCol, count, bytes(encSeed), out.h))
+        return out
+
+    def EncryptZero(self, encSeed, streamId=0xFFFFFFFF, out=None, index=0):
+        """zeroCol of fhe.Encode (fhe/code.go:15-22)"""
+        out = self.NewStore(1) if out is None else out
+        check(_capi.lib().lmn_encrypt_zero(self.ctx, bytes(encSeed), streamId, out.h, index))
+        return out
+
+    def WitnessColumns(self, rows, cols, firstCol=0, count=None, witnessKey=None):
+        """columns of core.RandomMatrixRowMajor's matrix, generated on the device: [count][rows]"""
+        count = cols - firstCol if count is None else count
+        out = np.empty((count, rows), np.uint64)
+        key = bytes(witnessKey) if witnessKey is not None else REFERENCE_WITNESS_KEY
+        check(_capi.lib().lmn_witness_columns(self.ctx, key, rows, cols, firstCol, count, _ptr(out)))
+        return out
+
+
+REFERENCE_WITNESS_KEY = (1).to_bytes(8, "little") + bytes(24)     # core/utils.go:55-56: seed = LE64(1) || 0...
+
+
+class ClientBFV(ServerBFV):
+    """ref: fhe/bfv.go:60-106, as far as EncryptedProof.Decrypt uses it: rlwe.Decryptor + bgv.Encoder.Decode on the device
+    (SURVEY 8f-4).  sk: [k][N] = sk.Value.Q in NTT + Montgomery form."""
+
+    def __init__(self, ptField, params, sk, device=0, **kw):
+        super().__init__(ptField, params, device=device, **kw)
+        self.LoadPlaintextRing()
+        check(_capi.lib().lmn_load_secret_key(self.ctx, _ptr(_u64(sk))))
+
+    def DecryptDecode(self, store, nValues, first=0, count=None):
+        """Decrypt + Decode of store[first : first + count]: the first nValues slots of each, [count][nValues]"""
+        count = store.count - first if count is None else count
+        out = np.empty((count, nValues), np.uint64)
+        check(_capi.lib().lmn_decrypt_decode(self.ctx, store.h, first, count, int(store.scale), nValues, _ptr(out)))
+        return out
+
+    def DecryptArrays(self, cts, scale, nValues):
+        """the same for ciphertexts that arrived as host arrays [count][2][level+1][N] (EncryptedProof.ReadFrom)"""
+        cts = _u64(cts)
+        st = CiphertextStore(self, cts.shape[0], cts.shape[2] - 1).upload(cts)
+        st.scale = scale
+        try:
+            return self.DecryptDecode(st, nValues)
+        finally:
+            st.free()
+
 
 def NTT(values, size, backend):
     """ref: fhe/ntt.go:12-17 (len(values) == size).  Returns a new store holding the returned slice."""
@@ -372,6 +459,21 @@ class EncryptedProof:
         check(lib.lmn_proof_marshal(*args, C.c_void_p(buf.ctypes.data), buf.nbytes, C.byref(n)))
         return buf.tobytes()
 
+    def Decrypt(self, client):
+        """ref: fhe/ligero.go:381-502: queried columns -> `rows` slot values each, MatR / MatZ -> slot 0 of every ciphertext.
+        Returns Proof.  The stores are used in place when they live in the client's context, else they travel through the host
+        (in the reference the proof arrives over HTTP)."""
+        def dec(store, n):
+            if store.backend is client:
+                return client.DecryptDecode(store, n)
+            return client.DecryptArrays(store.download(), store.scale, n)
+        if self.MatR.N != client.params.N:
+            raise ValueError("ring-switched MatR / MatZ decrypt under the small-ring client (RingSwitch.NewClient), not this one")
+        q = dec(self.QueriedCols, self.Metadata.Rows)
+        r = dec(self.MatR, 1)[:, 0]
+        z = dec(self.MatZ, 1)[:, 0]
+        return Proof(self.Metadata, self.Root, r, z, q, self.MerklePaths)
+
     @staticmethod
     def UnmarshalBinary(data, params, leafFormat, queryFormat=None, matLevel=1, matN=None):
         """EncryptedProof.ReadFrom (ligero.go:706-755), host side (numpy): returns (metadata, MatR, MatZ, QueriedCols as uint64 arrays
@@ -413,6 +515,13 @@ class EncryptedProof:
             off += 32 * depth
         root = bytes(data[off:off + 32])
         return LigeroMetadata(rows, cols, rhoInv, queries), matR, matZ, qc, paths, root
+
+
+class Proof:
+    """ref: fhe/ligero.go:372-379: the decrypted proof (MatR / MatZ as field elements, queried columns as slot values)"""
+
+    def __init__(self, metadata, root, matR, matZ, queriedCols, merklePaths):
+        self.Metadata, self.Root, self.MatR, self.MatZ, self.QueriedCols, self.MerklePaths = metadata, root, matR, matZ, queriedCols, merklePaths
 
 
 class LeafFormat:

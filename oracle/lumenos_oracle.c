@@ -266,6 +266,7 @@ void orc_params_psi(const orc_params *P, u64 *psi_q, u64 *psi_p) {
     for (int i = 0; i < P->k; i++) psi_q[i] = P->mods[i].psi;
     for (int j = 0; j < P->np; j++) psi_p[j] = P->mods[P->k + j].psi;
 }
+u64 orc_params_psi_t(const orc_params *P) { return P->modt.psi; }   /* 2N-th root of the encoder's ring T (lattigo: ringT) */
 int orc_beta(const orc_params *P) { return (P->k + P->np - 1) / P->np; }
 
 void orc_ntt_limb(const orc_params *P, int mi, u64 *a) { ntt_fwd(&P->mods[mi], a); }

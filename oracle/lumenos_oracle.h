@@ -52,6 +52,7 @@ int orc_params_N(const orc_params *P);
 uint64_t orc_params_t(const orc_params *P);
 void orc_params_moduli(const orc_params *P, uint64_t *q, uint64_t *p);
 void orc_params_psi(const orc_params *P, uint64_t *psi_q, uint64_t *psi_p); /* plain (non-Montgomery) 2N-th roots */
+uint64_t orc_params_psi_t(const orc_params *P);                             /* the same for the plaintext ring Z_t[X]/(X^N+1) */
 /* fhe.GenerateBGVParamsForNTT heuristic: number of Q primes for a given nttSize (=cols) */
 int orc_num_q_primes_for_ntt(int nttSize, uint64_t t);
 

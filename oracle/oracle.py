@@ -56,6 +56,7 @@ def lib():
         "orc_params_t": (u64, [vp]),
         "orc_params_moduli": (None, [vp, _u64p, _u64p]),
         "orc_params_psi": (None, [vp, _u64p, _u64p]),
+        "orc_params_psi_t": (u64, [vp]),
         "orc_num_q_primes_for_ntt": (i, [i, u64]),
         "orc_witness_matrix": (None, [i, i, u64, _u64p]),
         "orc_field_roots_forward": (i, [u64, i, i, _u64p]),
@@ -127,6 +128,7 @@ class Params:
         self.psi_q = np.zeros(self.k, np.uint64)
         self.psi_p = np.zeros(self.np, np.uint64)
         L.orc_params_psi(self.h, self.psi_q, self.psi_p)
+        self.psi_t = L.orc_params_psi_t(self.h)
         self.beta = L.orc_beta(self.h)
         self.max_level = self.k - 1
 

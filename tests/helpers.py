@@ -31,9 +31,31 @@ class Scenario:
     def backend(self, **kw):
         from lumenos_b200 import fhe
         P = self.P
-        params = fhe.BGVParameters(self.logN, P.q, P.p, P.t, P.psi_q, P.psi_p)
+        params = fhe.BGVParameters(self.logN, P.q, P.p, P.t, P.psi_q, P.psi_p, P.psi_t)
         field = fhe.PrimeField(P.t, self.roots)
         be = fhe.ServerBFV(field, params, **kw)
         for g, e in zip(self.gal, self.evks):
             be.LoadGaloisKey(g, e)
         return be
+
+
+def mform(x, q):
+    """x * 2^64 mod q elementwise (Lattigo keeps keys in Montgomery form)"""
+    return np.array([(int(v) << 64) % int(q) for v in np.asarray(x).ravel()], dtype=np.uint64).reshape(np.shape(x))
+
+
+def pk_as_lattigo(P, pk):
+    """oracle public key [2][k][N] (NTT, canonical) -> NTT + Montgomery, as rlwe.PublicKey holds it"""
+    out = np.empty_like(pk)
+    for i in range(P.k):
+        out[:, i, :] = mform(pk[:, i, :], P.q[i])
+    return out
+
+
+def sk_as_lattigo(P, sk):
+    """oracle secret key (ternary coefficients) -> [k][N] NTT + Montgomery, as rlwe.SecretKey.Value.Q holds it"""
+    out = np.empty((P.k, P.N), np.uint64)
+    for i in range(P.k):
+        q = int(P.q[i])
+        out[i] = mform(P.ntt(np.array([int(v) % q for v in sk], dtype=np.uint64), i), q)
+    return out

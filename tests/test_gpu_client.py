@@ -1,0 +1,147 @@
+"""GPU tests (-m gpu) of the stages either side of the hot path, through the C ABI:
+  * the device witness generator against the oracle's core.RandomMatrixRowMajor restatement and the reference's P(1) known answers;
+  * the device batch encoder bit for bit against the oracle's bgv.Encoder.Encode;
+  * the device public-key encryptor at P0: the oracle's client decrypts every column to the witness, with noise no larger than the
+    oracle's own encryptor + 1 bit (Lattigo's sampler stream cannot be reproduced, so ciphertext bits are not the contract);
+  * the device decryptor + decoder against the oracle's Decrypt + Decode on the prover's real outputs."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from helpers import Scenario, pk_as_lattigo, sk_as_lattigo  # noqa: E402
+from oracle import oracle as O  # noqa: E402
+
+T = O.T_DEFAULT
+KAT = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "kat.json")))
+SEED = bytes(range(32))
+
+
+def _server(S):
+    be = S.backend()
+    be.LoadPublicKey(pk_as_lattigo(S.P, S.pk))
+    return be
+
+
+def test_witness_generator_matches_oracle_and_known_answers():
+    from lumenos_b200 import fhe, hostutil as H
+    S = Scenario(6, 32, 8, 3)
+    be = S.backend()
+    for rows, cols in ((32, 8), (33, 7), (64, 24)):
+        M = O.witness_matrix(rows, cols)
+        assert np.array_equal(be.WitnessColumns(rows, cols), M.T)
+        assert np.array_equal(be.WitnessColumns(rows, cols, firstCol=cols // 2, count=2), M.T[cols // 2:cols // 2 + 2])
+    be.Close()
+    # the reference's printed P(1) = sum of all entries mod t (results/baseline/client/bench_*.txt:22), at every benchmark shape
+    for shape, logN in (("2048x1024", 12), ("4096x2048", 12), ("8192x4096", 13), ("16384x4096", 14)):
+        rows, cols = map(int, shape.split("x"))
+        q, p = H.generate_moduli(logN, 2)
+        params = fhe.BGVParameters(logN, q, p, T, [H.psi_of(m, logN) for m in q], [H.psi_of(m, logN) for m in p])
+        be = fhe.ServerBFV(fhe.PrimeField(T, H.field_roots_forward(16, T)), params)
+        total = 0
+        for c0 in range(0, cols, 1024):
+            W = be.WitnessColumns(rows, cols, firstCol=c0, count=min(1024, cols - c0))
+            total += int((W & np.uint64(0xFFFFFFFF)).sum(dtype=np.uint64)) + (int((W >> np.uint64(32)).sum(dtype=np.uint64)) << 32)
+        assert total % T == KAT["witness_p1"][shape], shape
+        be.Close()
+
+
+@pytest.mark.parametrize("logN,k", [(6, 3), (8, 4), (12, 3), (13, 2), (14, 2)])
+def test_encode_plaintext_bit_exact(logN, k):
+    S = Scenario(logN, 1 << (logN - 1), 2, k)
+    be = S.backend()
+    rng = np.random.default_rng(logN)
+    for n in (1, 5, S.P.N // 2, S.P.N):
+        v = rng.integers(0, 2**63, size=n, dtype=np.uint64) * np.uint64(2) + np.uint64(1)      # unreduced, like SampleUints
+        assert np.array_equal(be.Encode(v), S.P.encode(v)), (logN, n)
+    be.Close()
+
+
+@pytest.mark.parametrize("logN,rows,cols,k", [(6, 32, 16, 6), (8, 256, 8, 4), (12, 2048, 8, 4), (12, 4096, 8, 3), (13, 8192, 4, 3), (14, 16384, 4, 3)])
+def test_encrypt_columns_decrypts_to_the_witness(logN, rows, cols, k):
+    S = Scenario(logN, rows, cols, k)
+    P = S.P
+    be = _server(S)
+    M = O.witness_matrix(rows, cols)
+    st = be.EncryptColumns(rows, cols, SEED)                       # witness generated on the device
+    cts = st.download()
+    ref_noise = max(P.noise_bits(S.sk, P.encrypt(S.pk, None, 77 + j)) for j in range(4))
+    for j in range(cols):
+        assert np.array_equal(P.decrypt(S.sk, cts[j])[:rows], M[:, j]), "column %d does not decrypt to the witness" % j
+    zero = be.EncryptZero(SEED).download()[0]
+    assert not P.decrypt(S.sk, zero).any()
+    assert P.noise_bits(S.sk, zero) <= ref_noise + 1.0, (P.noise_bits(S.sk, zero), ref_noise)
+    # the same columns from host values, in two shards: identical ciphertexts (randomness is keyed by the column index)
+    a = be.EncryptColumns(rows, cols, SEED, firstCol=0, count=cols // 2, values=M.T[:cols // 2].copy()).download()
+    b = be.EncryptColumns(rows, cols, SEED, firstCol=cols // 2, values=M.T[cols // 2:].copy()).download()
+    assert np.array_equal(np.concatenate([a, b]), cts)
+    # a different seed gives different ciphertexts of the same plaintexts; distinct columns use distinct randomness
+    other = be.EncryptColumns(rows, cols, bytes(32)).download()
+    assert not np.array_equal(other[0], cts[0]) and np.array_equal(P.decrypt(S.sk, other[0])[:rows], M[:, 0])
+    z2 = be.EncryptColumns(rows, 2, SEED, values=np.zeros((2, rows), np.uint64)).download()
+    assert not np.array_equal(z2[0], z2[1])
+    # sampler sanity on the raw noise polynomial of the zero encryption: c0 + c1 s = u e_pk + e0 + e1 s
+    be.Close()
+
+
+def test_encrypted_matrix_runs_the_whole_protocol():
+    """cmd/server/main.go:187-262 with the matrix encrypted on the device: Encrypt -> Commit -> Prove -> client Decrypt (device) ->
+    the checks of Proof.Verify, against the plaintext prover"""
+    from lumenos_b200 import fhe
+    logN, rows, cols, k = 8, 256, 16, 6
+    S = Scenario(logN, rows, cols, k)
+    P = S.P
+    be = _server(S)
+    M = O.witness_matrix(rows, cols)
+    matrix = be.EncryptColumns(rows, cols, SEED)
+    zero = be.EncryptZero(SEED)
+    committer = fhe.LigeroCommitter(128, rows, cols, 2)
+    lf = fhe.LeafFormat.placeholder(1, P.N)
+    prover = committer.Commit(matrix, be, (zero, 0), leafFormat=lf)
+    idx = (np.random.default_rng(5).integers(0, 2**62, size=committer.Queries) % (2 * cols)).astype(np.uint32)
+    rpt, bpt = be.Encode(S.r), be.Encode(S.b)                      # Prove's plaintexts encoded on the device
+    assert np.array_equal(rpt, S.rpt) and np.array_equal(bpt, S.bpt)
+    proof = prover.Prove(rpt, bpt, idx, be)
+    params = fhe.BGVParameters(logN, P.q, P.p, P.t, P.psi_q, P.psi_p, P.psi_t)
+    client = fhe.ClientBFV(fhe.PrimeField(P.t, S.roots), params, sk_as_lattigo(P, S.sk))
+    dec = proof.Decrypt(client)
+    Mo = M.astype(object)
+    r = np.array([int(x) % T for x in S.r], dtype=object)
+    b = np.array([int(x) for x in S.b], dtype=object)
+    assert [int(x) for x in dec.MatR] == [int(x) % T for x in r.dot(Mo)]
+    assert [int(x) for x in dec.MatZ] == [int(x) % T for x in b.dot(Mo)]
+    encR, encZ = O.core_encode(dec.MatR, 2, S.roots), O.core_encode(dec.MatZ, 2, S.roots)
+    for i, ix in enumerate(idx):
+        col = dec.QueriedCols[i].astype(object)
+        assert int(col.dot(r)) % T == int(encR[ix]) and int(col.dot(b)) % T == int(encZ[ix]), "well-formedness check failed for column %d" % ix
+    client.Close(); be.Close()
+
+
+@pytest.mark.parametrize("logN,rows,cols,k", [(6, 32, 16, 6), (8, 256, 8, 5), (12, 4096, 8, 4), (14, 16384, 4, 3)])
+def test_decrypt_decode_matches_oracle(logN, rows, cols, k):
+    from lumenos_b200 import fhe
+    S = Scenario(logN, rows, cols, k)
+    P = S.P
+    params = fhe.BGVParameters(logN, P.q, P.p, P.t, P.psi_q, P.psi_p, P.psi_t)
+    client = fhe.ClientBFV(fhe.PrimeField(P.t, S.roots), params, sk_as_lattigo(P, S.sk))
+    for g, e in zip(S.gal, S.evks):
+        client.LoadGaloisKey(g, e)
+    # max-level inputs: every slot
+    st = client.NewStore(cols).upload(S.cts)
+    got = client.DecryptDecode(st, P.N)
+    for j in range(cols):
+        assert np.array_equal(got[j], P.decrypt(S.sk, S.cts[j])), j
+    assert np.array_equal(got[:, :rows], O.witness_matrix(rows, cols).T)
+    # level-1 outputs of the prover with the tracked Scale (Rescale multiplies it by q_l^-1 mod t)
+    matR = fhe.matrixInnerSumEval(st, S.rpt, rows, client)
+    lvl1 = matR.download()
+    got = client.DecryptDecode(matR, 3)
+    for j in range(cols):
+        assert np.array_equal(got[j], P.decrypt(S.sk, lvl1[j], matR.scale)[:3]), j
+    # ranges and the host-array path
+    assert np.array_equal(client.DecryptDecode(matR, 1, first=1, count=2), got[1:3, :1])
+    assert np.array_equal(client.DecryptArrays(lvl1, matR.scale, 3), got)
+    client.Close()

@@ -250,6 +250,8 @@ def main():
     be = fhe.ServerBFV(field, params, device=local, stream=stream.cuda_stream)
     be.SetBatch(args.batch)
     lib = _capi.lib()
+    if G > 1:
+        sharding.init_comm(be, rank, G)      # the library's own NCCL communicator: every exchange of the path runs behind the C ABI
     rng = np.random.default_rng(1234 + rank)
     mods = list(q) + list(p)
     beta = (k + len(p) - 1) // len(p)
@@ -295,6 +297,7 @@ def main():
     matR = be.NewStore(cols_loc, lout)
     matZ = be.NewStore(cols_loc, lout)
     queried = be.NewStore(max(1, len(my_q)), lout)
+    q_full = be.NewStore(max(1, len(my_q)), k - 1) if G > 1 else None     # whole ciphertexts of this rank's queried columns
     rpt = np.stack([rng.integers(0, m, size=N, dtype=np.uint64) for m in q])
     bpt = np.stack([rng.integers(0, m, size=N, dtype=np.uint64) for m in q])
     plan = be._plan(cols, RHO_INV)
@@ -320,12 +323,9 @@ def main():
         if G == 1:
             _capi.check(lib.lmn_query_columns(be.ctx, enc_store.h, my_idx.ctypes.data_as(vp), len(my_idx), queried.h))
         else:
-            # coefficient slices of the queried columns -> whole ciphertexts on the rank that rescales them
-            full = sharding.exchange_queried(enc_t, qidx, rank, G)
-            st = fhe.CiphertextStore(be, len(my_q), k - 1, wrap_ptr=full.data_ptr())
-            _capi.check(lib.lmn_query_columns(be.ctx, st.h, arange_idx.ctypes.data_as(vp), len(my_q), queried.h))
-            torch.cuda.current_stream(dev).synchronize()
-            st.free()
+            # coefficient slices of the queried columns -> whole ciphertexts on the rank that rescales them (lmn_exchange_queried)
+            sharding.exchange_queried(be, enc_t, qidx, out=q_full)
+            _capi.check(lib.lmn_query_columns(be.ctx, q_full.h, arange_idx.ctypes.data_as(vp), len(my_q), queried.h))
 
     def barrier():
         if G > 1:
@@ -507,13 +507,10 @@ def main():
                 _capi.check(lib.lmn_commit_leaves(be.ctx, enc_store.h, leaves.h))
                 t = fhe.MerkleTree(be, leaves, lf)
             else:
-                # coefficient slices -> this rank's block of whole encoded columns (all-to-all), local leaves + hashes, gathered tree
-                blk = sharding.exchange_encoded(enc_t, rank, G)
-                st = fhe.CiphertextStore(be, n_loc, k - 1, wrap_ptr=blk.data_ptr())
-                _capi.check(lib.lmn_commit_leaves(be.ctx, st.h, leaves.h))
-                t = sharding.commit_tree(be, leaves, lf, rank, G)
-                torch.cuda.current_stream(dev).synchronize()
-                st.free()
+                # coefficient slices -> this rank's block of whole encoded columns, rescaled to leaves chunk by chunk behind the all-to-all
+                # (lmn_commit_leaves_from_slices), leaf hashes per rank, all-gathered (lmn_allgather_leaf_hashes), tree on every rank
+                sharding.commit_leaves_from_slices(be, enc_t, leaves)
+                t = sharding.commit_tree(be, leaves, lf)
             root = t.MerkleRoot()
             t.free()
             return root
@@ -576,6 +573,32 @@ def main():
                          "note": "MatR || MatZ || QueriedCols serialised on the GPU (k_ct_stream) in 64 MiB chunks, each copied to the pinned proof buffer while the next is produced; metadata, Merkle paths and root written by the host"}
         lib.lmn_host_free(h_proof)
 
+    # ---- SURVEY 8f rows 3 and 4, beside the headline: the demo server's "Encrypt matrix" span (cmd/server/main.go:199-207, witness
+    # generated and encrypted on the device: no upload at all) and the client's Decrypt of the proof (fhe/ligero.go:381-502) ----
+    encrypt_matrix = client_decrypt = None
+    if not args.no_commit:
+        be.params.psi_t = H.psi_of(T, logN)
+        be.LoadPublicKey(np.stack([rng.integers(0, m, size=(2, N), dtype=np.uint64) for m in q], axis=1))          # [2][k][N] random residues
+        _capi.check(lib.lmn_load_secret_key(be.ctx, np.stack([rng.integers(0, m, size=N, dtype=np.uint64) for m in q]).ctypes.data_as(vp)))
+        seed = bytes(range(32))
+        enc_once = lambda: be.EncryptColumns(rows, cols, seed, firstCol=rank * cols_loc, count=cols_loc, out=mat_cols)  # noqa: E731
+        enc_once()
+        em_ms = timed(enc_once, 1)
+        encrypt_matrix = {"ms": em_ms, "columns": cols, "published_reference_s": {"A": 3.30, "B": 7.14, "C": 32.15, "D": 66.84}.get(args.config),
+                          "note": "core.RandomMatrixRowMajor's ChaCha20 witness + bgv Encode + pk EncryptNew of every column on the device "
+                                  "(lmn_encrypt_columns), ciphertexts written straight into the matrix store; with it the matrix upload of e2e disappears"}
+        vals_q = np.empty((max(1, len(my_q)), rows), np.uint64)
+        vals_r, vals_z = np.empty((cols_loc, 1), np.uint64), np.empty((cols_loc, 1), np.uint64)
+
+        def dec_once():
+            for st, out, nv in ((queried, vals_q, rows), (matR, vals_r, 1), (matZ, vals_z, 1)):
+                _capi.check(lib.lmn_decrypt_decode(be.ctx, st.h, 0, st.count, 1, nv, out.ctypes.data_as(vp)))
+        dec_once()
+        cd_ms = timed(dec_once, 1)
+        client_decrypt = {"ms": cd_ms, "ciphertexts": 2 * cols + nq_total, "published_reference_s": {"A": 0.627, "B": 1.16, "C": 4.54, "D": 48.05}.get(args.config),
+                          "note": "EncryptedProof.Decrypt on the device (lmn_decrypt_decode): %d queried columns to %d values each, MatR / MatZ to slot 0; "
+                                  "published = the reference client Decrypt total span (README.md:87, m6i.large client)" % (nq_total, rows)}
+
     # ---- e2e: host buffers through the C ABI, H2D + D2H inside the timed region ----
     e2e = None
     if not args.no_e2e:
@@ -585,9 +608,8 @@ def main():
             return ptr
         h_mat = halloc(mat_cols.nbytes)
         _capi.check(lib.lmn_store_download(mat_cols.h, 0, cols_loc, h_mat))
-        h_enc_t = mat_enc_t.cpu().pin_memory() if G > 1 else None   # pinned host copy of this rank's Encode slice
         h_r, h_z, h_q = halloc(matR.nbytes), halloc(matZ.nbytes), halloc(queried.nbytes)
-        h2d = mat_cols.nbytes + (mat_enc_t.numel() * 8 if G > 1 else 0) + 2 * k * N * 8
+        h2d = mat_cols.nbytes + 2 * k * N * 8
         d2h = matR.nbytes + matZ.nbytes + queried.nbytes
 
         def e2e_step():
@@ -596,8 +618,9 @@ def main():
             if G == 1:
                 _capi.check(lib.lmn_encode_host(be.ctx, plan, h_mat, mat_cols.h, zero_store.h, 0, enc_store.h))
             else:
+                # the matrix goes up ONCE, as this rank's column block; its coefficient slices for Encode are derived over NVLink
                 _capi.check(lib.lmn_store_upload(mat_cols.h, 0, cols_loc, h_mat))
-                mat_enc_t.copy_(h_enc_t, non_blocking=True)
+                sharding.to_slices(be, mat_cols, cols, mat_enc_t)
                 _capi.check(lib.lmn_encode_lanes(be.ctx, plan, vp(mat_enc_t.data_ptr()), vp(zero_t.data_ptr()), vp(enc_t.data_ptr()), log_ns))
             _capi.check(lib.lmn_inner_product2_host(be.ctx, mat_cols.h, rpt.ctypes.data_as(vp), bpt.ctypes.data_as(vp), rows, matR.h, matZ.h, h_r, h_z))
             query_stage()
@@ -606,7 +629,7 @@ def main():
         e2e_steps = max(1, min(args.steps, 3))
         e2e_ms = timed(e2e_step, e2e_steps) / e2e_steps
         e2e = {"value": e2e_ms / 1e3, "unit": "s", "h2d_bytes_per_step": int(h2d) * G, "d2h_bytes_per_step": int(d2h) * G, "steps": e2e_steps,
-               "path": "lmn_encode_host (pinned host -> HBM limb by limb behind the Encode kernels) + lmn_inner_product2_host (results to pinned host batch by batch behind the kernels) + lmn_query_columns + lmn_store_download"}
+               "path": ("lmn_encode_host (pinned host -> HBM limb by limb behind the Encode kernels)" if G == 1 else "lmn_store_upload of the column block + lmn_exchange_to_slices (NVLink all-to-all) + lmn_encode_lanes") + " + lmn_inner_product2_host (results to pinned host batch by batch behind the kernels) + " + ("" if G == 1 else "lmn_exchange_queried + ") + "lmn_query_columns + lmn_store_download"}
         for hptr in (h_mat, h_r, h_z, h_q):
             if hptr:
                 lib.lmn_host_free(hptr)
@@ -628,7 +651,8 @@ def main():
                        "batch_jobs": args.batch},
             "parity_check": parity,
             "e2e": e2e, "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "roofline_hbm": roofline_hbm,
-            "roofline_encode": roofline_encode, "kernel_rooflines": kernel_rooflines, "kernel_breakdown_one_step": breakdown, "commit_merkle": commit_merkle, "ring_switch_E": ring_switch, "proof_marshal": proof_marshal, "cpu_baseline": cpu,
+            "roofline_encode": roofline_encode, "kernel_rooflines": kernel_rooflines, "kernel_breakdown_one_step": breakdown, "commit_merkle": commit_merkle, "ring_switch_E": ring_switch, "proof_marshal": proof_marshal,
+            "encrypt_matrix": encrypt_matrix, "client_decrypt": client_decrypt, "cpu_baseline": cpu,
             "published_reference_s": PUBLISHED_S[args.config],
         }
         print(json.dumps(out))

@@ -232,6 +232,33 @@ int lmn_ct_copy(lmn_ctx *ctx, const lmn_store *a, uint32_t ai, lmn_store *o, uin
 /* ring.SubRing NTT / INTT of one limb of one polynomial, in place (test hook for the limb kernels) */
 int lmn_limb_ntt(lmn_ctx *ctx, lmn_store *a, uint32_t ai, uint32_t poly, uint32_t limb, int inverse);
 
+/* ---------------- multi-GPU exchange (one process per GPU, NCCL over NVLink) ---------------- */
+/* The inner products, the query rescale and the leaf rescale shard by COLUMN BLOCK (rank r owns ciphertexts [r n/G, (r+1) n/G));
+ * Encode shards by COEFFICIENT SLICE (rank r holds coefficients [r N/G, (r+1) N/G) of every limb of every ciphertext, laid out
+ * [ciphertext][poly][limb][N/G], see lmn_encode_lanes).  The calls below are the layout changes between the two, as grouped
+ * ncclSend / ncclRecv all-to-alls on the communicator's own stream, ordered with the context's stream by events.  Every rank must
+ * make the same calls in the same order with the same batch size (lmn_ctx_set_batch bounds the chunk of an exchange).  NCCL is
+ * resolved at run time (dlopen of libnccl.so.2: the copy the process already has loaded, else the system's). */
+int lmn_comm_unique_id(uint8_t *out128);                                    /* ncclGetUniqueId on one rank; the host distributes it */
+int lmn_comm_init(lmn_ctx *ctx, const uint8_t *id128, int rank, int world); /* ncclCommInitRank on the context's device */
+int lmn_comm_destroy(lmn_ctx *ctx);
+int lmn_comm_rank(const lmn_ctx *ctx);
+int lmn_comm_world(const lmn_ctx *ctx);
+/* Prove without a leaves store (fhe/ligero.go:262-280): whole max-level ciphertexts of the queried columns this rank rescales
+ * (query positions rank, rank + G, ... of query_idx, which is identical on all ranks) from every rank's slice of the encoded
+ * matrix (n ciphertexts); out holds ceil((n_queries - rank) / G) entries in list order */
+int lmn_exchange_queried(lmn_ctx *ctx, const void *enc_slice_dev, uint32_t n, const uint32_t *query_idx, uint32_t n_queries, lmn_store *out);
+/* the whole encoded matrix: slices -> this rank's column block (n / G max-level ciphertexts) */
+int lmn_exchange_encoded(lmn_ctx *ctx, const void *enc_slice_dev, uint32_t n, lmn_store *block);
+/* Commit's leaves (fhe/ligero.go:126-183) of this rank's column block straight from the slices: the all-to-all of one chunk runs
+ * while the previous chunk is rescaled to level 1; == lmn_exchange_encoded + lmn_commit_leaves without the intermediate store */
+int lmn_commit_leaves_from_slices(lmn_ctx *ctx, const void *enc_slice_dev, uint32_t n, lmn_store *leaves);
+/* the inverse: this rank's column block of n / G ciphertexts -> its coefficient slice of all n ciphertexts (a matrix uploaded or
+ * encrypted once as column blocks feeds the slice-wise Encode) */
+int lmn_exchange_to_slices(lmn_ctx *ctx, const lmn_store *block, uint32_t n, void *slice_dev);
+/* Merkle leaf hashes of all ranks in column order: mine = 32 n_local bytes (lmn_leaf_hashes), all = 32 n_local G bytes (host) */
+int lmn_allgather_leaf_hashes(lmn_ctx *ctx, const uint8_t *mine, uint32_t n_local, uint8_t *all);
+
 /* ---------------- the stages either side of the path ---------------- */
 /* Keys and the plaintext ring arrive as Lattigo holds them: psi_t = the primitive 2N-th root of unity of the encoder's ring T
  * (ring.SubRing of t, as psi_q above); pk = pk.Value[0].Q, pk.Value[1].Q as [2][num_q][N] and sk = sk.Value.Q as [num_q][N],

@@ -65,6 +65,16 @@ SIGNATURES = {
     "lmn_kernel_count": (C.c_int, []),
     "lmn_kernel_name": (C.c_char_p, [C.c_int]),
     "lmn_bench_int_peak": (C.c_int, [vp, C.POINTER(C.c_double)]),
+    "lmn_comm_unique_id": (C.c_int, [C.c_char_p]),
+    "lmn_comm_init": (C.c_int, [vp, C.c_char_p, C.c_int, C.c_int]),
+    "lmn_comm_destroy": (C.c_int, [vp]),
+    "lmn_comm_rank": (C.c_int, [vp]),
+    "lmn_comm_world": (C.c_int, [vp]),
+    "lmn_exchange_queried": (C.c_int, [vp, vp, C.c_uint32, vp, C.c_uint32, vp]),
+    "lmn_exchange_encoded": (C.c_int, [vp, vp, C.c_uint32, vp]),
+    "lmn_commit_leaves_from_slices": (C.c_int, [vp, vp, C.c_uint32, vp]),
+    "lmn_exchange_to_slices": (C.c_int, [vp, vp, C.c_uint32, vp]),
+    "lmn_allgather_leaf_hashes": (C.c_int, [vp, C.c_char_p, C.c_uint32, C.c_char_p]),
     "lmn_load_plaintext_ring": (C.c_int, [vp, C.c_uint64]),
     "lmn_load_public_key": (C.c_int, [vp, vp]),
     "lmn_load_secret_key": (C.c_int, [vp, vp]),

@@ -336,6 +336,7 @@ void lmn_ctx_destroy(lmn_ctx *c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     client_state_free(c->client);
+    comm_state_free(c->comm);
     for (auto &kv : c->ks) cudaFree(kv.second.second);
     for (auto &kv : c->rs) cudaFree(kv.second);
     for (auto &kv : c->rs_chain) cudaFree(kv.second.second);
@@ -874,6 +875,24 @@ static int rescale_select(lmn_ctx *c, const lmn_store *enc, const uint32_t *idx,
     CK(cudaGetLastError());
     return 0;
 }
+}  // extern "C"
+// out[j] (level 1, packed) = src[j] (max level, consecutive raw device ciphertexts) rescaled, j < count.  Caller holds the lock.
+int rescale_consecutive(lmn_ctx *c, const u64 *src, uint32_t count, u64 *out) {
+    const int Lmax = c->k - 1, lout = std::min(1, Lmax);
+    const uint32_t bc = c->batch;
+    if (int rc = ensure_workspace(c, std::min(bc, count))) return rc;
+    Launch L = c->L();
+    const size_t out_words = 2 * (size_t)(lout + 1) * c->n, in_words = 2 * (size_t)c->k * c->n;
+    for (uint32_t j0 = 0; j0 < count; j0 += bc) {
+        const uint32_t nj = std::min(bc, count - j0);
+        KsJobs J = jobs_view(c, 0, nj);
+        if (int rc = rescale_jobs_to(c, Lmax, lout, J, src + (size_t)j0 * in_words)) return rc;
+        launch_pack_out(L, c->T, J, lout + 1, out + j0 * out_words);
+    }
+    CK(cudaGetLastError());
+    return 0;
+}
+extern "C" {
 int lmn_query_columns(lmn_ctx *c, const lmn_store *enc, const uint32_t *idx, uint32_t n_idx, lmn_store *out) {
     if (!c || !enc || !idx || !out || n_idx == 0) return fail(LMN_ERR_INVALID, "null argument");
     std::lock_guard<std::mutex> g(c->mu);

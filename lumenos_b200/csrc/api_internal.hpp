@@ -28,12 +28,14 @@ struct DevScratch {
     void *release() { void *r = p; p = nullptr; return r; }
 };
 
+struct CommState;
 struct ClientState;     // plaintext ring, public / secret key material of the client-side entry points (api_client.cu)
 void client_state_free(ClientState *);
 
 struct lmn_ctx {
     int device = 0;
     ClientState *client = nullptr;
+    CommState *comm = nullptr;
     int logn = 0, n = 0, k = 0, np = 0;
     u64 t = 0;
     std::vector<u64> q, p;                  // moduli: mod(i) = i < k ? q[i] : p[i-k]
@@ -81,6 +83,10 @@ struct lmn_store {
     uint32_t n = 0;   // ring degree of the entries (ctx->n, or the small ring for ring-switch outputs)
     size_t words() const { return 2 * (size_t)(level + 1) * n; }
 };
+
+struct CommState;       // NCCL communicator and exchange buffers (api_comm.cu)
+void comm_state_free(CommState *);
+int rescale_consecutive(lmn_ctx *c, const u64 *src, uint32_t count, u64 *out);   // api.cu; caller holds the context lock
 
 // staged host -> device copies on the context's stream (api.cu); caller holds the context lock
 int stage_begin(lmn_ctx *c, size_t total);

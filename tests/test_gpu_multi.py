@@ -34,12 +34,16 @@ vp = C.c_void_p
 _capi.check(lib.lmn_encode_lanes(be.ctx, be._plan(S.cols, 2), vp(m_sl.data_ptr()), vp(z_sl.data_ptr()), vp(e_sl.data_ptr()), (hi - lo).bit_length() - 1))
 be.Synchronize()
 assert np.array_equal(e_sl.cpu().numpy().astype(np.uint64), want_enc[..., lo:hi]), "sliced Encode differs"
-# query columns via the all-to-all
+# the library's communicator (NCCL behind the C ABI), bootstrapped through torch.distributed
+sharding.init_comm(be, rank, world)
+assert lib.lmn_comm_rank(be.ctx) == rank and lib.lmn_comm_world(be.ctx) == world
+# query columns via the library's all-to-all (lmn_exchange_queried), cross-checked against the torch.distributed twin
 qidx = np.random.default_rng(3).integers(0, 2 * S.cols, size=37); qidx[4] = qidx[1]
-full = sharding.exchange_queried(e_sl, qidx, rank, world)
 mine = sharding.queries_of(len(qidx), rank, world)
-st = fhe.CiphertextStore(be, len(mine), P.k - 1, wrap_ptr=full.data_ptr())
-out = be.NewStore(len(mine), 1)
+st = sharding.exchange_queried(be, e_sl, qidx)
+full = sharding.exchange_queried_torch(e_sl, qidx, rank, world)
+assert np.array_equal(st.download()[:len(mine)], full.cpu().numpy().astype(np.uint64)), "library and torch all-to-all disagree"
+out = be.NewStore(max(1, len(mine)), 1)
 idx = np.arange(len(mine), dtype=np.uint32)
 _capi.check(lib.lmn_query_columns(be.ctx, st.h, idx.ctypes.data_as(vp), len(mine), out.h))
 got = out.download()
@@ -64,21 +68,40 @@ dist.all_gather_object(parts_z, sharding.marshal_columns(be, mz, wf))
 want_r = b"".join(O.leaf_bytes(P.inner_sum_eval_column(S.cts[j], S.rpt, S.rows, S.gal, S.evks)[0], wf.header, wf.polyHeader, wf.limbHeader) for j in range(S.cols))
 want_z = b"".join(O.leaf_bytes(P.inner_sum_eval_column(S.cts[j], S.bpt, S.rows, S.gal, S.evks)[0], wf.header, wf.polyHeader, wf.limbHeader) for j in range(S.cols))
 assert b"".join(parts_r) == want_r and b"".join(parts_z) == want_z, "sharded MatR / MatZ wire sections differ from the oracle"
-# Commit's Merkle span, sharded: slices -> column blocks, local leaf rescale + leaf hashes, gathered tree == the 1-GPU tree
+# Commit's Merkle span, sharded: slices -> column blocks (lmn_exchange_encoded), local leaf rescale + leaf hashes, gathered tree
 n = 2 * S.cols
-blk = sharding.exchange_encoded(e_sl, rank, world, chunks=2)
 a2, b2 = sharding.column_range(n, rank, world)
-assert np.array_equal(blk.cpu().numpy().astype(np.uint64), want_enc[a2:b2]), "column block of the encoded matrix differs"
-est = fhe.CiphertextStore(be, b2 - a2, P.k - 1, wrap_ptr=blk.data_ptr())
-leaves = be.NewStore(b2 - a2, 1)
-_capi.check(lib.lmn_commit_leaves(be.ctx, est.h, leaves.h))
+for batch in (64, 3):                       # the batch size bounds the exchange chunk: one chunk, and several with a remainder
+    be.SetBatch(batch)
+    blk = sharding.exchange_encoded(be, e_sl)
+    assert np.array_equal(blk.download(), want_enc[a2:b2]), "column block of the encoded matrix differs (batch %%d)" %% batch
+    blk_t = sharding.exchange_encoded_torch(e_sl, rank, world, chunks=2)
+    assert np.array_equal(blk_t.cpu().numpy().astype(np.uint64), want_enc[a2:b2])
+    # the pipelined form: leaves straight from the slices == exchange + lmn_commit_leaves
+    leaves = sharding.commit_leaves_from_slices(be, e_sl)
+    leaves2 = be.NewStore(b2 - a2, 1)
+    _capi.check(lib.lmn_commit_leaves(be.ctx, blk.h, leaves2.h))
+    want_leaves = np.stack([P.rescale_to_level1(want_enc[j])[0] for j in range(a2, b2)])
+    assert np.array_equal(leaves.download(), want_leaves) and np.array_equal(leaves2.download(), want_leaves), "leaves differ (batch %%d)" %% batch
+    # and back: column block -> coefficient slices reproduces this rank's slice of the encoded matrix
+    back = torch.empty_like(e_sl)
+    sharding.to_slices(be, blk, n, back)
+    be.Synchronize()
+    assert torch.equal(back, e_sl), "block -> slices does not invert slices -> block (batch %%d)" %% batch
 lf = fhe.LeafFormat.with_prefixes(b"hdr-bytes", 1, P.N)
-tree = sharding.commit_tree(be, leaves, lf, rank, world)
+tree = sharding.commit_tree(be, leaves, lf)
 bufs = [O.leaf_bytes(P.rescale_to_level1(want_enc[j])[0], lf.header, lf.polyHeader, lf.limbHeader) for j in range(n)]
 want_tree = O.MerkleTree(bufs)
 assert tree.MerkleRoot() == want_tree.root(), "sharded Merkle root differs from the oracle"
 for j in (0, a2, b2 - 1, n - 1):
     assert tree.GetMerklePath(j) == want_tree.path(j)
+# the matrix itself: uploaded once as a column block, its coefficient slices derived over NVLink feed the same Encode
+a, b = sharding.column_range(S.cols, rank, world)
+mat_blk = be.NewStore(b - a).upload(S.cts[a:b])
+m_sl2 = torch.empty_like(m_sl)
+sharding.to_slices(be, mat_blk, S.cols, m_sl2)
+be.Synchronize()
+assert torch.equal(m_sl2, m_sl), "matrix slices derived from the column blocks differ from the host-sliced ones"
 # query stage from the local leaves
 own = [int(q) for q in qidx if a2 <= q < b2]
 if own:

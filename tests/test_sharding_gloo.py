@@ -21,13 +21,13 @@ g = torch.Generator().manual_seed(5)
 enc = torch.randint(0, 2**62, (n, 2, k, N), generator=g, dtype=torch.int64)        # same on every rank
 qidx = np.random.default_rng(3).integers(0, n, size=nq); qidx[4] = qidx[1]
 lo, hi = S.coefficient_range(N, rank, world)
-full = S.exchange_queried(enc[..., lo:hi].contiguous(), qidx, rank, world)
+full = S.exchange_queried_torch(enc[..., lo:hi].contiguous(), qidx, rank, world)
 mine = S.queries_of(nq, rank, world)
 assert full.shape == (len(mine), 2, k, N)
 assert torch.equal(full, enc[torch.as_tensor(qidx[mine])]), "rank %%d: reassembled ciphertexts differ" %% rank
 # whole encoded matrix: coefficient slices -> column blocks (Commit's leaf span)
 for chunks in (1, 3, 8):
-    blk = S.exchange_encoded(enc[..., lo:hi].contiguous(), rank, world, chunks=chunks)
+    blk = S.exchange_encoded_torch(enc[..., lo:hi].contiguous(), rank, world, chunks=chunks)
     a, b = S.column_range(n, rank, world)
     assert blk.shape == (b - a, 2, k, N) and torch.equal(blk, enc[a:b]), "rank %%d: column block differs" %% rank
 # partitions

@@ -9,7 +9,6 @@ for CFG in "$@"; do
     [ $G -le $N ] || continue
     python -m torch.distributed.run --nnodes=1 --nproc-per-node $G --master-addr 127.0.0.1 --master-port $((29700+G)) bench.py --gpus $G --config $CFG --no-cpu \
       > gpurun_out/${TAG}_bench_${CFG}_${G}gpu.json 2> gpurun_out/${TAG}_bench_${CFG}_${G}gpu.err || tail -20 gpurun_out/${TAG}_bench_${CFG}_${G}gpu.err
-    python -c "
-import json;d=json.loads(open("gpurun_out/${TAG}_bench_${CFG}_${G}gpu.json").read().strip().splitlines()[-1]);print('$CFG',$G,'s/step',d['value'],'e2e',d['e2e']['value'],d['parity_check'][:40],'roofline',d['roofline']['frac'],'merkle',d['commit_merkle']['ms'])"
+    python tools/benchline.py gpurun_out/${TAG}_bench_${CFG}_${G}gpu.json
   done
 done

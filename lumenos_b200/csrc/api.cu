@@ -342,7 +342,7 @@ void lmn_ctx_destroy(lmn_ctx *c) {
     for (auto &kv : c->rs_chain) cudaFree(kv.second.second);
     for (auto &kv : c->galois) cudaFree(kv.second);
     cudaFree(c->d_mods); cudaFree(c->d_twf); cudaFree(c->d_twi); cudaFree(c->d_twbf); cudaFree(c->d_twbi); cudaFree(c->ws_pt); cudaFree(c->ws_scalar);
-    cudaFree(c->ws_col); cudaFree(c->ws_col2); cudaFree(c->ws_y); cudaFree(c->ws_acc); cudaFree(c->ws_idx);
+    cudaFree(c->ws_col); cudaFree(c->ws_col2); cudaFree(c->ws_y); cudaFree(c->ws_acc); cudaFree(c->ws_idx); cudaFree(c->ws_ser);
     cudaFree(c->d_rs_evk); cudaFree(c->d_small_mod); cudaFree(c->d_small_tw); cudaFree(c->d_key_fm); cudaFree(c->ws_mu);
     for (int i = 0; i < KID_COUNT; i++) for (auto &sp : c->prof.spans[i]) { cudaEventDestroy(sp.first); cudaEventDestroy(sp.second); }
     for (auto e : c->prof.pool) cudaEventDestroy(e);
@@ -1191,16 +1191,17 @@ int lmn_proof_marshal(lmn_ctx *c, const lmn_ligero_metadata *md, const lmn_store
 // leaf hashes (level 0) computed on the device into d_nodes[0 .. n); caller holds the lock
 static cudaError_t hash_leaves_dev(lmn_ctx *c, const lmn_store *leaves, const LeafFormat &F, uint32_t *d_nodes) {
     const uint32_t n = leaves->count;
-    u64 *ser = nullptr;
-    cudaError_t e = cudaMalloc(&ser, (size_t)n * F.padded_len);
-    if (e != cudaSuccess) return e;
+    const size_t bytes = (size_t)n * F.padded_len;
+    if (c->ws_ser_cap < bytes) {
+        cudaFree(c->ws_ser); c->ws_ser = nullptr; c->ws_ser_cap = 0;
+        cudaError_t e = cudaMalloc(&c->ws_ser, bytes);
+        if (e != cudaSuccess) return e;
+        c->ws_ser_cap = bytes;
+    }
     Launch L = c->L();
-    launch_leaf_serialize(L, F, leaves->d, leaves->words(), n, ser);
-    launch_sha256_leaves(L, ser, F.padded_len, n, d_nodes);
-    e = cudaGetLastError();
-    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);   // `ser` is freed below
-    cudaFree(ser);
-    return e;
+    launch_leaf_serialize(L, F, leaves->d, leaves->words(), n, c->ws_ser);
+    launch_sha256_leaves(L, c->ws_ser, F.padded_len, n, d_nodes);
+    return cudaGetLastError();
 }
 // parent levels on the device from the n leaf hashes in d_nodes, the whole tree copied to the host object
 static cudaError_t finish_tree(lmn_ctx *c, lmn_merkle *m, uint32_t *d_nodes, uint32_t total_nodes) {
@@ -1251,7 +1252,9 @@ int lmn_leaf_hashes(lmn_ctx *c, const lmn_store *leaves, const lmn_leaf_format *
     uint32_t *d_nodes = nullptr;
     cudaError_t e = cudaMalloc(&d_nodes, (size_t)leaves->count * 32);
     if (e == cudaSuccess) e = hash_leaves_dev(c, leaves, F, d_nodes);
-    if (e == cudaSuccess) e = cudaMemcpy(out, d_nodes, (size_t)leaves->count * 32, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_nodes, (size_t)leaves->count * 32, cudaMemcpyDeviceToHost, c->stream);
+    cudaError_t e2 = cudaStreamSynchronize(c->stream);        // the hashes are home; d_nodes / d_hdr may go
+    if (e == cudaSuccess) e = e2;
     cudaFree(d_nodes); cudaFree(d_hdr);
     if (e != cudaSuccess) return fail(LMN_ERR_CUDA, std::string("leaf hashes: ") + cudaGetErrorString(e));
     return 0;

@@ -64,6 +64,7 @@ struct lmn_ctx {
     uint32_t batch = 64;
     u64 *ws_col = nullptr, *ws_col2 = nullptr, *ws_y = nullptr, *ws_acc = nullptr, *ws_mu = nullptr, *ws_pt = nullptr;
     uint32_t *ws_idx = nullptr; size_t ws_idx_cap = 0;
+    u64 *ws_ser = nullptr; size_t ws_ser_cap = 0;           // serialised leaves of the Merkle build (pooled: no allocation per Commit)
     ulonglong2 *ws_scalar = nullptr;
     uint32_t ws_jobs = 0;
     uint64_t launches = 0;

@@ -5,7 +5,8 @@
 // The rescale of the n encoded ciphertexts is the rescale pipeline of the prove path (kernels_blk.cu); here:
 //   k_leaf_serialize   leaf byte stream = header || 2 x ( poly_header || (level+1) x ( limb_header || N little-endian u64 ) )
 //                      plus the SHA-256 padding, written as whole 64-byte blocks (HBM-bound, byte-exact for any header length)
-//   k_sha256_leaves    one thread per leaf, streaming its blocks (latency-bound chain of 64 rounds per block; n chains)
+//   k_sha256_leaves    one lane per leaf (a leaf is one sequential SHA-256 chain; n chains), a producer warp expanding the message
+//                      schedule for the consumer warp that runs the rounds
 //   k_sha256_nodes     one thread per parent: SHA-256(left || right), right = left for the unpaired last node
 // The framing bytes are the caller's (lattigo's rlwe.Ciphertext.WriteTo layout is owned by the Go host).
 #include <cstdlib>
@@ -153,30 +154,75 @@ __global__ void __launch_bounds__(256) k_ct_stream(const LeafFormat F, const u64
     out[w] = v;
 }
 
-// one thread per leaf; blocks are read one ahead of the compression that consumes them
-__global__ void __launch_bounds__(32) k_sha256_leaves(const uint4 *__restrict__ ser, uint32_t blocks_per_leaf, uint32_t n_leaves,
+// SHA-256 of the serialised leaves.  A leaf is ONE message (one sequential chain of compressions), so the only parallelism is across
+// leaves: n chains, one per lane.  What can be taken off the chain is the message schedule: a CTA is a pair of warps over the same
+// 32 leaves - the PRODUCER warp loads each 64-byte block, expands W[0..63] and leaves W[i] + K[i] in a 4-deep ring in shared memory,
+// the CONSUMER warp runs only the 64 rounds (per round: SHF, LOP3, IADD3 on the e-chain).  The two warps sit on different
+// schedulers and hand slots over with named barriers (bar.arrive releases the producer's stores, bar.sync acquires them).
+// Measured on B200, 8192 leaves of 512 KiB: 15.8 ms with one thread doing both halves -> see DESIGN.md section 8.
+constexpr int SHA_DEPTH = 4;
+__device__ __forceinline__ void named_sync(int id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
+__device__ __forceinline__ void named_arrive(int id) { asm volatile("bar.arrive %0, 64;" ::"r"(id) : "memory"); }
+__global__ void __launch_bounds__(64) k_sha256_leaves(const uint4 *__restrict__ ser, uint32_t blocks_per_leaf, uint32_t n_leaves,
                                                       uint32_t *__restrict__ hashes) {
-    const uint32_t leaf = blockIdx.x * blockDim.x + threadIdx.x;
-    if (leaf >= n_leaves) return;
-    const uint4 *p = ser + (size_t)leaf * blocks_per_leaf * 4;
-    uint32_t st[8];
-    sha256_init(st);
-    uint4 nx[4];
+    __shared__ uint32_t ring[SHA_DEPTH][64][32];      // [slot][round][lane] = W + K
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t leaf_id = blockIdx.x * 32 + lane;
+    const uint32_t leaf = leaf_id < n_leaves ? leaf_id : n_leaves - 1;     // idle lanes shadow the last leaf (barriers count whole warps)
+    if (warp == 1) {
+        const uint4 *p = ser + (size_t)leaf * blocks_per_leaf * 4;
+        uint4 nx[4];
 #pragma unroll
-    for (int j = 0; j < 4; j++) nx[j] = __ldcs(p + j);
+        for (int j = 0; j < 4; j++) nx[j] = __ldcs(p + j);
 #pragma unroll 1
-    for (uint32_t b = 0; b < blocks_per_leaf; b++) {
-        uint32_t w[16];
+        for (uint32_t b = 0; b < blocks_per_leaf; b++) {
+            uint32_t w[16];
 #pragma unroll
-        for (int j = 0; j < 4; j++) { w[4 * j] = bswap32(nx[j].x); w[4 * j + 1] = bswap32(nx[j].y); w[4 * j + 2] = bswap32(nx[j].z); w[4 * j + 3] = bswap32(nx[j].w); }
-        if (b + 1 < blocks_per_leaf) {
+            for (int j = 0; j < 4; j++) { w[4 * j] = bswap32(nx[j].x); w[4 * j + 1] = bswap32(nx[j].y); w[4 * j + 2] = bswap32(nx[j].z); w[4 * j + 3] = bswap32(nx[j].w); }
+            if (b + 1 < blocks_per_leaf) {
 #pragma unroll
-            for (int j = 0; j < 4; j++) nx[j] = __ldcs(p + 4 * (size_t)(b + 1) + j);
+                for (int j = 0; j < 4; j++) nx[j] = __ldcs(p + 4 * (size_t)(b + 1) + j);
+            }
+            const int slot = (int)(b & (SHA_DEPTH - 1));
+            if (b >= SHA_DEPTH) named_sync(1 + SHA_DEPTH + slot);           // the consumer has finished with this slot
+#pragma unroll
+            for (int i = 0; i < 64; i++) {
+                if (i >= 16) {
+                    const uint32_t w15 = w[(i + 1) & 15], w2 = w[(i + 14) & 15];
+                    const uint32_t s0 = rotr(w15, 7) ^ rotr(w15, 18) ^ (w15 >> 3);
+                    const uint32_t s1 = rotr(w2, 17) ^ rotr(w2, 19) ^ (w2 >> 10);
+                    w[i & 15] = w[i & 15] + s0 + w[(i + 9) & 15] + s1;
+                }
+                ring[slot][i][lane] = w[i & 15] + SHA_K[i];
+            }
+            named_arrive(1 + slot);                                        // slot full
         }
-        sha256_compress(st, w);
-    }
+    } else {
+        uint32_t st[8];
+        sha256_init(st);
+#pragma unroll 1
+        for (uint32_t b = 0; b < blocks_per_leaf; b++) {
+            const int slot = (int)(b & (SHA_DEPTH - 1));
+            named_sync(1 + slot);
+            uint32_t a = st[0], bb = st[1], c = st[2], d = st[3], e = st[4], f = st[5], g = st[6], h = st[7];
 #pragma unroll
-    for (int i = 0; i < 8; i++) hashes[(size_t)leaf * 8 + i] = bswap32(st[i]);   // digest bytes in memory order
+            for (int i = 0; i < 64; i++) {
+                const uint32_t x = h + ring[slot][i][lane];               // off the chain: h is three rounds old
+                const uint32_t S1 = rotr(e, 6) ^ rotr(e, 11) ^ rotr(e, 25);
+                const uint32_t ch = (e & f) ^ (~e & g);
+                const uint32_t t1 = x + S1 + ch;
+                const uint32_t S0 = rotr(a, 2) ^ rotr(a, 13) ^ rotr(a, 22);
+                const uint32_t mj = (a & bb) ^ (a & c) ^ (bb & c);
+                h = g; g = f; f = e; e = d + t1; d = c; c = bb; bb = a; a = t1 + S0 + mj;
+            }
+            if (b + SHA_DEPTH < blocks_per_leaf) named_arrive(1 + SHA_DEPTH + slot);   // slot free (only while the producer still waits for it)
+            st[0] += a; st[1] += bb; st[2] += c; st[3] += d; st[4] += e; st[5] += f; st[6] += g; st[7] += h;
+        }
+        if (leaf_id < n_leaves) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) hashes[(size_t)leaf * 8 + i] = bswap32(st[i]);   // digest bytes in memory order
+        }
+    }
 }
 
 // parents[i] = SHA-256(children[2i] || children[2i+1]); the last child of an odd level is paired with itself (tree.go:122-130)
@@ -212,11 +258,7 @@ void launch_ct_stream(const Launch &L, const LeafFormat &F, const u64 *cts, uint
 }
 void launch_sha256_leaves(const Launch &L, const u64 *ser, uint32_t padded_len, uint32_t n_leaves, uint32_t *hashes) {
     LaunchScope scope(L, KID_SHA_LEAF);
-    // a leaf is one sequential SHA-256 chain, so the launch has only n_leaves threads.  Lanes per warp, measured on B200:
-    // 256 leaves of 512 KiB: 15.6 ms (32 lanes) / 14.4 ms (8); 8192 leaves: 15.8 ms (32) / 24.1 ms (8) - full warps win once every
-    // scheduler has a chain to run
-    constexpr int tpb = 32;   // == the kernel's __launch_bounds__
-    k_sha256_leaves<<<(n_leaves + tpb - 1) / tpb, tpb, 0, L.stream>>>(reinterpret_cast<const uint4 *>(ser), padded_len / 64, n_leaves, hashes);
+    k_sha256_leaves<<<(n_leaves + 31) / 32, 64, 0, L.stream>>>(reinterpret_cast<const uint4 *>(ser), padded_len / 64, n_leaves, hashes);
 }
 void launch_sha256_nodes(const Launch &L, const uint32_t *children, uint32_t n_children, uint32_t *parents) {
     LaunchScope scope(L, KID_SHA_NODE);

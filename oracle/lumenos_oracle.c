@@ -459,6 +459,16 @@ void orc_core_encode(const u64 *row, int cols, int rhoInv, u64 t, const u64 *roo
     orc_core_ntt(out, n, n, t, roots, n);
 }
 
+/* ref: core/math.go:8-21 InnerProduct over every column of a row-major matrix, as LigeroProveReference computes MatR / MatZ
+ * (fhe/ligero.go:799-953): out[j] = sum_i (r_i mod t) M[i][j] mod t */
+void orc_vec_mat_mod(const u64 *r, const u64 *M_rowmajor, int rows, int cols, u64 t, u64 *out) {
+    memset(out, 0, sizeof(u64) * (size_t)cols);
+    for (int i = 0; i < rows; i++) {
+        const u64 ri = r[i] % t; const u64 *row = M_rowmajor + (size_t)i * cols;
+        for (int j = 0; j < cols; j++) out[j] = addmod(out[j], mulmod(ri, row[j], t), t);
+    }
+}
+
 /* ------------------------------------------------------------------------------------------ */
 /* ServerBFV operator level                                                                   */
 /* ------------------------------------------------------------------------------------------ */

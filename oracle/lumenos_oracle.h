@@ -56,6 +56,9 @@ uint64_t orc_params_psi_t(const orc_params *P);                             /* t
 /* fhe.GenerateBGVParamsForNTT heuristic: number of Q primes for a given nttSize (=cols) */
 int orc_num_q_primes_for_ntt(int nttSize, uint64_t t);
 
+/* plaintext prover's row combinations (core/math.go:8-21, fhe/ligero.go:799-953): out[j] = sum_i r_i M[i][j] mod t */
+void orc_vec_mat_mod(const uint64_t *r, const uint64_t *M_rowmajor, int rows, int cols, uint64_t t, uint64_t *out);
+
 /* ---- witness generator (core/utils.go:46-82) ---- */
 void orc_witness_matrix(int rows, int cols, uint64_t t, uint64_t *out_rowmajor);
 

@@ -60,6 +60,7 @@ def lib():
         "orc_num_q_primes_for_ntt": (i, [i, u64]),
         "orc_witness_matrix": (None, [i, i, u64, _u64p]),
         "orc_field_roots_forward": (i, [u64, i, i, _u64p]),
+        "orc_vec_mat_mod": (None, [_u64p, _u64p, i, i, u64, _u64p]),
         "orc_core_ntt": (None, [_u64p, i, i, u64, _u64p, i]),
         "orc_core_encode": (None, [_u64p, i, i, u64, _u64p, _u64p]),
         "orc_ntt_limb": (None, [vp, i, _u64p]), "orc_intt_limb": (None, [vp, i, _u64p]),
@@ -310,6 +311,14 @@ def field_roots_forward(n_field, t=T_DEFAULT, primroot_start=3):
     if lib().orc_field_roots_forward(t, n_field, primroot_start, tab) != 0:
         raise ValueError("invalid field parameters")
     return tab
+
+
+def vec_mat_mod(r, M, t=T_DEFAULT):
+    """sum_i r_i M[i][j] mod t for every column j of the row-major matrix M (the plaintext prover's MatR / MatZ)"""
+    M = np.ascontiguousarray(M, np.uint64)
+    out = np.zeros(M.shape[1], np.uint64)
+    lib().orc_vec_mat_mod(np.ascontiguousarray(r, np.uint64), M, M.shape[0], M.shape[1], t, out)
+    return out
 
 
 def core_ntt(values, size, roots, t=T_DEFAULT):

@@ -145,3 +145,67 @@ def test_decrypt_decode_matches_oracle(logN, rows, cols, k):
     assert np.array_equal(client.DecryptDecode(matR, 1, first=1, count=2), got[1:3, :1])
     assert np.array_equal(client.DecryptArrays(lvl1, matR.scale, 3), got)
     client.Close()
+
+
+@pytest.mark.parametrize("rows,cols,logN,k,p1", [(8192, 4096, 13, 12, 125815544481056462), (16384, 4096, 14, 12, 5538402014578059)])
+def test_config_C_D_whole_protocol_on_real_encryptions(rows, cols, logN, k, p1):
+    """BASELINE.json configs[2] and configs[3] (the headline shape) end to end on REAL ciphertexts, which the device encryptor makes
+    affordable: the ChaCha20 witness of the reference (P(1) known answer from results/baseline/client/bench_*.txt:22) is encrypted on
+    the GPU under an oracle-generated key pair, Commit (Encode + leaves + Merkle tree) and Prove (both inner products with the
+    row-swap step, 309 queried columns) run at full size with real Galois keys, the client decrypts on the GPU, and the checks of the
+    reference's own test pass: MatR / MatZ == LigeroProveReference (fhe/ligero_test.go:164-174), both well-formedness relations of
+    Proof.Verify on every queried column (fhe/ligero.go:554-571), every Merkle path, the evaluation claim.  Two MatR columns and one
+    queried column are also compared bit for bit with the oracle evaluated on the downloaded input ciphertexts."""
+    import hashlib
+    from lumenos_b200 import fhe
+    assert O.lib().orc_num_q_primes_for_ntt(cols, T) == k
+    P = O.Params(logN, k=k)
+    sk = P.keygen_sk(2); pk = P.keygen_pk(sk, 3)
+    gal = P.galois_elements_for_innersum(rows)
+    evks = [P.keygen_galois(sk, g, 5) for g in gal]
+    roots = O.field_roots_forward(2 * cols)
+    params = fhe.BGVParameters(logN, P.q, P.p, P.t, P.psi_q, P.psi_p, P.psi_t)
+    be = fhe.ClientBFV(fhe.PrimeField(P.t, roots), params, sk_as_lattigo(P, sk))      # server and client roles on one context
+    be.LoadPublicKey(pk_as_lattigo(P, pk))
+    for g, e in zip(gal, evks):
+        be.LoadGaloisKey(g, e)
+    be.SetBatch(592)
+    M = O.witness_matrix(rows, cols)
+    total = int((M & np.uint64(0xFFFFFFFF)).sum(dtype=np.uint64)) + (int((M >> np.uint64(32)).sum(dtype=np.uint64)) << 32)
+    assert total % T == p1
+    matrix = be.EncryptColumns(rows, cols, SEED)
+    zero = be.EncryptZero(SEED)
+    committer = fhe.LigeroCommitter(128, rows, cols, 2)
+    assert committer.Queries == 309
+    lf = fhe.LeafFormat.placeholder(1, P.N)
+    prover = committer.Commit(matrix, be, (zero, 0), leafFormat=lf)
+    rng = np.random.default_rng(1)
+    r = rng.integers(0, 2**63, size=rows, dtype=np.uint64) * np.uint64(2) + np.uint64(1)
+    z = 3
+    zc = pow(z, cols, T)
+    b = np.array([pow(zc, i, T) for i in range(rows)], dtype=np.uint64)
+    idx = (np.random.default_rng(5).integers(0, 2**62, size=309) % (2 * cols)).astype(np.uint32)
+    idx[7] = idx[3]
+    proof = prover.Prove(be.Encode(r), be.Encode(b), idx, be)
+    dec = proof.Decrypt(be)
+    wantR, wantZ = O.vec_mat_mod(r, M), O.vec_mat_mod(b, M)
+    assert np.array_equal(dec.MatR, wantR), "MatR differs from the plaintext prover"
+    assert np.array_equal(dec.MatZ, wantZ), "MatZ differs from the plaintext prover"
+    encR, encZ = O.core_encode(dec.MatR, 2, roots), O.core_encode(dec.MatZ, 2, roots)
+    qcols = proof.QueriedCols.download()
+    for i, ix in enumerate(idx):
+        col = dec.QueriedCols[i]
+        assert int(O.vec_mat_mod(r, col[:, None])[0]) == int(encR[ix]), "well-formedness R check failed for column %d" % ix
+        assert int(O.vec_mat_mod(b, col[:, None])[0]) == int(encZ[ix]), "well-formedness B check failed for column %d" % ix
+        leaf = O.leaf_bytes(qcols[i], lf.header, lf.polyHeader, lf.limbHeader)
+        assert fhe.VerifyMerklePath(leaf, proof.MerklePaths[i], proof.Root, int(ix)), "merkle path of column %d" % ix
+    a = np.array([pow(z, i, T) for i in range(cols)], dtype=np.uint64)
+    assert int(O.vec_mat_mod(a, dec.MatZ[:, None])[0]) == int(O.vec_mat_mod(a, wantZ[:, None])[0])      # the evaluation claim
+    # P1 on samples: the oracle evaluated on the very ciphertexts the device encryptor produced
+    rpt = be.Encode(r)
+    for j in (0, cols - 1):
+        want, _ = P.inner_sum_eval_column(matrix.download(j, 1)[0], rpt, rows, gal, evks)
+        assert np.array_equal(proof.MatR.download(j, 1)[0], want), "MatR[%d] differs from the oracle" % j
+    assert np.array_equal(qcols[3], qcols[7])
+    assert np.array_equal(qcols[0], P.rescale_to_level1(prover.EncodedMatrix.download(int(idx[0]), 1)[0])[0])
+    be.Close()

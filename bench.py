@@ -473,6 +473,15 @@ def main():
                        "traffic": (NCU_ENCODE_TRAFFIC_D if args.config == "D" and G == 1 and not args.cols_override else None),
                        "traffic_source": "ncu --set full at config D, both passes (profiles/, see NCU_ENCODE_TRAFFIC_D)",
                        "ms_per_step": enc_s * 1e3, "share_of_step": enc_ms / total_ms}
+    # the same kernel on the integer side: per lane one Encode is `adds` butterflies (one add + one sub) and `muls` Shoup multiplications
+    # (fhe/ntt.go op counts); 28 multiplier-pipe cycles per multiplication against 5.7 pipe lane-cycles per HBM byte
+    # of machine balance put it ABOVE the ridge (12.8 lane-cycles per algorithmic byte at D): it is integer / issue bound, not HBM bound
+    p_adds, p_subs, p_muls = be.PlanCounts(cols, RHO_INV)
+    enc_lanes = 2 * k * (Ns if G > 1 else N)
+    roofline_encode["int"] = {"bound": "int", "unit": "Gbutterfly/s", "achieved": p_adds * enc_lanes / enc_s / 1e9, "peak": pk.value / 1e9,
+                              "frac": p_adds * enc_lanes / enc_s / pk.value, "muls_per_butterfly": p_muls / p_adds,
+                              "note": "butterflies (add + sub pairs) per second against the NTT butterfly ceiling; an Encode butterfly carries %.2f multiplications "
+                                      "where an NTT butterfly carries 1, so this fraction understates the kernel by about that factor in multiplier work and overstates it in additions" % (p_muls / p_adds)}
 
     # kernel-class breakdown of one extra (untimed) step with every class bracketed by event pairs, and one integer-roofline object per
     # hot class: units of work per job from work_per_job(), jobs from the library's launch accounting
@@ -630,6 +639,25 @@ def main():
         e2e_ms = timed(e2e_step, e2e_steps) / e2e_steps
         e2e = {"value": e2e_ms / 1e3, "unit": "s", "h2d_bytes_per_step": int(h2d) * G, "d2h_bytes_per_step": int(d2h) * G, "steps": e2e_steps,
                "path": ("lmn_encode_host (pinned host -> HBM limb by limb behind the Encode kernels)" if G == 1 else "lmn_store_upload of the column block + lmn_exchange_to_slices (NVLink all-to-all) + lmn_encode_lanes") + " + lmn_inner_product2_host (results to pinned host batch by batch behind the kernels) + " + ("" if G == 1 else "lmn_exchange_queried + ") + "lmn_query_columns + lmn_store_download"}
+        if encrypt_matrix is not None:
+            # the demo server's own flow (cmd/server/main.go:187-262, -benchMode): the matrix is generated and encrypted by the server, so
+            # nothing is uploaded; results still come home inside the timed region
+            def e2e_dev_step():
+                be.EncryptColumns(rows, cols, seed, firstCol=rank * cols_loc, count=cols_loc, out=mat_cols)
+                if G == 1:
+                    _capi.check(lib.lmn_encrypt_zero(be.ctx, seed, 0xFFFFFFFF, zero_store.h, 0))
+                    _capi.check(lib.lmn_encode(be.ctx, plan, mat_cols.h, zero_store.h, 0, enc_store.h))
+                else:
+                    sharding.to_slices(be, mat_cols, cols, mat_enc_t)
+                    _capi.check(lib.lmn_encode_lanes(be.ctx, plan, vp(mat_enc_t.data_ptr()), vp(zero_t.data_ptr()), vp(enc_t.data_ptr()), log_ns))
+                _capi.check(lib.lmn_inner_product2_host(be.ctx, mat_cols.h, rpt.ctypes.data_as(vp), bpt.ctypes.data_as(vp), rows, matR.h, matZ.h, h_r, h_z))
+                query_stage()
+                _capi.check(lib.lmn_store_download(queried.h, 0, max(1, len(my_q)), h_q))
+            e2e_dev_step()
+            dv_ms = timed(e2e_dev_step, e2e_steps) / e2e_steps
+            encrypt_matrix["e2e_with_device_encryption_s"] = dv_ms / 1e3
+            encrypt_matrix["e2e_with_device_encryption_note"] = ("Encrypt matrix (device) + Encode + Prove with MatR / MatZ / queried columns copied to pinned host memory inside the "
+                                                                 "timed region; h2d = the two plaintexts only (the contract's `e2e` above keeps the 12.9 GB upload)")
         for hptr in (h_mat, h_r, h_z, h_q):
             if hptr:
                 lib.lmn_host_free(hptr)

@@ -9,6 +9,7 @@
 //   fhe::matrixInnerSumEval        fhe/ligero.go:299-370     fhe::calculateQueries     fhe/ligero.go:65-71
 //
 //   core::MerkleTree / NewTree     core/tree.go:15-21, 76-219  (Commit's "Merkle tree built" span, fhe/ligero.go:105-116)
+//   fhe::ServerBFV::EncryptColumns cmd/server/main.go:187-207 fhe::ClientBFV            fhe/bfv.go:60-106, fhe/ligero.go:381-502
 //
 // Keys, encryption and the merlin transcript stay with the host application (they are Lattigo / Go territory in the
 // reference); they enter here as data (plaintext limbs, Galois keys, the zero column, query indices, the framing bytes of
@@ -65,6 +66,7 @@ struct Parameters {
     int LogN = 0;
     std::vector<uint64_t> Q, P, PsiQ, PsiP;   // moduli and the primitive 2N-th roots the host rings use (plain form)
     uint64_t T = 0;
+    uint64_t PsiT = 0;                        // primitive 2N-th root of the encoder's ring T (Encode / Encrypt / Decode only)
     int N() const { return 1 << LogN; }
     int MaxLevel() const { return (int)Q.size() - 1; }
     uint64_t GaloisElement(int k) const {
@@ -152,6 +154,19 @@ class ServerBFV {
     void CopyNew(Operand a, Operand o) { check(lmn_ct_copy(ctx_, a.first->handle(), a.second, o.first->handle(), o.second)); }
     uint64_t RescaleScale(int from, int to) const { return lmn_rescale_scale(ctx_, (uint32_t)from, (uint32_t)to); }
 
+    // the bgv.Encoder / rlwe.Encryptor halves of ServerBFV (fhe/bfv.go:13-27) on the device
+    void LoadPlaintextRing() { check(lmn_load_plaintext_ring(ctx_, params_.PsiT)); }
+    void LoadPublicKey(const uint64_t *pk) { LoadPlaintextRing(); check(lmn_load_public_key(ctx_, pk)); }   // [2][k][N] NTT + Montgomery
+    std::vector<uint64_t> Encode(const std::vector<uint64_t> &values) {                                      // bgv.Encoder.Encode at max level
+        std::vector<uint64_t> pt(params_.Q.size() * (size_t)params_.N());
+        check(lmn_encode_plaintext(ctx_, values.data(), (uint32_t)values.size(), pt.data()));
+        return pt;
+    }
+    // "Encrypt matrix" (cmd/server/main.go:187-207); values == nullptr: core.RandomMatrixRowMajor's ChaCha20 witness on the device
+    void EncryptColumns(uint32_t rows, uint32_t cols, uint32_t firstCol, uint32_t count, const uint8_t encSeed[32], CiphertextStore &out,
+                        const uint64_t *valuesColMajor = nullptr);
+    void EncryptZero(const uint8_t encSeed[32], CiphertextStore &out, uint32_t index = 0, uint32_t streamId = 0xffffffffu);
+
     lmn_plan *plan(uint32_t cols, uint32_t rhoInv) {
         auto key = std::make_pair(cols, rhoInv);
         for (auto &pl : plans_) if (pl.first == key) return pl.second;
@@ -169,6 +184,31 @@ class ServerBFV {
     lmn_ctx *ctx_ = nullptr;
     int mulCounter_ = 0;
     std::vector<std::pair<std::pair<uint32_t, uint32_t>, lmn_plan *>> plans_;
+};
+
+inline void ServerBFV::EncryptColumns(uint32_t rows, uint32_t cols, uint32_t firstCol, uint32_t count, const uint8_t encSeed[32], CiphertextStore &out,
+                                      const uint64_t *valuesColMajor) {
+    uint8_t key[32] = {1};                   // core/utils.go:55-56: seed = LE64(1) followed by zeros
+    check(lmn_encrypt_columns(ctx_, valuesColMajor, valuesColMajor ? nullptr : key, rows, cols, firstCol, count, encSeed, out.handle()));
+}
+inline void ServerBFV::EncryptZero(const uint8_t encSeed[32], CiphertextStore &out, uint32_t index, uint32_t streamId) {
+    check(lmn_encrypt_zero(ctx_, encSeed, streamId, out.handle(), index));
+}
+
+// fhe.ClientBFV as far as EncryptedProof.Decrypt uses it (fhe/bfv.go:60-106, fhe/ligero.go:381-502, 577-636): Decrypt + Decode on the device
+class ClientBFV : public ServerBFV {
+  public:
+    ClientBFV(const PrimeField &ptField, const Parameters &params, const uint64_t *sk, int device = 0) : ServerBFV(ptField, params, device) {
+        LoadPlaintextRing();
+        check(lmn_load_secret_key(ctx(), sk));      // [k][N] = sk.Value.Q, NTT + Montgomery
+    }
+    // the first nValues slots of store[first .. first + count): [count][nValues]
+    std::vector<uint64_t> DecryptDecode(const CiphertextStore &s, uint32_t nValues, uint32_t first = 0, uint32_t count = 0) {
+        if (!count) count = s.size() - first;
+        std::vector<uint64_t> out((size_t)count * nValues);
+        check(lmn_decrypt_decode(ctx(), s.handle(), first, count, s.Scale, nValues, out.data()));
+        return out;
+    }
 };
 
 inline CiphertextStore::CiphertextStore(ServerBFV &be, uint32_t count, int level)

@@ -347,6 +347,11 @@ __global__ void __launch_bounds__(CHAIN_THREADS, LMN_CHAIN_MINB) k_rs_chain(cons
     const int n = blockIdx.x * CHAIN_THREADS + threadIdx.x;
     const u64 *raw = J.acc + (size_t)job * J.acc_words + (((size_t)c * (from + 1)) << LOGN) + n;
     u64 *out = J.mu + (size_t)job * J.mu_words + (((size_t)c * (to + 1)) << LOGN) + n;
+    // the S raw values of limb i - 1 are requested while limb i is processed: with two warps per scheduler (the dropped limbs' residues
+    // fill the shared memory) nothing else hides a global load (ncu r2d: long_scoreboard was the top stall, 1.3 cycles per issue)
+    u64 nx[S];
+#pragma unroll
+    for (int r = 0; r < S; r++) nx[r] = ld_pin(raw + ((size_t)from << LOGN) + (size_t)r * M);
 #pragma unroll 1
     for (int i = from; i >= 0; i--) {
         const ModDev mi = mods[i];
@@ -354,7 +359,11 @@ __global__ void __launch_bounds__(CHAIN_THREADS, LMN_CHAIN_MINB) k_rs_chain(cons
         const FwdMod fm = {q, 0 - q, mi.q3, (unsigned)mi.pad[0]};
         u64 v[S];
 #pragma unroll
-        for (int r = 0; r < S; r++) v[r] = raw[((size_t)i << LOGN) + (size_t)r * M];
+        for (int r = 0; r < S; r++) v[r] = nx[r];
+        if (i > 0) {
+#pragma unroll
+            for (int r = 0; r < S; r++) nx[r] = ld_pin(raw + ((size_t)(i - 1) << LOGN) + (size_t)r * M);
+        }
         couple_inv<S>(v, tw_inv + ((size_t)i << LOGN), fm);
 #pragma unroll
         for (int r = 0; r < S; r++) v[r] = mul_shoup(v[r], mi.ninv, mi.ninvs, q);

@@ -61,6 +61,7 @@ int main(int argc, char **argv) {
     params.Q.resize(k); params.P.resize(np); params.PsiQ.resize(k); params.PsiP.resize(np);
     orc_params_moduli(P, params.Q.data(), params.P.data());
     orc_params_psi(P, params.PsiQ.data(), params.PsiP.data());
+    params.PsiT = orc_params_psi_t(P);
     try {
         fhe::ServerBFV server(field, params, 0);
         for (int i = 0; i < ngal; i++) server.LoadGaloisKey(galEls[i], evks[i].data());
@@ -166,6 +167,39 @@ int main(int argc, char **argv) {
             bool oob = false;
             try { comm.Tree->GetMerklePath((uint32_t)n); } catch (const Error &) { oob = true; }
             REQUIRE(oob, "GetMerklePath out of bounds must fail");
+        }
+        // the stages either side: device encoder bit-exact vs the oracle's, device-encrypted columns decrypt (oracle
+        // client) to the witness, device decrypt + decode == the oracle's on the prover's level-1 outputs
+        {
+            auto mform = [](u64 x, u64 q) { return (u64)(((unsigned __int128)x << 64) % q); };
+            std::vector<u64> pkm(ctw), skm((size_t)k * N), sn(N);
+            for (int c = 0; c < 2; c++) for (int i = 0; i < k; i++) for (int j = 0; j < N; j++)
+                pkm[((size_t)c * k + i) * N + j] = mform(pk[((size_t)c * k + i) * N + j], params.Q[i]);
+            for (int i = 0; i < k; i++) {
+                for (int j = 0; j < N; j++) sn[j] = sk[j] >= 0 ? (u64)sk[j] : params.Q[i] - (u64)(-sk[j]);
+                orc_ntt_limb(P, i, sn.data());
+                for (int j = 0; j < N; j++) skm[(size_t)i * N + j] = mform(sn[j], params.Q[i]);
+            }
+            fhe::ClientBFV client(field, params, skm.data(), 0);
+            client.LoadPublicKey(pkm.data());
+            REQUIRE(client.Encode(r) == rpt && client.Encode(b) == bpt, "device bgv.Encoder.Encode differs from the oracle");
+            uint8_t seed32[32]; for (int i = 0; i < 32; i++) seed32[i] = (uint8_t)i;
+            fhe::CiphertextStore encd(client, cols);
+            client.EncryptColumns((uint32_t)rows, (uint32_t)cols, 0, (uint32_t)cols, seed32, encd);
+            std::vector<u64> ec = encd.Download();
+            for (int j = 0; j < cols; j++) {
+                orc_decrypt_decode(P, sk.data(), ec.data() + ctw * j, k - 1, 1, dec.data());
+                for (int i = 0; i < rows; i++) REQUIRE(dec[i] == M[(size_t)i * cols + j], "device-encrypted column %d does not decrypt to the witness", j);
+            }
+            std::vector<u64> all = client.DecryptDecode(encd, (uint32_t)rows);
+            for (int j = 0; j < cols; j++) for (int i = 0; i < rows; i++) REQUIRE(all[(size_t)j * rows + i] == M[(size_t)i * cols + j], "device decrypt of column %d", j);
+            fhe::CiphertextStore l1(client, cols, 1);
+            l1.Upload(matR.data(), 0, cols); l1.Scale = proof.MatR->Scale;
+            std::vector<u64> s0 = client.DecryptDecode(l1, 1);
+            for (int j = 0; j < cols; j++) {
+                orc_decrypt_decode(P, sk.data(), matR.data() + l1w * j, 1, proof.MatR->Scale, dec.data());
+                REQUIRE(s0[j] == dec[0], "device decrypt of MatR[%d] differs from the oracle", j);
+            }
         }
         // error behaviour: missing key / bad shapes raise, they do not abort
         fhe::ServerBFV bare(field, params, 0);

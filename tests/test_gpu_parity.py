@@ -557,3 +557,29 @@ def test_ring_switch_key_with_base2_digits_is_rejected():
         fhe.RingSwitchServer(be, good[:1], 6)
     fhe.RingSwitchServer(be, good, 6)
     be.Close()
+
+
+def test_merkle_maximum_leaf_count():
+    """65536 leaves = the largest codeword length lmn_plan_create admits: the leaf serialiser folds the leaf index into grid.x (a
+    grid.y of 65536 does not launch), the SHA-256 producer / consumer pairs cover 2048 CTAs; root and sampled paths against hashlib."""
+    import hashlib
+    from lumenos_b200 import fhe
+    S = scenario(6, 32, 16, 3)
+    be = S.backend()
+    n = 65536
+    rng = np.random.default_rng(9)
+    cts = rng.integers(0, 2**55, size=(n, 2, 2, 64), dtype=np.uint64)
+    leaves = be.NewStore(n, 1).upload(cts)
+    lf = fhe.LeafFormat.with_prefixes(b"\x01abc", 1, 64)
+    t = fhe.MerkleTree(be, leaves, lf)
+    le = lambda a: a.astype("<u8").tobytes()  # noqa: E731
+    buf = lambda j: lf.header + b"".join(lf.polyHeader + b"".join(lf.limbHeader + le(cts[j, p, l]) for l in range(2)) for p in range(2))  # noqa: E731
+    lv = [hashlib.sha256(buf(j)).digest() for j in range(n)]
+    for j in (0, 1, 4097, n - 1):
+        assert t.LeafHash(j) == lv[j]
+    while len(lv) > 1:
+        lv = [hashlib.sha256(lv[i] + lv[i + 1]).digest() for i in range(0, len(lv), 2)]
+    assert t.MerkleRoot() == lv[0]
+    for j in (0, 12345, n - 1):
+        assert fhe.VerifyMerklePath(buf(j), t.GetMerklePath(j), t.MerkleRoot(), j)
+    be.Close()

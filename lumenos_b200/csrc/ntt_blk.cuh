@@ -122,7 +122,9 @@ __device__ __forceinline__ void ntt2048_fwd(u64 (&a)[8], u64 *s, const ulonglong
       r8_fwd_f(a, [&](int t, int b) { return stw[((8 + i) << t) + b]; }, m);               // levels 3-5
 #pragma unroll
       for (int r = 0; r < 8; r++) s[PAD(i * 256 + j + 32 * r)] = a[r]; }
-    __syncthreads();
+    // from here on a warp only touches its own 256-point segment [256 w, 256 w + 255] (levels 3-5 wrote it, levels 6-8 and 9-10 read and
+    // write inside it), so the two remaining exchanges need a warp barrier, not a CTA barrier
+    __syncwarp();
     { const unsigned i = u >> 2, j = u & 3;
 #pragma unroll
       for (int r = 0; r < 8; r++) a[r] = s[PAD(i * 32 + j + 4 * r)];
@@ -130,7 +132,7 @@ __device__ __forceinline__ void ntt2048_fwd(u64 (&a)[8], u64 *s, const ulonglong
       r8_fwd_f(a, [&](int t, int b) { return stw[((64 + i) << t) + b]; }, m);              // levels 6-8
 #pragma unroll
       for (int r = 0; r < 8; r++) s[PAD(i * 32 + j + 4 * r)] = a[r]; }
-    __syncthreads();
+    __syncwarp();
 #pragma unroll
     for (int r = 0; r < 8; r++) a[r] = s[PAD(8 * u + r)];
 #pragma unroll
@@ -193,14 +195,14 @@ __device__ __forceinline__ void ntt2048_inv(u64 (&a)[8], u64 *s, const ulonglong
     before_store();   // runs after the first register stage and before the first store to `s`
 #pragma unroll
     for (int r = 0; r < 8; r++) s[PAD(8 * u + r)] = a[r];
-    __syncthreads();
+    __syncwarp();      // levels 10-6 stay inside the warp's own 256-point segment: warp barriers; the CTA barrier comes before levels 2-0
     { const unsigned i = u >> 2, j = u & 3;
 #pragma unroll
       for (int r = 0; r < 8; r++) a[r] = s[PAD(i * 32 + j + 4 * r)];
       r8_inv_f(a, [&](int t, int b) { return stw[((64 + i) << t) + b]; }, m, q4);           // levels 8-6
 #pragma unroll
       for (int r = 0; r < 8; r++) s[PAD(i * 32 + j + 4 * r)] = a[r]; }
-    __syncthreads();
+    __syncwarp();
     { const unsigned i = u >> 5, j = u & 31;
 #pragma unroll
       for (int r = 0; r < 8; r++) a[r] = s[PAD(i * 256 + j + 32 * r)];

@@ -32,12 +32,12 @@ sys.path.insert(0, ROOT)
 CONFIGS = {  # rows, cols, logN  (scripts/benchmark_server.sh:34-39, README.md:59-61)
     "A": (2048, 1024, 12), "B": (4096, 2048, 12), "C": (8192, 4096, 13), "D": (16384, 4096, 14),
 }
-NCU_MAC_TRAFFIC_PER_JOB_D = (3.611e9 + 0.924e9) / 256   # bytes per job, profiles/r1d_top_kernels.csv (r1j: 10.49 GB per 592-job launch, the same per job)
+NCU_MAC_TRAFFIC_PER_JOB_D = (3.626e9 + 0.927e9) / 256   # bytes per job: dram__bytes_read + write of one 256-job launch of k_mac_rd<8>, profiles/r2c_mac_kernel.csv
 NCU_ENCODE_TRAFFIC_D = 92.6e9                           # both passes, profiles/r1k_encode_kernels.csv
-# sm__pipe_fmaheavy_cycles_active (% of peak) of each hot kernel class from the committed ncu captures (profiles/r1j_top_kernels.csv,
-# r1k_commit_kernels.csv): the hardware's own reading of how busy the multiplier pipe is, next to the modelled fractions below
-NCU_FMAHEAVY = {"k_mac": 66.0, "k_modup": 76.0, "k_down_pre": 79.0, "k_intt_c1": 65.0, "k_pintt": 65.0, "k_down": 51.0, "k_rs_pre": 57.0,
-                "k_rs_intt": 65.0}
+# sm__pipe_fmaheavy_cycles_active (% of peak) of each hot kernel class from the committed round-2 ncu captures (profiles/r2c_mac_kernel.csv,
+# r2c_top_kernels.csv, r2d_other_kernels.csv): the hardware's own reading of how busy the multiplier pipe is, next to the modelled fractions
+NCU_FMAHEAVY = {"k_mac": 66.4, "k_modup": 76.1, "k_down_pre": 78.7, "k_intt_c1": 64.9, "k_pintt": 62.1, "k_down": 51.5, "k_rs_pre": 56.7,
+                "k_rs_intt": 64.9}
 PUBLISHED_COMMIT_S = {"A": 1.03, "B": 2.04, "C": 9.17, "D": 18.79}  # "Commit eval": leaf rescale + Merkle (BASELINE.md:23)
 PUBLISHED_S = {"A": 14.77, "B": 36.80, "C": 179.93, "D": 397.85}  # Encode + Prove eval, m7i.8xlarge 32 vCPU
 RHO_INV, SECURITY_BITS = 2, 128
@@ -210,7 +210,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--config", default="D", choices=list(CONFIGS))
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=592, help="column-vector jobs per launch; multiples of 37 make every grid a whole number of waves on 148 SMs")
+    ap.add_argument("--batch", type=int, default=1184, help="column-vector jobs per launch; multiples of 37 make every grid a whole number of waves on 148 SMs (measured at D: 296 -> 2.976 s per step, 592 -> 2.957, 1184 -> 2.942, 2368 -> 2.939)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-commit", action="store_true", help="skip the Commit Merkle span (reported beside the headline)")
     ap.add_argument("--no-cpu", action="store_true")

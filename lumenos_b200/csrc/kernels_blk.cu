@@ -519,7 +519,7 @@ __global__ void __launch_bounds__(RA_THREADS, LMN_BLKFWD_MINB) k_blk_fwd(const M
 // jobs per CTA: as many as keep at least four waves of CTAs in flight (the twiddle table is filled once per CTA)
 static int pick_jb(int ctas_per_job, int jobs) {
     const int want = 4 * 148 * 3;
-    static const int jmax = getenv("LMN_BLK_JB") ? atoi(getenv("LMN_BLK_JB")) : 4;   // tuning knob
+    static const int jmax = getenv("LMN_BLK_JB") ? atoi(getenv("LMN_BLK_JB")) : 16;   // tuning knob (config D, 1184 jobs: 4 -> 454 ms of k_down per step, 16 -> 450)
     for (int jb = jmax; jb > 1; jb >>= 1)
         if ((long)ctas_per_job * ((jobs + jb - 1) / jb) >= want) return jb;
     return 1;

@@ -164,7 +164,11 @@ void launch_mac_blk(const Launch &L, const DeviceTables &T, const KsConsts *Cd, 
     const int SB = blk_blocks(T.logn);
     static const int jbe = getenv("LMN_MAC_JB") ? atoi(getenv("LMN_MAC_JB")) : 0;
     const int ctas = (Ch.nq + Ch.np) * SB;
-    int jb = jbe > 0 ? jbe : (ctas * ((J.jobs + 1) / 2) >= 8 * 148 * 2 ? 2 : 1);
+    // jobs per CTA: the twiddle table and the pipeline start-up are paid once per CTA; as many as leave eight waves of CTAs
+    // (measured at config D, 1184 jobs per launch: 1 -> 1296 ms per step, 2 -> 1270, 4 -> 1247, 8 -> 1243)
+    int jb = 1;
+    if (jbe > 0) jb = jbe;
+    else for (int c = 8; c > 1; c >>= 1) if ((long)ctas * ((J.jobs + c - 1) / c) >= 8 * 148 * 2) { jb = c; break; }
     const dim3 g(ctas, (J.jobs + jb - 1) / jb);
     if (SB == 8) k_mac_rd<8><<<g, RA_THREADS, MAC_RD_SMEM, L.stream>>>(T.mods, T.twb_fwd, Cd, J, evk, jb);
     else if (SB == 4) k_mac_rd<4><<<g, RA_THREADS, MAC_RD_SMEM, L.stream>>>(T.mods, T.twb_fwd, Cd, J, evk, jb);

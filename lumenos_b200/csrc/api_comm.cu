@@ -260,7 +260,9 @@ int lmn_commit_leaves_from_slices(lmn_ctx *c, const void *enc_slice_dev, uint32_
     const int lout = std::min(1, c->k - 1);
     if ((int)leaves->level != lout || leaves->n != (uint32_t)c->n || leaves->count < per) return fail(LMN_ERR_INVALID, "the leaves store holds n / world level-1 ciphertexts");
     const size_t out_words = 2 * (size_t)(lout + 1) * c->n;
-    return slices_to_blocks(c, (const u64 *)enc_slice_dev, n, c->batch, nullptr,
+    // at least four chunks, so that the rescale of one overlaps the all-to-all of the next even when the whole block fits one batch
+    const uint32_t chunk = std::max(1u, std::min(c->batch, (per + 3) / 4));
+    return slices_to_blocks(c, (const u64 *)enc_slice_dev, n, chunk, nullptr,
                             [&](u64 *w, uint32_t c0, uint32_t cnt) { return rescale_consecutive(c, w, cnt, leaves->d + (size_t)c0 * out_words); });
 }
 

@@ -209,3 +209,50 @@ def test_config_C_D_whole_protocol_on_real_encryptions(rows, cols, logN, k, p1):
     assert np.array_equal(qcols[3], qcols[7])
     assert np.array_equal(qcols[0], P.rescale_to_level1(prover.EncodedMatrix.download(int(idx[0]), 1)[0])[0])
     be.Close()
+
+
+def test_client_entry_points_fail_loudly():
+    """error behaviour of the new entry points: missing ring / keys / communicator and bad shapes return a status, never abort"""
+    import ctypes as C
+    from lumenos_b200 import _capi, fhe
+    S = Scenario(6, 32, 8, 3)
+    be = S.backend()
+    lib = _capi.lib()
+    st = be.NewStore(8)
+    with pytest.raises(fhe.LumenosError, match="plaintext ring not loaded"):
+        check_rc = lib.lmn_encrypt_columns(be.ctx, None, fhe.REFERENCE_WITNESS_KEY, 32, 8, 0, 8, SEED, st.h)
+        _capi.check(check_rc)
+    be.LoadPlaintextRing()
+    with pytest.raises(fhe.LumenosError, match="public key not loaded"):
+        be.EncryptColumns(32, 8, SEED, out=st)
+    with pytest.raises(fhe.LumenosError, match="secret key not loaded"):
+        out = np.empty((8, 4), np.uint64)
+        _capi.check(lib.lmn_decrypt_decode(be.ctx, st.h, 0, 8, 1, 4, out.ctypes.data_as(C.c_void_p)))
+    be.LoadPublicKey(pk_as_lattigo(S.P, S.pk))
+    with pytest.raises(fhe.LumenosError, match="column range"):
+        be.EncryptColumns(32, 8, SEED, firstCol=4, count=8, out=st)
+    with pytest.raises(fhe.LumenosError, match="between 1 and N"):
+        be.EncryptColumns(65, 8, SEED, out=st)
+    with pytest.raises(fhe.LumenosError, match="max-level"):
+        be.EncryptColumns(32, 8, SEED, out=be.NewStore(8, 1))
+    with pytest.raises(fhe.LumenosError, match="primitive 2N-th root"):
+        be.LoadPlaintextRing(12345)
+    with pytest.raises(fhe.LumenosError, match="no communicator"):
+        _capi.check(lib.lmn_exchange_encoded(be.ctx, C.c_void_p(st.device_ptr), 8, st.h))
+    with pytest.raises(fhe.LumenosError, match="power of two"):
+        _capi.check(lib.lmn_comm_init(be.ctx, bytes(128), 0, 3))
+    with pytest.raises(fhe.LumenosError, match="Scale must be invertible"):
+        out = np.empty((8, 4), np.uint64)
+        _capi.check(lib.lmn_decrypt_decode(be.ctx, st.h, 0, 8, 0, 4, out.ctypes.data_as(C.c_void_p)))
+    # a single-rank communicator works and the exchanges degenerate to copies
+    from lumenos_b200 import sharding
+    import torch
+    sharding.init_comm(be, 0, 1)
+    be.EncryptColumns(32, 8, SEED, out=st)
+    t = torch.empty((8, 2, 3, 64), dtype=torch.int64, device="cuda")
+    sharding.to_slices(be, st, 8, t)
+    be.Synchronize()
+    assert np.array_equal(t.cpu().numpy().astype(np.uint64), st.download())
+    blk = sharding.exchange_encoded(be, t)
+    assert np.array_equal(blk.download(), st.download())
+    be.Close()

@@ -163,25 +163,29 @@ __global__ void __launch_bounds__(256) k_ct_stream(const LeafFormat F, const u64
 constexpr int SHA_DEPTH = 4;
 __device__ __forceinline__ void named_sync(int id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
 __device__ __forceinline__ void named_arrive(int id) { asm volatile("bar.arrive %0, 64;" ::"r"(id) : "memory"); }
-__global__ void __launch_bounds__(64) k_sha256_leaves(const uint4 *__restrict__ ser, uint32_t blocks_per_leaf, uint32_t n_leaves,
+constexpr int SHA_PRODUCERS = 1;     // producer warps per consumer warp (2, taking alternate blocks: 10.2 ms against 8.3 - the consumer is the limit: 960 instructions per block at one issue per two cycles per warp)
+__global__ void __launch_bounds__(32 * (1 + SHA_PRODUCERS)) k_sha256_leaves(const uint4 *__restrict__ ser, uint32_t blocks_per_leaf, uint32_t n_leaves,
                                                       uint32_t *__restrict__ hashes) {
     __shared__ uint32_t ring[SHA_DEPTH][64][32];      // [slot][round][lane] = W + K
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t leaf_id = blockIdx.x * 32 + lane;
     const uint32_t leaf = leaf_id < n_leaves ? leaf_id : n_leaves - 1;     // idle lanes shadow the last leaf (barriers count whole warps)
-    if (warp == 1) {
+    if (warp >= 1) {
         const uint4 *p = ser + (size_t)leaf * blocks_per_leaf * 4;
+        const uint32_t b0 = (uint32_t)(warp - 1);
         uint4 nx[4];
+        if (b0 < blocks_per_leaf) {
 #pragma unroll
-        for (int j = 0; j < 4; j++) nx[j] = __ldcs(p + j);
+            for (int j = 0; j < 4; j++) nx[j] = __ldcs(p + 4 * (size_t)b0 + j);
+        }
 #pragma unroll 1
-        for (uint32_t b = 0; b < blocks_per_leaf; b++) {
+        for (uint32_t b = b0; b < blocks_per_leaf; b += SHA_PRODUCERS) {
             uint32_t w[16];
 #pragma unroll
             for (int j = 0; j < 4; j++) { w[4 * j] = bswap32(nx[j].x); w[4 * j + 1] = bswap32(nx[j].y); w[4 * j + 2] = bswap32(nx[j].z); w[4 * j + 3] = bswap32(nx[j].w); }
-            if (b + 1 < blocks_per_leaf) {
+            if (b + SHA_PRODUCERS < blocks_per_leaf) {
 #pragma unroll
-                for (int j = 0; j < 4; j++) nx[j] = __ldcs(p + 4 * (size_t)(b + 1) + j);
+                for (int j = 0; j < 4; j++) nx[j] = __ldcs(p + 4 * (size_t)(b + SHA_PRODUCERS) + j);
             }
             const int slot = (int)(b & (SHA_DEPTH - 1));
             if (b >= SHA_DEPTH) named_sync(1 + SHA_DEPTH + slot);           // the consumer has finished with this slot
@@ -207,13 +211,16 @@ __global__ void __launch_bounds__(64) k_sha256_leaves(const uint4 *__restrict__ 
             uint32_t a = st[0], bb = st[1], c = st[2], d = st[3], e = st[4], f = st[5], g = st[6], h = st[7];
 #pragma unroll
             for (int i = 0; i < 64; i++) {
-                const uint32_t x = h + ring[slot][i][lane];               // off the chain: h is three rounds old
+                // the chain through e is SHF -> LOP3 -> IADD3 per round: h + W + K and d are three rounds old, so x and y are off it
+                const uint32_t x = h + ring[slot][i][lane];
+                const uint32_t y = x + d;
                 const uint32_t S1 = rotr(e, 6) ^ rotr(e, 11) ^ rotr(e, 25);
                 const uint32_t ch = (e & f) ^ (~e & g);
+                const uint32_t en = y + S1 + ch;                          // = d + t1
                 const uint32_t t1 = x + S1 + ch;
                 const uint32_t S0 = rotr(a, 2) ^ rotr(a, 13) ^ rotr(a, 22);
                 const uint32_t mj = (a & bb) ^ (a & c) ^ (bb & c);
-                h = g; g = f; f = e; e = d + t1; d = c; c = bb; bb = a; a = t1 + S0 + mj;
+                h = g; g = f; f = e; e = en; d = c; c = bb; bb = a; a = t1 + S0 + mj;
             }
             if (b + SHA_DEPTH < blocks_per_leaf) named_arrive(1 + SHA_DEPTH + slot);   // slot free (only while the producer still waits for it)
             st[0] += a; st[1] += bb; st[2] += c; st[3] += d; st[4] += e; st[5] += f; st[6] += g; st[7] += h;
@@ -258,7 +265,7 @@ void launch_ct_stream(const Launch &L, const LeafFormat &F, const u64 *cts, uint
 }
 void launch_sha256_leaves(const Launch &L, const u64 *ser, uint32_t padded_len, uint32_t n_leaves, uint32_t *hashes) {
     LaunchScope scope(L, KID_SHA_LEAF);
-    k_sha256_leaves<<<(n_leaves + 31) / 32, 64, 0, L.stream>>>(reinterpret_cast<const uint4 *>(ser), padded_len / 64, n_leaves, hashes);
+    k_sha256_leaves<<<(n_leaves + 31) / 32, 32 * (1 + SHA_PRODUCERS), 0, L.stream>>>(reinterpret_cast<const uint4 *>(ser), padded_len / 64, n_leaves, hashes);
 }
 void launch_sha256_nodes(const Launch &L, const uint32_t *children, uint32_t n_children, uint32_t *parents) {
     LaunchScope scope(L, KID_SHA_NODE);

@@ -642,6 +642,12 @@ class LigeroProver:
         queryIndices: sampleQueryIndices(transcript, Queries, cols*rhoInv) (ligero.go:266, 638-644)."""
         md = self.Committer
         lib = _capi.lib()
+        # r / b given as slot values (what transcript.SampleUints and the powers of z^cols produce, ligero.go:202-216) are encoded on
+        # the device exactly as backend.Encode does (ligero.go:204-205, 218-219); plaintext limbs [k][N] pass through
+        if np.ndim(rPt) == 1:
+            rPt = backend.Encode(rPt)
+        if np.ndim(bPt) == 1:
+            bPt = backend.Encode(bPt)
         lout = min(1, backend.params.MaxLevel())
         matR = backend.NewStore(self.Matrix.count, lout)
         matZ = backend.NewStore(self.Matrix.count, lout)

@@ -104,7 +104,7 @@ def test_encrypted_matrix_runs_the_whole_protocol():
     idx = (np.random.default_rng(5).integers(0, 2**62, size=committer.Queries) % (2 * cols)).astype(np.uint32)
     rpt, bpt = be.Encode(S.r), be.Encode(S.b)                      # Prove's plaintexts encoded on the device
     assert np.array_equal(rpt, S.rpt) and np.array_equal(bpt, S.bpt)
-    proof = prover.Prove(rpt, bpt, idx, be)
+    proof = prover.Prove(S.r, S.b, idx, be)                        # slot values: encoded on the device inside Prove
     params = fhe.BGVParameters(logN, P.q, P.p, P.t, P.psi_q, P.psi_p, P.psi_t)
     client = fhe.ClientBFV(fhe.PrimeField(P.t, S.roots), params, sk_as_lattigo(P, S.sk))
     dec = proof.Decrypt(client)

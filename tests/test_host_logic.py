@@ -175,3 +175,44 @@ def test_placeholder_framing_reproduces_every_logged_size():
     md0 = [o - (1 + 8 + 2 * 8 + 2 * 8) for o in o0s]
     both = sorted(set(md1) & set(md0))
     assert (both[0], both[-1]) == (268, 310) and fhe.LeafFormat.PLACEHOLDER_METADATA_LEN in both
+
+
+# ---- bench.py's work model and reference arm (no GPU) ----
+def _bench():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("lmn_bench", os.path.join(ROOT, "bench.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m
+
+
+@pytest.mark.parametrize("cfg,k,ks_ntts,rescale_ntts,total_bfly", [("A", 10, 84, 104, 5.17e10), ("B", 11, 104, 126, 1.38e11), ("C", 12, 112, 150, 7.0e11),
+                                                                   ("D", 12, 112, 150, 1.61e12)])
+def test_bench_work_model_reproduces_survey_counts(cfg, k, ks_ntts, rescale_ntts, total_bfly):
+    """the per-kernel-class butterfly counts behind bench.py's integer rooflines add up to SURVEY App. C: limb transforms per key
+    switch, and NTT butterflies of both inner products at every benchmark shape (the chained rescale does fewer transforms than the
+    step-by-step count of App. C - 2 (k + 2) instead of 2 sum (l + 1) - so it is compared separately)"""
+    B = _bench()
+    rows, cols, logN = B.CONFIGS[cfg]
+    N = 1 << logN
+    w = B.work_per_job(k, 2, logN)
+    per_limb = N // 2 * logN
+    ks = sum(w[c]["butterflies"] for c in ("k_intt_c1", "k_modup", "k_mac", "k_pintt", "k_down_pre", "k_down"))
+    assert ks == ks_ntts * per_limb                                  # SURVEY App. C "ks limb-NTTs"
+    chain = sum(w[c]["butterflies"] for c in ("k_rs_intt", "k_rs_pre", "k_rs_apply"))
+    assert chain == 2 * (k + 2) * per_limb                           # DESIGN section 3: 2k inverse + 4 forward transforms per ciphertext
+    n_ks = (logN if rows == N else rows.bit_length() - 1)            # log2(rows) rotations, the row swap included when rows == N
+    survey = 2 * cols * (n_ks * ks_ntts + rescale_ntts) * per_limb   # both vectors, step-by-step rescale as App. C counts it
+    assert abs(survey - total_bfly) / total_bfly < 0.01
+    ours = 2 * cols * (n_ks * ks + chain)
+    assert ours < survey and ours > 0.9 * survey
+
+
+def test_reference_arm_sample_runs_on_cpu():
+    """`bench.py --impl reference` times the oracle on a bounded sample: a tiny sample of config A must run here and scale to a
+    plausible full-shape figure (the published 32-vCPU number for A is 14.77 s; one to a few hundred seconds on a handful of cores)"""
+    B = _bench()
+    total, desc, parts = B.cpu_reference_sample("A", 2, enc_lanes=64, ip_cols=2, q_cols=2)
+    assert set(parts) == {"encode_s_1core", "inner_product_s", "query_s_parallel"} and all(v > 0 for v in parts.values())
+    assert 5.0 < total < 5000.0 and "2 of 2048 column-vectors" in desc
+    assert B.workload_string("D") == "D: 16384x4096 LogN=14 k=12 encode + prove eval (inner products r,b + 309 query columns)"

@@ -786,7 +786,10 @@ static int inner_product2_impl(lmn_ctx *c, const lmn_store *matrix, const uint64
     cudaSetDevice(c->device);
     const size_t N = c->n, k = c->k;
     const int nvec = pt_b ? 2 : 1;
-    const uint32_t bc = std::max(1u, c->batch / nvec);
+    uint32_t bc = std::max(1u, c->batch / nvec);
+    // results that also go home are copied batch by batch behind the next batch's kernels: keep at least four batches (of at least 64
+    // columns) so that a rank whose whole block fits one launch still hides three quarters of its device-to-host copy
+    if (host_r) bc = std::min(bc, std::max(64u, (matrix->count + 3) / 4));
     if (int rc = ensure_workspace(c, std::min(bc, matrix->count) * nvec)) return rc;
     Launch L = c->L();
     // plaintexts: upload, fold T and the Montgomery factor (tensorStandard's T * pt)

@@ -257,7 +257,7 @@ def main():
     beta = (k + len(p) - 1) // len(p)
 
     # Galois keys: random canonical residues in the evk layout [beta][2][k+np][N]
-    gal_els, evks_host = params.GaloisElementsForInnerSum(1, rows), []
+    gal_els, evks_host = [g for g in params.GaloisElementsForInnerSum(1, rows) if g != 1], []      # identity elements carry no key on the device
     for g in gal_els:
         evk = np.empty((beta, 2, k + len(p), N), np.uint64)
         for i, m in enumerate(mods):

@@ -75,10 +75,12 @@ struct Parameters {
         return g;
     }
     std::vector<uint64_t> GaloisElementsForInnerSum(int batch, int n) const {
+        // lattigo: rotations batch * {2^i < n} and batch * n (identity elements included: it generates keys for them and the library
+        // ignores them), plus the row swap when n * batch > N / 2
         std::vector<uint64_t> g;
-        int m = std::min(n * batch, N() / 2);
-        for (int s = batch; s < m; s <<= 1) g.push_back(GaloisElement(s));
-        if (n * batch == N()) g.push_back(2ull * N() - 1);
+        for (int s = 1; s < n; s <<= 1) g.push_back(GaloisElement(s * batch));
+        g.push_back(GaloisElement(n * batch));
+        if (n * batch > N() / 2) g.push_back(2ull * N() - 1);
         return g;
     }
 };

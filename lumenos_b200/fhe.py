@@ -68,13 +68,16 @@ class BGVParameters:
         return pow(5, k % (self.N // 2), 2 * self.N)
 
     def GaloisElementsForInnerSum(self, batch, n):
-        """lattigo bgv.Parameters.GaloisElementsForInnerSum(1, n) (ref: fhe/ligero_test.go:53)"""
-        m = min(n * batch, self.N // 2)
-        g, s = [], batch
-        while s < m:
-            g.append(self.GaloisElement(s))
+        """lattigo bgv.Parameters.GaloisElementsForInnerSum(batch, n) (ref: fhe/ligero_test.go:53, cmd/client/main.go:81) for power-of-two n:
+        the rotations batch * {2^i : 2^i < n} and batch * n, plus the row swap when n * batch > N/2.  Rotations by multiples of N/2 are
+        the identity (Galois element 1): Lattigo generates keys for them all the same - the logged key-blob sizes count them
+        (tests/test_host_logic.py::test_key_blob_sizes_pin_the_key_shapes_and_the_galois_set) - and the library ignores them."""
+        g, s = [], 1
+        while s < n:
+            g.append(self.GaloisElement(s * batch))
             s <<= 1
-        if n * batch == self.N:
+        g.append(self.GaloisElement(n * batch))
+        if n * batch > self.N // 2:
             g.append(2 * self.N - 1)
         return g
 

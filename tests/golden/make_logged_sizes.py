@@ -21,5 +21,13 @@ for kind in ("baseline", "experimental"):
             if m:
                 rec["queries"] = int(m.group(1))
         out.append(rec)
+# "Marshaled keys length" of the client logs (cmd/client/main.go:136): humanize.Bytes of the JSON body that carries pk, rlk, the Galois keys of
+# GaloisElementsForInnerSum(1, rows) and (experimental runs) the ring-switch evk, each as base64 of its MarshalBinary
+for rec in out:
+    f = os.path.join(REF, rec["kind"], "client", os.path.basename(rec["file"]))
+    for line in open(f):
+        m = re.match(r"Marshaled keys length: (.*)$", line.strip())
+        if m:
+            rec["keys"] = m.group(1)
 json.dump(out, open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "logged_sizes.json"), "w"), indent=1)
 print(len(out), "logs")

@@ -216,3 +216,50 @@ def test_reference_arm_sample_runs_on_cpu():
     assert set(parts) == {"encode_s_1core", "inner_product_s", "query_s_parallel"} and all(v > 0 for v in parts.values())
     assert 5.0 < total < 5000.0 and "2 of 2048 column-vectors" in desc
     assert B.workload_string("D") == "D: 16384x4096 LogN=14 k=12 encode + prove eval (inner products r,b + 309 query columns)"
+
+
+def _keys_blob_bytes(rec, galois_keys, beta, ring_switch_evks=0, np_=2, pk_limbs=None, framing=0):
+    """size of the client's JSON key blob (cmd/client/main.go:86-136): pk, rlk, the Galois keys and the optional ring-switch evk, each the
+    base64 of its MarshalBinary; an evaluation key is [beta][2][k + np][N] u64, the public key 2 polynomials over QP"""
+    N = 1 << rec["logN"]
+    k = (rec["cols"] & -rec["cols"]).bit_length() - 1           # GenerateBGVParamsForNTT, fhe/bfv.go:141-158
+    evk = (beta if beta else (k + np_ - 1) // np_) * 2 * (k + np_) * N * 8
+    pk = 2 * (pk_limbs if pk_limbs else k + np_) * N * 8
+    b64 = lambda n: 4 * ((n + 2) // 3)  # noqa: E731
+    return b64(pk) + (1 + galois_keys) * b64(evk) + ring_switch_evks * b64(evk) + framing
+
+
+def test_key_blob_sizes_pin_the_key_shapes_and_the_galois_set():
+    """A second reference-held constraint on the Lattigo half: the client logs print humanize.Bytes of the marshalled keys (8 logs).  They
+    are reproduced exactly by: hybrid evaluation keys of ceil(k / 2) RNS digits over Q and P WITHOUT base-2 sub-digits (so the
+    BaseTwoDecomposition: 13 that fhe/ring_switch.go:47-55 requests has no effect - the ABI's base2_digits == 1), one such key for the ring
+    switch, and the Galois set of bgv GaloisElementsForInnerSum(1, rows): rotations 2^0 .. rows/2 AND rows (identity elements included)
+    plus the row swap when rows > N/2 - i.e. the row-swap step of InnerSum at rows == N is present in the key set.
+    Every alternative reading misses at least one log."""
+    logs = json.load(open(os.path.join(ROOT, "tests", "golden", "logged_sizes.json")))
+    assert len(logs) == 8 and all("keys" in r for r in logs)
+
+    def lattigo_count(rec):
+        N, rows = 1 << rec["logN"], rec["rows"]
+        return (rows.bit_length() - 1) + 1 + (1 if rows > N // 2 else 0)       # {2^i : 2^i < rows} + {rows} (+ row swap)
+
+    def fits(count, beta=0, rs_factor=1, **kw):
+        ok = True
+        for rec in logs:
+            rs = rs_factor if rec["kind"] == "experimental" else 0
+            sizes = {_humanize_bytes(_keys_blob_bytes(rec, count(rec), beta, rs, framing=f, **kw)) for f in (0, 16384, 65536)}
+            ok &= sizes == {rec["keys"]}
+        return ok
+    assert fits(lattigo_count)
+    assert not fits(lambda r: lattigo_count(r) - (1 if r["rows"] > (1 << r["logN"]) // 2 else 0))          # no row-swap key
+    assert not fits(lambda r: lattigo_count(r) - 1)                                                          # no key for the rotation by `rows`
+    assert not fits(lattigo_count, rs_factor=5)                                                              # ring-switch key with ceil(58 / 13) base-2 digits
+    assert not fits(lattigo_count, beta=1) and not fits(lattigo_count, beta=12)                              # other digit counts
+    # the host mirror hands out exactly that set
+    for rec in logs[:4]:
+        N, rows = 1 << rec["logN"], rec["rows"]
+        prm = fhe.BGVParameters(rec["logN"], [1], [1], T, [1], [1])
+        g = prm.GaloisElementsForInnerSum(1, rows)
+        assert len(g) == lattigo_count(rec)
+        assert (2 * N - 1 in g) == (rows > N // 2)
+        assert g.count(1) == (2 if rows == N else 1 if rows == N // 2 else 0)

@@ -90,7 +90,9 @@ def test_galois_elements_for_innersum_match_oracle():
     for logN, rows in [(6, 32), (6, 64), (8, 64), (12, 2048), (12, 4096)]:
         P = O.Params(logN, k=2)
         params = fhe.BGVParameters(logN, P.q, P.p, T, P.psi_q, P.psi_p)
-        assert params.GaloisElementsForInnerSum(1, rows) == P.galois_elements_for_innersum(rows)
+        # the mirror returns Lattigo's full list (identity elements for rotations by multiples of N/2 included, pinned by the logged key-blob
+        # sizes); the oracle lists the keys InnerSum actually uses - the same list without the identity elements
+        assert [g for g in params.GaloisElementsForInnerSum(1, rows) if g != 1] == P.galois_elements_for_innersum(rows)
 
 
 def test_context_creation_without_gpu_reports_error(lib):

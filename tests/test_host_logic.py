@@ -268,3 +268,20 @@ def test_key_blob_sizes_pin_the_key_shapes_and_the_galois_set():
         assert len(g) == lattigo_count(rec)
         assert (2 * N - 1 in g) == (rows > N // 2)
         assert g.count(1) == (2 if rows == N else 1 if rows == N // 2 else 0)
+
+
+def test_header_is_plain_c_and_links_from_c(tmp_path):
+    """cgo compiles include/lumenos_b200.h as C and links the shared library by name: the header must be valid C11 without any C++ and
+    every declared function must resolve at link time from a C translation unit (no GPU call is made)"""
+    import subprocess
+    lb.build()
+    header = open(os.path.join(ROOT, "include", "lumenos_b200.h")).read()
+    names = sorted(set(re.findall(r"\b(lmn_[a-z0-9_]+)\s*\(", header)))
+    src = tmp_path / "abi.c"
+    src.write_text('#include "lumenos_b200.h"\n#include <stdio.h>\ntypedef void (*fn_t)(void);\nint main(void) {\n  fn_t fns[] = {' + ", ".join("(fn_t)" + n for n in names) +
+                   '};\n  printf("%d %d %s\\n", (int)(sizeof(fns) / sizeof(fns[0])), lmn_kernel_count(), lmn_kernel_name(4));\n  return 0;\n}\n')
+    exe = tmp_path / "abi"
+    subprocess.check_call(["gcc", "-std=c11", "-Wall", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe),
+                           "-L", os.path.join(ROOT, "lumenos_b200"), "-llumenos_b200", "-Wl,-rpath," + os.path.join(ROOT, "lumenos_b200")])
+    out = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()
+    assert int(out[0]) == len(names) and int(out[1]) >= 18 and out[2] == "k_mac"

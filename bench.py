@@ -440,7 +440,9 @@ def main():
     pk = C.c_double()
     _capi.check(lib.lmn_bench_int_peak(be.ctx, C.byref(pk)))
     sm_mhz = clocks.get("sm_mhz") or 1965.0
-    fma_bound = 148 * 4 * 32 * sm_mhz * 1e6 / 24.0     # butterflies/s if the fmaheavy pipe did nothing but the butterfly's multiplies
+    # butterflies/s if the multiplier pipe did nothing but one butterfly's multiplies: 5 IMAD.WIDE at 4.4 cycles per warp and sub-partition
+    # + 6 IMAD-class instructions at 2 (profiles/r2c_int_pipe_probe.txt, profiles/sass_summary.txt) = 34 pipe cycles
+    fma_bound = 148 * 4 * 32 * sm_mhz * 1e6 / 34.0
     work = work_per_job(k, np_, logN)
     mac_avg_s = mac_ms / max(1, mac_n) * 1e-3
     jobs_avg = mac_jobs / max(1, mac_n)                 # from the library's own launch accounting (the last batch of a rank is shorter)
@@ -449,7 +451,7 @@ def main():
                 "achieved": mac_bfly / mac_avg_s / 1e9, "peak": pk.value / 1e9, "unit": "Gbutterfly/s", "frac": mac_bfly / mac_avg_s / pk.value,
                 "peak_source": "lmn_bench_int_peak, this run: the product's own 3-product Shoup butterfly (ntt_blk.cuh bfly_ct3), register-resident on all SMs, no loads or barriers",
                 "peak_fmaheavy_only": fma_bound / 1e9,
-                "peak_fmaheavy_only_note": "148 SMs x 4 sub-partitions x 32 lanes x %.0f MHz / 24 fmaheavy pipe-cycles per butterfly (6 wide multiplies of 4 cycles, tools/int_pipe_probe.cu): the butterfly ceiling above is %.0f %% of it because the ALU and issue slots of the same butterfly are not free" % (sm_mhz, 100 * pk.value / fma_bound),
+                "peak_fmaheavy_only_note": "148 SMs x 4 sub-partitions x 32 lanes x %.0f MHz / 34 multiplier-pipe cycles per butterfly (5 IMAD.WIDE of 4.4 cycles + 6 IMAD of 2, measured by tools/int_pipe_probe.cu and counted in the SASS): the butterfly ceiling above is %.0f %% of it because a butterfly also needs about 32 issue slots and 26 ALU cycles" % (sm_mhz, 100 * pk.value / fma_bound),
                 "frac_of_fmaheavy_only": mac_bfly / mac_avg_s / fma_bound,
                 "work_per_launch": {"jobs": jobs_avg, "butterflies_per_job": work["k_mac"]["butterflies"], "gadget_macs_per_job": work["k_mac"]["macs"],
                                     "note": "butterflies = (digit, target modulus) pairs x N/2 x 11 block levels; the gadget MACs and Montgomery reductions (not counted in achieved) are extra integer work of the same kernel"},

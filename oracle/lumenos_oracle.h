@@ -14,7 +14,12 @@
  * (fhe/code_test.go:109-116, fhe/ligero_test.go:164-174).  Ciphertext-bit parity against
  * real Lattigo is "parity unpinned": the reference holds no golden ciphertexts (keys and
  * encryption noise are fresh-random in every reference test) and neither Go nor Lattigo's
- * source exist in this environment.
+ * source exist in this environment (probed on the GPU box too, profiles/r2_go_probe.txt).
+ * Structural facts of the Lattigo half that reference-held data does pin (tests/test_host_logic.py,
+ * fixture tests/golden/logged_sizes.json): the byte length of Ciphertext.WriteTo's framing (the logged
+ * sizes of MatR / MatZ / QueriedCols / proof), the evaluation-key shape [ceil(k/2)][2][k+2][N] without
+ * base-2 sub-digits, one such key for the ring switch, and the Galois set of InnerSum including the row
+ * swap at rows == N (the logged key-blob sizes).  What stays open is listed in DESIGN.md section 5.
  *
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
  * may load this library.  The product (lumenos_b200) never links or calls it.

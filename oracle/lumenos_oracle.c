@@ -1003,7 +1003,7 @@ void orc_keygen_galois(const orc_params *P, const int8_t *sk, u64 galEl, u64 see
     { u64 e = (u64)N - 1, base = galEl & mask; while (e) { if (e & 1) inv = (inv * base) & mask; base = (base * base) & mask; e >>= 1; } }
     uint32_t *idx = malloc(sizeof(uint32_t) * N);
     orc_automorphism_index(P, inv, idx);
-    u64 **so = malloc(sizeof(u64 *) * KP); u64 *tmp = malloc(sizeof(u64) * N);
+    u64 **so = calloc(KP, sizeof(u64 *)); u64 *tmp = malloc(sizeof(u64) * N);
     for (int m = 0; m < KP; m++) {
         so[m] = malloc(sizeof(u64) * N);
         sk_to_ntt(P, m, sk, tmp);
@@ -1019,7 +1019,7 @@ void orc_keygen_ringswitch(const orc_params *P, const int8_t *sk, const int8_t *
     int N = P->N, Ns = 1 << logNs, gap = N / Ns, KP = P->k + P->np;
     int8_t *emb = calloc(N, 1);
     for (int j = 0; j < Ns; j++) emb[(size_t)j * gap] = sk_small[j];
-    u64 **so = malloc(sizeof(u64 *) * KP);
+    u64 **so = calloc(KP, sizeof(u64 *));
     for (int m = 0; m < KP; m++) { so[m] = malloc(sizeof(u64) * N); sk_to_ntt(P, m, emb, so[m]); }
     gen_evk(P, sk, (const u64 *const *)so, seed ^ 0x51ULL, evk);
     for (int m = 0; m < KP; m++) free(so[m]);

@@ -198,6 +198,22 @@ int lmn_merkle_build(lmn_ctx *ctx, const lmn_store *leaves, const lmn_leaf_forma
  * the hashes are gathered in column order and the tree is built from them; lmn_merkle_build == the two calls on one GPU */
 int lmn_leaf_hashes(lmn_ctx *ctx, const lmn_store *leaves, const lmn_leaf_format *fmt, uint8_t *out);
 int lmn_merkle_from_leaf_hashes(lmn_ctx *ctx, const uint8_t *hashes, uint32_t n_leaves, lmn_merkle **out);
+/* No counterpart in the reference: the same tree as lmn_merkle_from_leaf_hashes for hosts that must not allocate while they run -
+ * a prover that has committed all of its HBM up front (stores, workspaces, another pool beside this library), so that a cudaMalloc
+ * in the middle of Commit may fail, or one whose other threads have kernels in flight, which every cudaMalloc / cudaFree would
+ * stall.  The call makes no cudaMalloc / cudaFree / new: the tree's nodes are built in a device array that is part of the library
+ * image (2 MiB per GPU, held until the process exits) and the results are written into the caller's host buffers:
+ *   root_out32          the 32-byte root (== lmn_merkle_root);
+ *   nodes_out, optional every node, 32 bytes each, level by level from the leaf hashes up - level l holds ceil(n_leaves / 2^l)
+ *                       nodes and the last level is the root - so that paths can be read off as lmn_merkle_path does (the sibling
+ *                       of node i is i ^ 1, or i itself when that is past the end of the level); nodes_cap = its size in bytes.
+ * n_leaves above LMN_MERKLE_NOALLOC_MAX_LEAVES is rejected with LMN_ERR_INVALID.  The first call on each GPU also resolves the
+ * array's device address; make it during set-up, before any stream capture begins.  The array is shared by all contexts of the
+ * process and keeps the last call's nodes (every entry a call reads is written by that call first); calls are serialised by a
+ * process-wide lock and return when their results are in host memory, because two that overlapped on the GPU would race. */
+#define LMN_MERKLE_NOALLOC_MAX_LEAVES 32768u
+int lmn_merkle_from_leaf_hashes_noalloc(lmn_ctx *ctx, const uint8_t *hashes, uint32_t n_leaves, uint8_t *root_out32, uint8_t *nodes_out,
+                                        size_t nodes_cap);
 void lmn_merkle_destroy(lmn_merkle *tree);
 uint32_t lmn_merkle_leaf_count(const lmn_merkle *tree);
 uint32_t lmn_merkle_depth(const lmn_merkle *tree);                            /* hashes per path */

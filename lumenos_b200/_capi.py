@@ -94,6 +94,7 @@ SIGNATURES = {
     "lmn_merkle_build": (C.c_int, [vp, vp, C.POINTER(LmnLeafFormat), C.POINTER(vp)]),
     "lmn_leaf_hashes": (C.c_int, [vp, vp, C.POINTER(LmnLeafFormat), vp]),
     "lmn_merkle_from_leaf_hashes": (C.c_int, [vp, vp, C.c_uint32, C.POINTER(vp)]),
+    "lmn_merkle_from_leaf_hashes_noalloc": (C.c_int, [vp, vp, C.c_uint32, vp, vp, C.c_size_t]),
     "lmn_merkle_destroy": (None, [vp]),
     "lmn_merkle_leaf_count": (C.c_uint32, [vp]),
     "lmn_merkle_depth": (C.c_uint32, [vp]),

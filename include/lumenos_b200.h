@@ -79,8 +79,18 @@ int lmn_ctx_set_stream(lmn_ctx *ctx, void *cuda_stream);
 int lmn_ctx_synchronize(lmn_ctx *ctx);
 /* number of kernels launched by this context since creation (bench.py's gpu_launches) */
 uint64_t lmn_ctx_launch_count(const lmn_ctx *ctx);
-/* columns processed together per inner-product / rescale batch (workspace = batch * ~(5k+4) limbs) */
+/* columns processed together per inner-product / rescale batch (workspace = batch * ~(5k+4) limbs).  The client-side entry points
+ * (lmn_witness_columns, lmn_encrypt_columns, lmn_decrypt_decode) do not follow it: they always work 256 columns at a time, i.e.
+ * pooled workspaces of 256 * N words for values and plaintexts and 256 * (level+1) * N words for decryption, kept by the context. */
 int lmn_ctx_set_batch(lmn_ctx *ctx, uint32_t jobs_per_batch);
+
+/* No reference counterpart (Go's GC plays this role there).  The context pools its scratch between calls so that a steady-state
+ * prover never allocates: batch workspaces of the inner products and rescales (batch * ~(5k+4) limbs), the serialised leaves of the
+ * last Merkle build (n_leaves * leaf bytes: 4 GiB for 8192 leaves of 512 KiB), exchange staging of the communicator (2 chunks of
+ * batch ciphertexts + one chunk of whole ciphertexts) and the client-side batch buffers.  A host that commits once and then keeps
+ * the context for a long time calls this to hand that memory back; it waits for the context's queued work, frees the pools and
+ * reports the bytes released (released_bytes may be NULL).  The pools regrow on the next call that needs them. */
+int lmn_ctx_trim(lmn_ctx *ctx, size_t *released_bytes);
 
 /* ---------------- device-resident ciphertext store ---------------- */
 /* replaces []*rlwe.Ciphertext held between Commit and Prove (fhe/ligero.go:118-123) */
@@ -292,14 +302,26 @@ int lmn_witness_columns(lmn_ctx *ctx, const uint8_t *chacha_key32, uint32_t rows
  *            ringT.Reduce; else generated on the device from chacha_key32 as lmn_witness_columns does, rows x cols_total);
  *   matrix[j] = EncryptNew(Encode(values)) at max level: ct = (u pk0 + e0 + pt, u pk1 + e1), u uniform ternary, e0 / e1 rounded
  *            Gaussians (sigma 3.2, bound 19 = lattigo DefaultXe).
- * All randomness comes from the ChaCha20 stream keyed by enc_seed32 with nonce (column index, stream), so a column's ciphertext
- * does not depend on which rank or batch produced it.  Lattigo's own sampler stream cannot be reproduced (not vendored): the
- * contract is that the client decrypts every column to the witness, with Lattigo-sized noise - not ciphertext bits. */
+ * All randomness comes from the ChaCha20 stream keyed by enc_seed32 with nonce (column index, domain tag | stream, attempt), so a
+ * column's ciphertext does not depend on which rank or batch produced it.  Lattigo's own sampler stream cannot be reproduced (not
+ * vendored): the contract is that the client decrypts every column to the witness, with Lattigo-sized noise - not ciphertext bits.
+ * SECURITY: enc_seed32 is the ONLY source of encryption randomness.  It must be 32 bytes of fresh CSPRNG output (crypto/rand) for
+ * every matrix and must never be used again: two matrices encrypted under one seed give ct_j - ct'_j = (pt_j - pt'_j, 0), which
+ * reveals the difference of the plaintexts without the key (the reference's EncryptNew draws fresh randomness on every call).  All
+ * ranks that encrypt column blocks of ONE matrix share its seed; the zero column of that matrix (lmn_encrypt_zero) may share it too:
+ * the nonce carries a domain tag (column / zero column), and the witness keystream uses the all-zero nonce, so the three uses never
+ * read the same ChaCha20 block even if enc_seed32 and chacha_key32 are the same bytes. */
 int lmn_encrypt_columns(lmn_ctx *ctx, const uint64_t *values_colmajor_host, const uint8_t *chacha_key32, uint32_t rows, uint32_t cols_total,
                         uint32_t first_col, uint32_t count, const uint8_t *enc_seed32, lmn_store *matrix);
-/* zeroCol of fhe.Encode (fhe/code.go:15-22): EncryptNew of the all-zero plaintext into out[out_idx]; stream_id plays the column
- * index in the nonce (use one outside [0, cols)) */
+/* zeroCol of fhe.Encode (fhe/code.go:15-22): EncryptNew of the all-zero plaintext into out[out_idx].  stream_id plays the column
+ * index in the nonce, under the zero-column domain tag: any value is safe against the matrix columns; two zero columns made from one
+ * seed need distinct stream_ids.  The seed rule of lmn_encrypt_columns applies (fresh per matrix, never reused). */
 int lmn_encrypt_zero(lmn_ctx *ctx, const uint8_t *enc_seed32, uint32_t stream_id, lmn_store *out, uint32_t out_idx);
+/* test hook: the three small polynomials the encryptor draws for one ciphertext - u (uniform ternary), e0, e1 (rounded Gaussians) -
+ * as signed coefficients, out3_host [3][N].  id = the column index (zero_column = 0) or lmn_encrypt_zero's stream_id (zero_column = 1).
+ * The encryption of zero made from the same seed and id satisfies c0 + c1 s = u e_pk + e0 + e1 s exactly, which is how the tests tie
+ * this dump to the ciphertexts.  Never call it with a seed that encrypts real data: u, e0 and e1 open the ciphertext. */
+int lmn_test_encryption_samples(lmn_ctx *ctx, const uint8_t *enc_seed32, uint32_t id, int zero_column, int64_t *out3_host);
 /* backend.Encode(values, pt) at max level (fhe/ligero.go:204-205, 218-219: the r and b plaintexts of Prove): pt_host [num_q][N] */
 int lmn_encode_plaintext(lmn_ctx *ctx, const uint64_t *values, uint32_t n_values, uint64_t *pt_host);
 /* client side: EncryptedProof.Decrypt's decryptBatchedParallel (fhe/ligero.go:381-502, 577-636) = rlwe.Decryptor.DecryptNew +

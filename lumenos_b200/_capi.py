@@ -35,6 +35,7 @@ SIGNATURES = {
     "lmn_ctx_set_stream": (C.c_int, [vp, vp]),
     "lmn_ctx_synchronize": (C.c_int, [vp]),
     "lmn_ctx_launch_count": (C.c_uint64, [vp]),
+    "lmn_ctx_trim": (C.c_int, [vp, C.POINTER(C.c_size_t)]),
     "lmn_ctx_set_batch": (C.c_int, [vp, C.c_uint32]),
     "lmn_store_create": (C.c_int, [vp, C.c_uint32, C.c_uint32, C.POINTER(vp)]),
     "lmn_store_wrap": (C.c_int, [vp, vp, C.c_uint32, C.c_uint32, C.POINTER(vp)]),
@@ -81,6 +82,7 @@ SIGNATURES = {
     "lmn_witness_columns": (C.c_int, [vp, C.c_char_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, vp]),
     "lmn_encrypt_columns": (C.c_int, [vp, vp, C.c_char_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_char_p, vp]),
     "lmn_encrypt_zero": (C.c_int, [vp, C.c_char_p, C.c_uint32, vp, C.c_uint32]),
+    "lmn_test_encryption_samples": (C.c_int, [vp, vp, C.c_uint32, C.c_int, vp]),
     "lmn_encode_plaintext": (C.c_int, [vp, vp, C.c_uint32, vp]),
     "lmn_decrypt_decode": (C.c_int, [vp, vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, vp]),
     "lmn_load_galois_key": (C.c_int, [vp, C.c_uint64, vp]),

@@ -331,6 +331,25 @@ int lmn_ctx_create(const lmn_params *P, int device, lmn_ctx **out) {
     return 0;
 }
 
+// Everything the context pools between calls and can rebuild on demand goes back to the driver: the key-switch / rescale batch
+// workspaces, the serialised-leaf buffer of the Merkle build (n leaves x 512 KiB at log N 14: 4 GiB at config D on one GPU), the
+// index list, the exchange staging buffers of the communicator and the client-side batch buffers.  Keys, tables, plans and stores stay.
+int lmn_ctx_trim(lmn_ctx *c, size_t *released_bytes) {
+    if (!c) return fail(LMN_ERR_INVALID, "null context");
+    std::lock_guard<std::mutex> g(c->mu);
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaStreamSynchronize(c->copy_stream));
+    const size_t N = c->n, k = c->k, KP = c->k + c->np, beta = (size_t)((c->k + c->np - 1) / c->np);
+    size_t bytes = (size_t)c->ws_jobs * (2 * 2 * k + k + 2 * KP + beta * KP) * N * 8 + c->ws_ser_cap + c->ws_idx_cap * sizeof(uint32_t);
+    cudaFree(c->ws_col); cudaFree(c->ws_col2); cudaFree(c->ws_y); cudaFree(c->ws_acc); cudaFree(c->ws_mu); cudaFree(c->ws_ser); cudaFree(c->ws_idx);
+    c->ws_col = c->ws_col2 = c->ws_y = c->ws_acc = c->ws_mu = c->ws_ser = nullptr; c->ws_idx = nullptr;
+    c->ws_jobs = 0; c->ws_ser_cap = 0; c->ws_idx_cap = 0;
+    bytes += comm_state_trim(c->comm);
+    bytes += client_state_trim(c->client);
+    if (released_bytes) *released_bytes = bytes;
+    return 0;
+}
 void lmn_ctx_destroy(lmn_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);

@@ -24,6 +24,13 @@ void client_state_free(ClientState *s) {
     cudaFree(s->d_vals); cudaFree(s->d_m); cudaFree(s->d_buf); cudaFree(s->d_crt);
     delete s;
 }
+size_t client_state_trim(ClientState *s) {
+    if (!s) return 0;
+    const size_t bytes = (s->vals_cap + s->m_cap + s->buf_cap) * 8;
+    cudaFree(s->d_vals); cudaFree(s->d_m); cudaFree(s->d_buf);
+    s->d_vals = s->d_m = s->d_buf = nullptr; s->vals_cap = s->m_cap = s->buf_cap = 0;
+    return bytes;
+}
 static int grow(u64 **p, size_t *cap, size_t words) {
     if (*cap >= words) return 0;
     cudaFree(*p); *p = nullptr; *cap = 0;
@@ -41,7 +48,7 @@ static int need_ring(lmn_ctx *c) {
     if (!c->client || !c->client->d_twf) return fail(LMN_ERR_NOKEY, "plaintext ring not loaded (lmn_load_plaintext_ring)");
     return 0;
 }
-static const uint32_t BATCH = 256;   // columns per launch: bounds the workspaces (256 x N words each)
+static const uint32_t BATCH = 256;   // columns per launch: bounds the workspaces (256 x N words each); fixed, independent of lmn_ctx_set_batch (header)
 
 extern "C" {
 
@@ -82,11 +89,12 @@ int lmn_load_plaintext_ring(lmn_ctx *c, uint64_t psi_t) {
     return 0;
 }
 
-static int load_key(lmn_ctx *c, const uint64_t *host, size_t limbs, u64 **dst) {
+static int load_key(lmn_ctx *c, const uint64_t *host, size_t limbs, bool secret) {
     if (!c || !host) return fail(LMN_ERR_INVALID, "null argument");
-    std::lock_guard<std::mutex> g(c->mu);
+    std::lock_guard<std::mutex> g(c->mu);           // c->client is created and read under this lock only
     cudaSetDevice(c->device);
     if (!c->client) c->client = new ClientState();
+    u64 **dst = secret ? &c->client->d_sk : &c->client->d_pk;
     const size_t bytes = limbs * (size_t)c->n * 8;
     if (!*dst) CK(cudaMalloc(dst, bytes));
     CK(cudaMemcpy(*dst, host, bytes, cudaMemcpyHostToDevice));
@@ -94,13 +102,11 @@ static int load_key(lmn_ctx *c, const uint64_t *host, size_t limbs, u64 **dst) {
 }
 int lmn_load_public_key(lmn_ctx *c, const uint64_t *pk) {
     if (!c) return fail(LMN_ERR_INVALID, "null context");
-    if (!c->client) { std::lock_guard<std::mutex> g(c->mu); if (!c->client) c->client = new ClientState(); }
-    return load_key(c, pk, 2 * (size_t)c->k, &c->client->d_pk);
+    return load_key(c, pk, 2 * (size_t)c->k, false);
 }
 int lmn_load_secret_key(lmn_ctx *c, const uint64_t *sk) {
     if (!c) return fail(LMN_ERR_INVALID, "null context");
-    if (!c->client) { std::lock_guard<std::mutex> g(c->mu); if (!c->client) c->client = new ClientState(); }
-    return load_key(c, sk, (size_t)c->k, &c->client->d_sk);
+    return load_key(c, sk, (size_t)c->k, true);
 }
 
 int lmn_witness_columns(lmn_ctx *c, const uint8_t *chacha_key32, uint32_t rows, uint32_t cols, uint32_t first_col, uint32_t n_cols, uint64_t *host_out) {
@@ -149,7 +155,7 @@ int lmn_encrypt_columns(lmn_ctx *c, const uint64_t *values_colmajor_host, const 
             launch_witness(L, wkey, c->t, rows, cols_total, first_col + j0, nj, S->d_vals);
         }
         launch_pt_encode(L, c->logn, S->R, S->d_vals, rows, rows, nj, S->d_m);
-        launch_encrypt(L, c->T, seed, first_col + j0, nj, S->d_m, S->d_tinv, S->d_pk, matrix->d + (size_t)j0 * matrix->words(), matrix->words());
+        launch_encrypt(L, c->T, seed, first_col + j0, ENC_DOMAIN_COLUMN, nj, S->d_m, S->d_tinv, S->d_pk, matrix->d + (size_t)j0 * matrix->words(), matrix->words());
     }
     CK(cudaGetLastError());
     return 0;
@@ -163,8 +169,24 @@ int lmn_encrypt_zero(lmn_ctx *c, const uint8_t *enc_seed32, uint32_t stream_id, 
     if (int rc = need_ring(c)) return rc;
     ClientState *S = c->client;
     if (!S->d_pk) return fail(LMN_ERR_NOKEY, "public key not loaded");
-    launch_encrypt(c->L(), c->T, key_words(enc_seed32), stream_id, 1, nullptr, S->d_tinv, S->d_pk, out->d + (size_t)out_idx * out->words(), out->words());
+    launch_encrypt(c->L(), c->T, key_words(enc_seed32), stream_id, ENC_DOMAIN_ZERO, 1, nullptr, S->d_tinv, S->d_pk, out->d + (size_t)out_idx * out->words(), out->words());
     CK(cudaGetLastError());
+    return 0;
+}
+
+// test hook (tests/test_gpu_client.py): the sampler's output for one column, so that its distribution can be checked directly
+int lmn_test_encryption_samples(lmn_ctx *c, const uint8_t *enc_seed32, uint32_t id, int zero_column, int64_t *out3_host) {
+    if (!c || !enc_seed32 || !out3_host) return fail(LMN_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    if (int rc = need_ring(c)) return rc;
+    DevScratch d;
+    const size_t bytes = 3 * (size_t)c->n * sizeof(long long);
+    if (d.alloc(bytes) != cudaSuccess) { cudaGetLastError(); return fail(LMN_ERR_NOMEM, "sample dump buffer"); }
+    launch_dump_small(c->L(), c->T, key_words(enc_seed32), id, zero_column ? ENC_DOMAIN_ZERO : ENC_DOMAIN_COLUMN, c->q[0], d.as<long long>());
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out3_host, d.p, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
     return 0;
 }
 

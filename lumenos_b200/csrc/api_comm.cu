@@ -52,6 +52,24 @@ int load_nccl() {
         if (r_ != ncclSuccess) return fail(LMN_ERR_CUDA, std::string(#call) + ": " + g_nccl.GetErrorString(r_)); \
     } while (0)
 
+// One grouped set of sends / receives.  The first failure is remembered and the group is ALWAYS closed: a return between
+// ncclGroupStart and ncclGroupEnd would leave the calling thread inside an open group, and every later NCCL call of that thread
+// (the communicator's destruction included) would be queued into it and never run.
+struct NcclGroup {
+    ncclResult_t first = ncclSuccess;
+    const char *what = "";
+    bool open = false;
+    NcclGroup() { note(g_nccl.GroupStart(), "ncclGroupStart"); open = first == ncclSuccess; }
+    ~NcclGroup() { if (open) g_nccl.GroupEnd(); }
+    void note(ncclResult_t r, const char *w) { if (r != ncclSuccess && first == ncclSuccess) { first = r; what = w; } }
+    void send(const void *p, size_t words, int peer, ncclComm_t comm, cudaStream_t st) { if (first == ncclSuccess) note(g_nccl.Send(p, words, ncclUint64, peer, comm, st), "ncclSend"); }
+    void recv(void *p, size_t words, int peer, ncclComm_t comm, cudaStream_t st) { if (first == ncclSuccess) note(g_nccl.Recv(p, words, ncclUint64, peer, comm, st), "ncclRecv"); }
+    int end() {
+        if (open) { open = false; note(g_nccl.GroupEnd(), "ncclGroupEnd"); }
+        return first == ncclSuccess ? 0 : fail(LMN_ERR_CUDA, std::string(what) + ": " + g_nccl.GetErrorString(first));
+    }
+};
+
 struct CommState {
     ncclComm_t comm = nullptr;
     int rank = 0, world = 1;
@@ -73,6 +91,16 @@ void comm_state_free(CommState *s) {
     if (s->ev_ready) cudaEventDestroy(s->ev_ready);
     if (s->stream) cudaStreamDestroy(s->stream);
     delete s;
+}
+size_t comm_state_trim(CommState *s) {
+    if (!s) return 0;
+    if (s->stream) cudaStreamSynchronize(s->stream);
+    const size_t bytes = (s->stage_cap[0] + s->stage_cap[1] + s->whole_cap + s->send_cap) * 8 + s->idx_cap * 4 + s->hash_cap;
+    for (int b = 0; b < 2; b++) { cudaFree(s->stage[b]); s->stage[b] = nullptr; s->stage_cap[b] = 0; }
+    cudaFree(s->whole); cudaFree(s->sendbuf); cudaFree(s->d_idx); cudaFree(s->d_hash);
+    s->whole = s->sendbuf = nullptr; s->d_idx = nullptr; s->d_hash = nullptr;
+    s->whole_cap = s->send_cap = s->idx_cap = s->hash_cap = 0;
+    return bytes;
 }
 template <class T> static int grow_dev(T **p, size_t *cap, size_t count) {
     if (*cap >= count) return 0;
@@ -144,6 +172,7 @@ int lmn_comm_world(const lmn_ctx *c) { return c && c->comm ? c->comm->world : 1;
 // ---- coefficient slices of the queried columns -> whole ciphertexts on the rank that rescales them (Prove without a leaves store) ----
 int lmn_exchange_queried(lmn_ctx *c, const void *enc_slice_dev, uint32_t n, const uint32_t *query_idx, uint32_t n_queries, lmn_store *out) {
     if (!c || !enc_slice_dev || !query_idx || !out || n_queries == 0) return fail(LMN_ERR_INVALID, "null argument");
+    if (out->ctx != c) return fail(LMN_ERR_INVALID, "objects belong to different contexts");
     std::lock_guard<std::mutex> g(c->mu);
     cudaSetDevice(c->device);
     if (int rc = need_comm(c)) return rc;
@@ -168,15 +197,17 @@ int lmn_exchange_queried(lmn_ctx *c, const void *enc_slice_dev, uint32_t n, cons
     launch_copy_rows(L, (const u64 *)enc_slice_dev, S->d_idx, S->sendbuf, n_queries, slice_words);
     CK(cudaEventRecord(S->ev_ready, c->stream));
     CK(cudaStreamWaitEvent(S->stream, S->ev_ready, 0));
-    NK(g_nccl.GroupStart());
-    size_t off = 0;
-    for (uint32_t d = 0; d < G; d++) {
-        const uint32_t cnt = queries_of(n_queries, d, G);
-        if (cnt) NK(g_nccl.Send(S->sendbuf + off * slice_words, cnt * slice_words, ncclUint64, (int)d, S->comm, S->stream));
-        off += cnt;
-        if (mine) NK(g_nccl.Recv(S->stage[0] + (size_t)d * mine * slice_words, mine * slice_words, ncclUint64, (int)d, S->comm, S->stream));
+    {
+        NcclGroup grp;
+        size_t off = 0;
+        for (uint32_t d = 0; d < G; d++) {
+            const uint32_t cnt = queries_of(n_queries, d, G);
+            if (cnt) grp.send(S->sendbuf + off * slice_words, cnt * slice_words, (int)d, S->comm, S->stream);
+            off += cnt;
+            if (mine) grp.recv(S->stage[0] + (size_t)d * mine * slice_words, mine * slice_words, (int)d, S->comm, S->stream);
+        }
+        if (int rc = grp.end()) return rc;
     }
-    NK(g_nccl.GroupEnd());
     CK(cudaEventRecord(S->ev_recv[0], S->stream));
     CK(cudaStreamWaitEvent(c->stream, S->ev_recv[0], 0));
     if (mine) launch_slices_to_whole(L, S->stage[0], out->d, G, mine, PL, ns);
@@ -191,13 +222,12 @@ static int exchange_chunk(lmn_ctx *c, const u64 *enc_slice, uint32_t per, uint32
     CommState *S = c->comm;
     const uint32_t G = (uint32_t)S->world;
     const size_t slice_words = (size_t)2 * c->k * (c->n / G);
-    NK(g_nccl.GroupStart());
+    NcclGroup grp;
     for (uint32_t d = 0; d < G; d++) {
-        NK(g_nccl.Send(enc_slice + ((size_t)d * per + c0) * slice_words, cnt * slice_words, ncclUint64, (int)d, S->comm, S->stream));
-        NK(g_nccl.Recv(S->stage[b] + (size_t)d * cnt * slice_words, cnt * slice_words, ncclUint64, (int)d, S->comm, S->stream));
+        grp.send(enc_slice + ((size_t)d * per + c0) * slice_words, cnt * slice_words, (int)d, S->comm, S->stream);
+        grp.recv(S->stage[b] + (size_t)d * cnt * slice_words, cnt * slice_words, (int)d, S->comm, S->stream);
     }
-    NK(g_nccl.GroupEnd());
-    return 0;
+    return grp.end();
 }
 // shared driver: the whole encoded matrix from coefficient slices to this rank's column block, chunk by chunk; consume(chunk) runs on
 // the context's stream on the whole ciphertexts of the chunk while the next chunk is in flight on the communicator's stream
@@ -241,6 +271,7 @@ extern "C" {
 
 int lmn_exchange_encoded(lmn_ctx *c, const void *enc_slice_dev, uint32_t n, lmn_store *block) {
     if (!c || !block) return fail(LMN_ERR_INVALID, "null argument");
+    if (block->ctx != c) return fail(LMN_ERR_INVALID, "objects belong to different contexts");
     std::lock_guard<std::mutex> g(c->mu);
     cudaSetDevice(c->device);
     if (int rc = check_slices(c, enc_slice_dev, n)) return rc;
@@ -253,6 +284,7 @@ int lmn_exchange_encoded(lmn_ctx *c, const void *enc_slice_dev, uint32_t n, lmn_
 // communicator's stream while chunk i is rescaled to level 1 (processLeafParallel, fhe/ligero.go:146-154) on the context's stream
 int lmn_commit_leaves_from_slices(lmn_ctx *c, const void *enc_slice_dev, uint32_t n, lmn_store *leaves) {
     if (!c || !leaves) return fail(LMN_ERR_INVALID, "null argument");
+    if (leaves->ctx != c) return fail(LMN_ERR_INVALID, "objects belong to different contexts");
     std::lock_guard<std::mutex> g(c->mu);
     cudaSetDevice(c->device);
     if (int rc = check_slices(c, enc_slice_dev, n)) return rc;
@@ -270,6 +302,7 @@ int lmn_commit_leaves_from_slices(lmn_ctx *c, const void *enc_slice_dev, uint32_
 // once as column blocks feeds the slice-wise Encode)
 int lmn_exchange_to_slices(lmn_ctx *c, const lmn_store *block, uint32_t n, void *slice_dev) {
     if (!c || !block) return fail(LMN_ERR_INVALID, "null argument");
+    if (block->ctx != c) return fail(LMN_ERR_INVALID, "objects belong to different contexts");
     std::lock_guard<std::mutex> g(c->mu);
     cudaSetDevice(c->device);
     if (int rc = check_slices(c, slice_dev, n)) return rc;
@@ -290,12 +323,14 @@ int lmn_exchange_to_slices(lmn_ctx *c, const lmn_store *block, uint32_t n, void 
         launch_whole_to_slices(L, block->d + (size_t)c0 * ct_words, S->stage[b], G, cnt, PL, ns);
         CK(cudaEventRecord(S->ev_recv[b], c->stream));
         CK(cudaStreamWaitEvent(S->stream, S->ev_recv[b], 0));
-        NK(g_nccl.GroupStart());
-        for (uint32_t d = 0; d < G; d++) {
-            NK(g_nccl.Send(S->stage[b] + (size_t)d * cnt * slice_words, cnt * slice_words, ncclUint64, (int)d, S->comm, S->stream));
-            NK(g_nccl.Recv(out + ((size_t)d * per + c0) * slice_words, cnt * slice_words, ncclUint64, (int)d, S->comm, S->stream));
+        {
+            NcclGroup grp;
+            for (uint32_t d = 0; d < G; d++) {
+                grp.send(S->stage[b] + (size_t)d * cnt * slice_words, cnt * slice_words, (int)d, S->comm, S->stream);
+                grp.recv(out + ((size_t)d * per + c0) * slice_words, cnt * slice_words, (int)d, S->comm, S->stream);
+            }
+            if (int rc = grp.end()) return rc;
         }
-        NK(g_nccl.GroupEnd());
         CK(cudaEventRecord(S->ev_free[b], S->stream));
     }
     CK(cudaEventRecord(S->ev_ready, S->stream));

@@ -31,6 +31,10 @@ struct DevScratch {
 struct CommState;
 struct ClientState;     // plaintext ring, public / secret key material of the client-side entry points (api_client.cu)
 void client_state_free(ClientState *);
+// pooled batch workspaces released (the state itself, keys and tables stay); return the bytes given back.  Caller holds the context lock
+// and has drained the streams.
+size_t client_state_trim(ClientState *);
+size_t comm_state_trim(CommState *);
 
 struct lmn_ctx {
     int device = 0;

@@ -34,9 +34,14 @@ void launch_pt_encode(const Launch &L, int logn, const PlainRing &R, const u64 *
 // pt[j][i][.] = NTT_qi(m[j] t^-1 mod q_i): the NTT-domain plaintext at `nl` limbs (bgv.Encoder.Encode output)
 void launch_pt_lift(const Launch &L, const DeviceTables &T, int nl, const u64 *m, uint32_t n_cols, const ulonglong2 *tinv, u64 *pt);
 // ct[j] = (u pk0 + e0 + pt_j, u pk1 + e1), u ternary, e0 / e1 Gaussian (sigma 3.2, bound 19) drawn from the ChaCha20 stream of
-// `seed` with nonce (column id first_id + j, stream); m may be null (encryption of zero).  pk: [2][k][N] NTT + Montgomery.
-void launch_encrypt(const Launch &L, const DeviceTables &T, const ChaChaKey &seed, uint32_t first_id, uint32_t n_cols, const u64 *m,
+// `seed` with nonce (column id first_id + j, domain | stream, attempt); m may be null (encryption of zero).  pk: [2][k][N] NTT +
+// Montgomery.  `domain` separates the users of one seed: a matrix column, the zero column and the witness keystream (nonce 0, 0, 0)
+// never share a ChaCha20 block, whatever ids the caller picks.
+constexpr uint32_t ENC_DOMAIN_COLUMN = 0x100u, ENC_DOMAIN_ZERO = 0x200u;
+void launch_encrypt(const Launch &L, const DeviceTables &T, const ChaChaKey &seed, uint32_t first_id, uint32_t domain, uint32_t n_cols, const u64 *m,
                     const ulonglong2 *tinv, const u64 *pk, u64 *cts, uint64_t ct_words);
+// test hook: out3[0..2][N] = the signed coefficients of u, e0, e1 that launch_encrypt draws for column id `id` under `domain`
+void launch_dump_small(const Launch &L, const DeviceTables &T, const ChaChaKey &seed, uint32_t id, uint32_t domain, u64 q, long long *out3);
 // buf[j][i][.] = INTT_qi(c0 + c1 s) N^-1 t : the coefficient-domain t-multiple of the decryption (s: [k][N] NTT + Montgomery)
 void launch_decrypt_limbs(const Launch &L, const DeviceTables &T, const CrtConsts *Cd, int nl, const u64 *cts, uint64_t ct_words, uint32_t n_ct,
                           const u64 *sk, u64 *buf);

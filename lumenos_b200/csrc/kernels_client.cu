@@ -97,14 +97,16 @@ __global__ void __launch_bounds__(1024) k_pt_lift(const ModDev *__restrict__ mod
     for (int c = threadIdx.x; c < N; c += blockDim.x) o[c] = barrett(sm[PAD(c)], md.q, md.mu);
 }
 
-// 16 samples of one ChaCha20 block per thread-task; stream 0: uniform ternary, streams 1 / 2: rounded Gaussian
+// 16 samples of one ChaCha20 block per thread-task; stream (low byte) 0: uniform ternary, 1 / 2: rounded Gaussian.  The upper bits of
+// `stream` are the domain tag of the caller (ENC_DOMAIN_*), so that the nonce (id, tag | stream, attempt) of a matrix column, of the zero
+// column and of the witness keystream (nonce 0, 0, 0) can never coincide under one 32-byte key
 template <int LOGN>
 __device__ __forceinline__ void fill_small(u64 *sm, const ChaChaKey &seed, uint32_t id, uint32_t stream, u64 q) {
     constexpr int N = 1 << LOGN;
     for (int b = threadIdx.x; b < N / 16; b += blockDim.x) {
         uint32_t ks[16];
         chacha20_block(seed, (uint32_t)b, id, stream, 0u, ks);
-        if (stream == 0) {
+        if ((stream & 0xffu) == 0) {
 #pragma unroll
             for (int s = 0; s < 16; s++) {
                 const uint32_t x = (uint32_t)(((u64)ks[s] * 3u) >> 32);                    // {0, 1, 2} -> {0, +1, -1}
@@ -136,7 +138,7 @@ __device__ __forceinline__ void fill_small(u64 *sm, const ChaChaKey &seed, uint3
 
 template <int LOGN>
 __global__ void __launch_bounds__(1024) k_encrypt(const ModDev *__restrict__ mods, const ulonglong2 *__restrict__ tw_fwd, int k, const ChaChaKey seed,
-                                                  uint32_t first_id, const u64 *__restrict__ m, const ulonglong2 *__restrict__ tinv,
+                                                  uint32_t first_id, uint32_t domain, const u64 *__restrict__ m, const ulonglong2 *__restrict__ tinv,
                                                   const u64 *__restrict__ pk, u64 *__restrict__ cts, uint64_t ct_words) {
     extern __shared__ u64 sm[];
     constexpr int N = 1 << LOGN;
@@ -148,7 +150,7 @@ __global__ void __launch_bounds__(1024) k_encrypt(const ModDev *__restrict__ mod
     const u64 *pk0 = pk + ((size_t)i << LOGN), *pk1 = pk + ((size_t)(k + i) << LOGN);
     u64 *c0 = cts + (size_t)j * ct_words + ((size_t)i << LOGN), *c1 = cts + (size_t)j * ct_words + ((size_t)(k + i) << LOGN);
     // u pk
-    fill_small<LOGN>(sm, seed, id, 0, q);
+    fill_small<LOGN>(sm, seed, id, domain | 0u, q);
     __syncthreads();
     ntt_fwd_smem<LOGN>(sm, tw, q, 1);
     for (int c = threadIdx.x; c < N; c += blockDim.x) {
@@ -158,7 +160,7 @@ __global__ void __launch_bounds__(1024) k_encrypt(const ModDev *__restrict__ mod
     }
     __syncthreads();
     // + e0 + pt  (the plaintext enters in the coefficient domain: NTT(e0 + m t^-1) = NTT(e0) + pt)
-    fill_small<LOGN>(sm, seed, id, 1, q);
+    fill_small<LOGN>(sm, seed, id, domain | 1u, q);
     __syncthreads();
     if (m) {
         const ulonglong2 ti = tinv[i];
@@ -170,10 +172,23 @@ __global__ void __launch_bounds__(1024) k_encrypt(const ModDev *__restrict__ mod
     for (int c = threadIdx.x; c < N; c += blockDim.x) c0[c] = add_mod(c0[c], barrett(sm[PAD(c)], q, md.mu), q);
     __syncthreads();
     // + e1
-    fill_small<LOGN>(sm, seed, id, 2, q);
+    fill_small<LOGN>(sm, seed, id, domain | 2u, q);
     __syncthreads();
     ntt_fwd_smem<LOGN>(sm, tw, q, 1);
     for (int c = threadIdx.x; c < N; c += blockDim.x) c1[c] = add_mod(c1[c], barrett(sm[PAD(c)], q, md.mu), q);
+}
+
+// test hook: the small polynomial fill_small draws for (id, stream), as signed coefficients
+template <int LOGN>
+__global__ void __launch_bounds__(1024) k_dump_small(const ChaChaKey seed, uint32_t id, uint32_t stream, u64 q, long long *__restrict__ out) {
+    extern __shared__ u64 sm[];
+    constexpr int N = 1 << LOGN;
+    fill_small<LOGN>(sm, seed, id, stream, q);
+    __syncthreads();
+    for (int c = threadIdx.x; c < N; c += blockDim.x) {
+        const u64 v = sm[PAD(c)];
+        out[c] = v > q / 2 ? -(long long)(q - v) : (long long)v;
+    }
 }
 
 template <int LOGN>
@@ -238,11 +253,16 @@ void launch_pt_lift(const Launch &L, const DeviceTables &T, int nl, const u64 *m
     LaunchScope scope(L, KID_OTHER);
     LMN_CLIENT_DISPATCH(T.logn, k_pt_lift<LG><<<dim3(nl, n_cols), client_threads(T.n), (size_t)padded_words(T.n) * 8, L.stream>>>(T.mods, T.tw_fwd, nl, m, tinv, pt));
 }
-void launch_encrypt(const Launch &L, const DeviceTables &T, const ChaChaKey &seed, uint32_t first_id, uint32_t n_cols, const u64 *m,
+void launch_encrypt(const Launch &L, const DeviceTables &T, const ChaChaKey &seed, uint32_t first_id, uint32_t domain, uint32_t n_cols, const u64 *m,
                     const ulonglong2 *tinv, const u64 *pk, u64 *cts, uint64_t ct_words) {
     LaunchScope scope(L, KID_OTHER);
     LMN_CLIENT_DISPATCH(T.logn, k_encrypt<LG><<<dim3(T.k, n_cols), client_threads(T.n), (size_t)padded_words(T.n) * 8, L.stream>>>(
-                                    T.mods, T.tw_fwd, T.k, seed, first_id, m, tinv, pk, cts, ct_words));
+                                    T.mods, T.tw_fwd, T.k, seed, first_id, domain, m, tinv, pk, cts, ct_words));
+}
+void launch_dump_small(const Launch &L, const DeviceTables &T, const ChaChaKey &seed, uint32_t id, uint32_t domain, u64 q, long long *out3) {
+    LaunchScope scope(L, KID_OTHER);
+    for (uint32_t s = 0; s < 3; s++)
+        LMN_CLIENT_DISPATCH(T.logn, k_dump_small<LG><<<1, client_threads(T.n), (size_t)padded_words(T.n) * 8, L.stream>>>(seed, id, domain | s, q, out3 + (size_t)s * T.n));
 }
 void launch_decrypt_limbs(const Launch &L, const DeviceTables &T, const CrtConsts *Cd, int nl, const u64 *cts, uint64_t ct_words, uint32_t n_ct,
                           const u64 *sk, u64 *buf) {
@@ -261,7 +281,7 @@ const char *kernels_client_init() {
     cudaError_t e = cudaSuccess;
     const int big = (int)padded_words(1 << 14) * 8;
 #define SETSM(K) do { if (e == cudaSuccess) e = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, big); } while (0)
-#define SETS(LG) SETSM(k_pt_encode<LG>); SETSM(k_pt_lift<LG>); SETSM(k_encrypt<LG>); SETSM(k_decrypt_limb<LG>); SETSM(k_crt_decode<LG>);
+#define SETS(LG) SETSM(k_pt_encode<LG>); SETSM(k_pt_lift<LG>); SETSM(k_encrypt<LG>); SETSM(k_decrypt_limb<LG>); SETSM(k_crt_decode<LG>); SETSM(k_dump_small<LG>);
     SETS(13) SETS(14)
 #undef SETS
 #undef SETSM

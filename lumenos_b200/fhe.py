@@ -227,6 +227,13 @@ class ServerBFV:
     def SetBatch(self, jobs):
         check(_capi.lib().lmn_ctx_set_batch(self.ctx, jobs))
 
+    def Trim(self):
+        """hand the pooled scratch of the context (batch workspaces, serialised leaves, exchange staging) back to the driver;
+        returns the bytes released.  Everything regrows on demand."""
+        n = C.c_size_t(0)
+        check(_capi.lib().lmn_ctx_trim(self.ctx, C.byref(n)))
+        return n.value
+
     def LaunchCount(self):
         return _capi.lib().lmn_ctx_launch_count(self.ctx)
 

@@ -83,7 +83,55 @@ def test_encrypt_columns_decrypts_to_the_witness(logN, rows, cols, k):
     assert not np.array_equal(other[0], cts[0]) and np.array_equal(P.decrypt(S.sk, other[0])[:rows], M[:, 0])
     z2 = be.EncryptColumns(rows, 2, SEED, values=np.zeros((2, rows), np.uint64)).download()
     assert not np.array_equal(z2[0], z2[1])
-    # sampler sanity on the raw noise polynomial of the zero encryption: c0 + c1 s = u e_pk + e0 + e1 s
+    be.Close()
+
+
+def _samples(be, seed, ident, zero_column=False):
+    import ctypes as C
+    from lumenos_b200 import _capi
+    out = np.empty((3, be.params.N), np.int64)
+    _capi.check(_capi.lib().lmn_test_encryption_samples(be.ctx, bytes(seed), ident, int(zero_column), out.ctypes.data_as(C.c_void_p)))
+    return out
+
+
+def test_encryption_sampler_distribution_and_its_tie_to_the_ciphertext():
+    """The security-relevant half of the public-key encryptor (rlwe.Encryptor: u uniform ternary, e0 / e1 ~ lattigo DefaultXe, sigma 3.2
+    bound 19): the polynomials the device draws are dumped (lmn_test_encryption_samples) and checked as distributions, and the dump is
+    tied to the real ciphertext by the exact identity c0 + c1 s = u e_pk + e0 + e1 s of an encryption of zero."""
+    logN, k, ncol = 12, 3, 8
+    S = Scenario(logN, 2048, 4, k)
+    P, N = S.P, S.P.N
+    be = _server(S)
+    D = np.stack([_samples(be, SEED, j) for j in range(ncol)])            # [ncol][3][N]
+    u, e0, e1 = D[:, 0].ravel(), D[:, 1].ravel(), D[:, 2].ravel()
+    n = u.size                                                            # 32768 samples per polynomial kind
+    assert set(np.unique(u)) == {-1, 0, 1}
+    for v in (-1, 0, 1):                                                  # sd of a frequency = 0.0026
+        assert abs((u == v).mean() - 1 / 3) < 0.012, (v, (u == v).mean())
+    for e in (e0, e1):
+        assert np.abs(e).max() <= 19 and np.abs(e).max() >= 9             # truncated at 6 sigma, and not a narrow stand-in
+        assert abs(e.mean()) < 0.09, e.mean()                             # sd of the mean = 0.018
+        assert abs(e.std() - 3.2) < 0.08, e.std()                         # rounding adds 1/12 to the variance: 3.213; sd of the estimate 0.0125
+        assert abs((np.abs(e) <= 3).mean() - 0.726) < 0.02                # P(|round(3.2 Z)| <= 3) = P(|Z| < 1.094)
+    assert not np.array_equal(D[:, 1], D[:, 2]) and abs(np.corrcoef(e0, e1)[0, 1]) < 0.03      # e0 and e1 are different draws
+    assert abs(np.corrcoef(e0[:-1], e0[1:])[0, 1]) < 0.03                 # neighbours of one Box-Muller pair are independent
+    assert len({D[j].tobytes() for j in range(ncol)}) == ncol             # every column has its own randomness
+    # domain separation of the nonce: the zero column never reuses a matrix column's stream, whatever stream_id the caller picks
+    z = _samples(be, SEED, 0, zero_column=True)
+    assert not np.array_equal(z, D[0])
+    zero_ct = be.EncryptZero(SEED, streamId=0).download()[0]
+    col0_of_zeros = be.EncryptColumns(2048, 4, SEED, count=1, values=np.zeros((1, 2048), np.uint64)).download()[0]
+    assert not np.array_equal(zero_ct, col0_of_zeros)
+    # the dump IS what the encryptor used: in the NTT domain of limb 0, c0 + c1 s == u e_pk + e0 + e1 s with e_pk = pk0 + pk1 s
+    q = int(P.q[0])
+    ntt = lambda a: P.ntt(np.array([int(x) % q for x in a], dtype=np.uint64), 0).astype(object)   # noqa: E731
+    s_h = ntt(S.sk)
+    e_pk = (S.pk[0, 0].astype(object) + S.pk[1, 0].astype(object) * s_h) % q
+    for ident, zc, ct in ((0, True, zero_ct), (0, False, col0_of_zeros)):
+        uu, a0, a1 = _samples(be, SEED, ident, zero_column=zc)
+        lhs = (ct[0, 0].astype(object) + ct[1, 0].astype(object) * s_h) % q
+        rhs = (ntt(uu) * e_pk + ntt(a0) + ntt(a1) * s_h) % q
+        assert (lhs == rhs).all(), "dumped samples are not the ones inside the ciphertext (zero_column=%s)" % zc
     be.Close()
 
 
@@ -255,4 +303,13 @@ def test_client_entry_points_fail_loudly():
     assert np.array_equal(t.cpu().numpy().astype(np.uint64), st.download())
     blk = sharding.exchange_encoded(be, t)
     assert np.array_equal(blk.download(), st.download())
+    # the exchange entry points refuse a store of another context (as the client entry points do)
+    be2 = S.backend()
+    foreign = be2.NewStore(8)
+    tp = C.c_void_p(t.data_ptr())
+    idx = (C.c_uint32 * 2)(0, 1)
+    for rc in (lib.lmn_exchange_encoded(be.ctx, tp, 8, foreign.h), lib.lmn_exchange_to_slices(be.ctx, foreign.h, 8, tp),
+               lib.lmn_exchange_queried(be.ctx, tp, 8, idx, 2, foreign.h), lib.lmn_commit_leaves_from_slices(be.ctx, tp, 8, be2.NewStore(8, 1).h)):
+        assert rc == -1 and "different contexts" in lib.lmn_last_error().decode()
+    be2.Close()
     be.Close()

@@ -176,6 +176,42 @@ def test_commit_prove_bit_exact(logN, rows, cols, k, batch):
     be.Close()
 
 
+def test_trim_releases_the_pools_and_results_do_not_change():
+    """lmn_ctx_trim: a context that has committed and proved holds its batch workspaces and the serialised leaves; trimming returns
+    them to the driver (free device memory grows by what the call reports), and the next Commit / Prove regrows them and produces
+    the same bytes"""
+    import torch
+    from lumenos_b200 import fhe
+    logN, rows, cols, k = 12, 2048, 16, 3
+    S = scenario(logN, rows, cols, k)
+    be = S.backend()
+    matrix = be.NewStore(cols).upload(S.cts)
+    zero = be.NewStore(1).upload(S.zero[None])
+    committer = fhe.LigeroCommitter(128, rows, cols, 2)
+    idx = np.arange(committer.Queries, dtype=np.uint32) % (2 * cols)
+
+    def run():
+        prover = committer.Commit(matrix, be, (zero, 0))
+        proof = prover.Prove(S.rpt, S.bpt, idx, be)
+        return proof.Root, proof.MatR.download(), proof.MatZ.download(), proof.QueriedCols.download()
+
+    first = run()
+    be.Synchronize()
+    torch.cuda.synchronize()
+    free0 = torch.cuda.mem_get_info()[0]
+    released = be.Trim()
+    free1 = torch.cuda.mem_get_info()[0]
+    leaf_bytes = 2 * cols * 2 * 2 * (1 << logN) * 8                        # the serialised leaves alone
+    assert released >= leaf_bytes, (released, leaf_bytes)
+    assert free1 - free0 >= released * 0.8, (free0, free1, released)        # the driver rounds allocations to its own granularity
+    assert be.Trim() == 0                                                   # nothing left to give back
+    second = run()
+    assert first[0] == second[0]
+    for a, b, what in zip(first[1:], second[1:], ("MatR", "MatZ", "QueriedCols")):
+        assert_same(b, a, what + " after trim")
+    be.Close()
+
+
 def test_ring_switch_bit_exact():
     from lumenos_b200 import fhe
     logN, logNs, rows, cols, k = 8, 6, 128, 16, 4

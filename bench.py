@@ -39,6 +39,14 @@ NCU_ENCODE_TRAFFIC_D = 92.6e9                           # both passes, profiles/
 NCU_FMAHEAVY = {"k_mac": 66.4, "k_modup": 76.1, "k_down_pre": 78.7, "k_intt_c1": 64.9, "k_pintt": 62.1, "k_down": 51.5, "k_rs_pre": 56.7,
                 "k_rs_intt": 64.9}
 PUBLISHED_COMMIT_S = {"A": 1.03, "B": 2.04, "C": 9.17, "D": 18.79}  # "Commit eval": leaf rescale + Merkle (BASELINE.md:23)
+# the reference's own span labels (core/tracer.go:10-65; fhe/ligero.go:97 "Encode", :224-225 "InnerProduct(Matrix, r)" / "InnerProduct(Matrix, b)"
+# run side by side, :262 "Query columns", "Prove FHE evaluation" = inner products + query) with the published seconds
+PUBLISHED_SPANS_S = {"Encode": {"A": 5.17, "B": 12.63, "C": 66.78, "D": 142.73},
+                     "InnerProduct(Matrix, r) || InnerProduct(Matrix, b)": {"A": 8.51, "B": 22.74, "C": 109.60, "D": 247.48},
+                     "Query columns": {"A": 1.10, "B": 1.42, "C": 3.55, "D": 7.63},
+                     "Prove FHE evaluation": {"A": 9.61, "B": 24.17, "C": 113.16, "D": 255.12}}
+NCU_TRAFFIC_CAPTURE = {"k_mac": "profiles/r2c_mac_kernel.csv (ncu --set full of one 256-job launch of k_mac_rd<8>, taken at commit 69ca6b1; k_mac_rd has not changed since)",
+                       "k_encode_pass": "profiles/r1k_encode_kernels.csv (ncu --set full of both Encode passes at config D, round 1; kernel unchanged since)"}
 PUBLISHED_S = {"A": 14.77, "B": 36.80, "C": 179.93, "D": 397.85}  # Encode + Prove eval, m7i.8xlarge 32 vCPU
 RHO_INV, SECURITY_BITS = 2, 128
 
@@ -307,15 +315,31 @@ def main():
         (rank, time.perf_counter() - t_setup, args.config, rows, cols, logN, k, G, torch.cuda.memory_allocated(dev) / 2**30))
 
     vp = C.c_void_p
+    # config E (fhe/ring_switch.go; the switch sits inside the per-column worker loop, fhe/ligero.go:336-342, so it shards with the columns):
+    # random residues in the evk layout [beta][2][k+np][N], the same on every rank
+    LOGN_SMALL = 10
+    rs_evk = None
+    if not args.no_commit and logN >= 12:
+        rs_rng = np.random.default_rng(777)
+        rs_evk = np.stack([rs_rng.integers(0, m, size=(beta, 2, N), dtype=np.uint64) for m in mods], axis=2)
+        be.SetRingSwitchServer(fhe.RingSwitchServer(be, rs_evk, LOGN_SMALL))
+        if args.no_parity:
+            rs_evk = True      # the key is on the device; the host copy is only needed by the oracle self-check
 
-    def step():
+    def encode_stage():
         # ---- Commit: Encode span (fhe/ligero.go:96-100) ----
         if G == 1:
             _capi.check(lib.lmn_encode(be.ctx, plan, mat_enc.h, zero_store.h, 0, enc_store.h))
         else:
             _capi.check(lib.lmn_encode_lanes(be.ctx, plan, vp(mat_enc_t.data_ptr()), vp(zero_t.data_ptr()), vp(enc_t.data_ptr()), log_ns))
+
+    def inner_product_stage():
         # ---- Prove: inner products (ligero.go:231-242) ----
         _capi.check(lib.lmn_inner_product2(be.ctx, mat_cols.h, rpt.ctypes.data_as(vp), bpt.ctypes.data_as(vp), rows, matR.h, matZ.h))
+
+    def step():
+        encode_stage()
+        inner_product_stage()
         query_stage()
 
     def query_stage():
@@ -372,6 +396,43 @@ def main():
                     full = torch.cat(parts, dim=-1)
                 if r == rank and not np.array_equal(gq[pos], P.rescale_to_level1(u(full))[0]):
                     bad.append("QueriedCols[%d] (column %d)" % (qs[pos], col))
+        extra = ""
+        if rs_evk is not None:
+            # config E: this rank's MatR block ring-switched to LogN 10 (lmn_ring_switch), two columns against the oracle's RingSwitchNew
+            small = be.RingSwitch().RingSwitchNew(matR)
+            gs = small.download()
+            for j in sorted({0, cols_loc - 1}):
+                if not np.array_equal(gs[j], P.ringswitch(gr[j], rs_evk, LOGN_SMALL)):
+                    bad.append("ring-switched MatR[%d]" % j)
+            small.free()
+            extra += ", 2 ring-switched MatR columns (config E)"
+        if G > 1:
+            # Commit's exchange (fhe/ligero.go:126-183 on column-sharded ranks): a seeded matrix of 2 G max-level ciphertexts held as
+            # coefficient slices -> lmn_commit_leaves_from_slices -> lmn_leaf_hashes -> lmn_allgather_leaf_hashes -> tree; the oracle
+            # rescales the whole ciphertexts (assembled by a plain all_gather) and builds core.NewTree over their leaf bytes
+            n_s = 2 * G
+            gen = torch.Generator(device=dev); gen.manual_seed(5150 + rank)
+            sl = torch.empty((n_s, 2, k, Ns), dtype=torch.int64, device=dev)
+            for i in range(k):
+                sl[:, :, i, :].random_(0, int(q[i]), generator=gen)
+            lf_s = fhe.LeafFormat.placeholder(lout, N)
+            lv = sharding.commit_leaves_from_slices(be, sl)
+            tree = sharding.commit_tree(be, lv, lf_s)
+            parts = [torch.empty_like(sl) for _ in range(G)]
+            dist.all_gather(parts, sl)
+            whole = u(torch.cat(parts, dim=-1))
+            want_leaves = [P.rescale_to_level1(whole[j])[0] for j in range(n_s)]
+            if not np.array_equal(lv.download(), np.stack(want_leaves[rank * 2:rank * 2 + 2])):
+                bad.append("leaves from slices")
+            want_tree = O.MerkleTree([O.leaf_bytes(w, lf_s.header, lf_s.polyHeader, lf_s.limbHeader) for w in want_leaves])
+            if tree.MerkleRoot() != want_tree.root() or tree.GetMerklePath(rank) != want_tree.path(rank):
+                bad.append("Merkle root / path of the sharded Commit")
+            # wire format of this rank's leaf block == the oracle's ct.WriteTo streams (sharding.marshal_columns -> lmn_store_marshal)
+            if sharding.marshal_columns(be, lv, lf_s) != b"".join(O.leaf_bytes(w, lf_s.header, lf_s.polyHeader, lf_s.limbHeader) for w in want_leaves[rank * 2:rank * 2 + 2]):
+                bad.append("marshalled column block")
+            tree.free(); lv.free()
+            del sl, parts, whole
+            extra += ", Commit exchange on %d seeded columns (leaves from slices, all-gathered leaf hashes, root, a path, marshalled block)" % n_s
         flag = torch.tensor([len(bad)], device=dev)
         if G > 1:
             dist.all_reduce(flag)
@@ -379,7 +440,7 @@ def main():
             log("[rank %d] PARITY FAILURE against the oracle: %s" % (rank, ", ".join(bad)))
         if int(flag.item()):
             raise SystemExit("parity check against the oracle failed on %d sampled outputs" % int(flag.item()))
-        return "ok: per rank 256 encoded lanes x %d, 3 MatR + 1 MatZ columns, 2 queried columns bit-identical to the oracle (%.0f s, untimed)" % (n, time.perf_counter() - t0)
+        return "ok: per rank 256 encoded lanes x %d, 3 MatR + 1 MatZ columns, 2 queried columns%s bit-identical to the oracle (%.0f s, untimed)" % (n, extra, time.perf_counter() - t0)
 
     def timed(fn, steps):
         barrier()
@@ -428,6 +489,29 @@ def main():
     enc_ms, enc_n, _ = prof("k_encode_pass")
     _capi.check(lib.lmn_profile_enable(be.ctx, 0))
 
+    # ---- the same step once more with an event between the stages: device time per span under the reference's own labels
+    # (core/tracer.go; BASELINE.md section 1 quotes the published numbers in these spans), max over ranks, outside the timed region ----
+    def span_pass(steps):
+        evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(steps)]
+        barrier()
+        for e in evs:
+            e[0].record(stream); encode_stage(); e[1].record(stream); inner_product_stage(); e[2].record(stream); query_stage(); e[3].record(stream)
+        barrier()
+        t = torch.tensor([sum(e[i].elapsed_time(e[i + 1]) for e in evs) / steps for i in range(3)], device=dev, dtype=torch.float64)
+        if G > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return [float(x) / 1e3 for x in t.tolist()]
+    sp_enc, sp_ip, sp_q = span_pass(max(1, min(args.steps, 3)))
+    pub = lambda name: PUBLISHED_SPANS_S[name].get(args.config) if not args.cols_override else None  # noqa: E731
+    reference_spans = {
+        "Encode": {"s": sp_enc, "published_reference_s": pub("Encode")},
+        "InnerProduct(Matrix, r) || InnerProduct(Matrix, b)": {"s": sp_ip, "published_reference_s": pub("InnerProduct(Matrix, r) || InnerProduct(Matrix, b)"),
+                                                               "note": "the reference runs the two from two goroutines side by side and logs their common span; here one fused call reads the matrix once"},
+        "Query columns": {"s": sp_q, "published_reference_s": pub("Query columns")},
+        "Prove FHE evaluation": {"s": sp_ip + sp_q, "published_reference_s": pub("Prove FHE evaluation")},
+        "note": "device time between CUDA events on the library's stream, one extra pass after the timed region, max over ranks per span; published = m7i.8xlarge 32 vCPU (BASELINE.md section 1), different hardware",
+    }
+
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -457,7 +541,7 @@ def main():
                                     "note": "butterflies = (digit, target modulus) pairs x N/2 x 11 block levels; the gadget MACs and Montgomery reductions (not counted in achieved) are extra integer work of the same kernel"},
                 "avg_launch_ms": mac_avg_s * 1e3, "launches": mac_n, "share_of_step": mac_ms / total_ms,
                 "traffic": (NCU_MAC_TRAFFIC_PER_JOB_D * jobs_avg if args.config == "D" else None),
-                "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of k_mac_rd<8> (profiles/, see NCU_MAC_TRAFFIC_PER_JOB_D), scaled per job",
+                "traffic_source": "NOT measured by this run: a constant from " + NCU_TRAFFIC_CAPTURE["k_mac"] + ", dram__bytes_read.sum + dram__bytes_write.sum scaled per job; re-capture when the kernel changes",
                 "ncu_fmaheavy_pct": NCU_FMAHEAVY.get("k_mac")}
     # the same kernel against HBM (it is not HBM-bound: kept so the reader sees both ceilings)
     mac_bytes = jobs_avg * (2 * k + 2 * (k + np_)) * limb_b + beta * 2 * (k + np_) * limb_b
@@ -473,7 +557,7 @@ def main():
                        "unit": "GB/s", "frac": enc_alg / enc_s / 1e9 / hbm_peak, "peak_source": hbm_src,
                        "algorithmic_bytes": enc_alg, "frac_two_pass": enc_two_pass / enc_s / 1e9 / hbm_peak, "two_pass_bytes": enc_two_pass,
                        "traffic": (NCU_ENCODE_TRAFFIC_D if args.config == "D" and G == 1 and not args.cols_override else None),
-                       "traffic_source": "ncu --set full at config D, both passes (profiles/, see NCU_ENCODE_TRAFFIC_D)",
+                       "traffic_source": "NOT measured by this run: a constant from " + NCU_TRAFFIC_CAPTURE["k_encode_pass"],
                        "ms_per_step": enc_s * 1e3, "share_of_step": enc_ms / total_ms}
     # the same kernel on the integer side: per lane one Encode is `adds` butterflies (one add + one sub) and `muls` Shoup multiplications
     # (fhe/ntt.go op counts); 28 multiplier-pipe cycles per multiplication against 5.7 pipe lane-cycles per HBM byte
@@ -540,6 +624,8 @@ def main():
         sha_ms = cm_parts.get("k_sha256_leaves", {}).get("ms", 0.0)
         commit_merkle = {"ms": cm_ms, "leaves": n, "leaf_bytes": leaf_len, "kernels": cm_parts,
                          "sha256_leaves_GBps": (n_loc * leaf_len / (sha_ms * 1e-3) / 1e9) if sha_ms else None,
+                         "sha256_leaves_note": "a leaf is ONE sequential SHA-256 chain of leaf_bytes / 64 blocks (8197 at log N 14) and one warp lane runs one chain, so k_sha256_leaves takes the "
+                                               "same ~8.3 ms for 1024 leaves per rank as for 8192: fewer leaves per GPU lower the GB/s, not the time - the floor of this span on many GPUs",
                          "query_gather_from_leaves_ms": gq_ms, "published_reference_s": PUBLISHED_COMMIT_S.get(args.config),
                          "note": "leaf rescale of all n encoded columns to level 1 + leaf serialisation + SHA-256 Merkle tree on the GPU; root read back to the host"
                                  + ("" if G == 1 else "; %d GPUs: all-to-all of the encoded matrix from coefficient slices to column blocks, leaves and leaf hashes per rank, all-gather of the hashes, tree on every rank" % G)}
@@ -547,11 +633,7 @@ def main():
 
     # ---- config E (experimental path, fhe/ring_switch.go): MatR / MatZ ring-switched to LogN = 10, beside the headline ----
     ring_switch = None
-    if G == 1 and not args.no_commit and logN >= 12:
-        beta_full = (k + len(p) - 1) // len(p)
-        rs_evk = np.stack([rng.integers(0, m, size=(beta_full, 2, N), dtype=np.uint64) for m in list(q) + list(p)], axis=2)   # [beta][2][k+np][N]
-        rs = fhe.RingSwitchServer(be, rs_evk, 10)
-        del rs_evk
+    if rs_evk is not None:
         small_r, small_z = fhe.CiphertextStore(be, cols_loc, small=True), fhe.CiphertextStore(be, cols_loc, small=True)
 
         def rs_step():
@@ -559,12 +641,40 @@ def main():
             _capi.check(lib.lmn_ring_switch(be.ctx, matZ.h, small_z.h))
         rs_step()
         rs_ms = timed(rs_step, 1)
-        ring_switch = {"ms": rs_ms, "ciphertexts": 2 * cols_loc, "to_logN": 10, "out_bytes": small_r.nbytes + small_z.nbytes,
-                       "note": "RingSwitchNew (fhe/ring_switch.go:106-113) of every MatR / MatZ ciphertext: level-0 key switch + decimation; config E = the headline step + this"}
+        ring_switch = {"ms": rs_ms, "ciphertexts": 2 * cols, "to_logN": LOGN_SMALL, "out_bytes": (small_r.nbytes + small_z.nbytes) * G,
+                       "config_E_step_s": (ms_per_step + rs_ms) / 1e3,
+                       "published_reference_inner_product_s": {"A": 8.51, "B": 22.65, "C": 110.17, "D": 248.44}.get(args.config),
+                       "note": "RingSwitchNew (fhe/ring_switch.go:106-113) of every MatR / MatZ ciphertext: level-0 key switch + decimation, each rank on its own column block (max over ranks); "
+                               "config E = the headline step + this; the switched columns are oracle-checked in parity_check"}
         small_r.free(); small_z.free()
 
     # ---- wire format (EncryptedProof.MarshalBinary, fhe/ligero.go:646-704), beside the headline ----
     proof_marshal = None
+    if G > 1 and not args.no_commit:
+        # every rank serialises its own MatR / MatZ block and its queried columns into pinned host memory (lmn_store_marshal; every stream has one
+        # length, so rank r's block lands at a fixed offset of the proof buffer: sharding.marshal_columns)
+        fm = fhe.LeafFormat.placeholder(lout, N).c_struct()
+        parts, tot = [], 0
+        for st, cnt in ((matR, cols_loc), (matZ, cols_loc), (queried, len(my_q))):
+            ln = C.c_size_t()
+            if cnt:
+                _capi.check(lib.lmn_store_marshal(be.ctx, st.h, 0, cnt, C.byref(fm), None, 0, C.byref(ln)))
+                parts.append((st, cnt, tot, ln.value)); tot += ln.value
+        h_proof = vp()
+        _capi.check(lib.lmn_host_alloc(max(tot, 8), C.byref(h_proof)))
+
+        def marshal_once():
+            for st, cnt, off, ln in parts:
+                got = C.c_size_t()
+                _capi.check(lib.lmn_store_marshal(be.ctx, st.h, 0, cnt, C.byref(fm), vp(h_proof.value + off), ln, C.byref(got)))
+        marshal_once()
+        pm_ms = timed(marshal_once, 1)
+        tot_t = torch.tensor([tot], device=dev, dtype=torch.int64)
+        dist.all_reduce(tot_t)
+        proof_marshal = {"ms": pm_ms, "bytes": int(tot_t.item()), "GBps_to_pinned_host": int(tot_t.item()) / (pm_ms * 1e-3) / 1e9,
+                         "published_reference_s": {"D": 2.25}.get(args.config),
+                         "note": "each of the %d ranks serialises its MatR / MatZ column block and its queried columns on its GPU into its range of the pinned proof buffer (max over ranks); metadata, paths and root are host bytes" % G}
+        lib.lmn_host_free(h_proof)
     if G == 1 and not args.no_commit:
         lfm = fhe.LeafFormat.placeholder(lout, N)
         depth = max(1, (n - 1).bit_length())
@@ -681,7 +791,7 @@ def main():
                        "batch_jobs": args.batch},
             "parity_check": parity,
             "e2e": e2e, "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "roofline_hbm": roofline_hbm,
-            "roofline_encode": roofline_encode, "kernel_rooflines": kernel_rooflines, "kernel_breakdown_one_step": breakdown, "commit_merkle": commit_merkle, "ring_switch_E": ring_switch, "proof_marshal": proof_marshal,
+            "roofline_encode": roofline_encode, "kernel_rooflines": kernel_rooflines, "kernel_breakdown_one_step": breakdown, "reference_spans": reference_spans, "commit_merkle": commit_merkle, "ring_switch_E": ring_switch, "proof_marshal": proof_marshal,
             "encrypt_matrix": encrypt_matrix, "client_decrypt": client_decrypt, "cpu_baseline": cpu,
             "published_reference_s": PUBLISHED_S[args.config],
         }

@@ -54,7 +54,7 @@ typedef enum lmn_status {
  * ring.ModExp(subRing.PrimitiveRoot, (q-1)/subRing.NthRoot, q).  The library derives its NTT tables from
  * them so that its NTT domain is the host's NTT domain. */
 typedef struct lmn_params {
-    uint32_t log_n;          /* ring degree N = 2^log_n (4..16)                         */
+    uint32_t log_n;          /* ring degree N = 2^log_n: 6, 8, 10, 12, 13 or 14 (others: LMN_ERR_UNSUPPORTED) */
     uint32_t num_q;          /* k: number of Q primes (max level = k-1)                  */
     uint32_t num_p;          /* number of special primes P (reference: 2)                */
     const uint64_t *q;       /* [num_q] params.Q()                                       */

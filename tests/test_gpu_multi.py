@@ -18,6 +18,7 @@ import ctypes as C
 import numpy as np, torch, torch.distributed as dist
 from helpers import Scenario
 from lumenos_b200 import fhe, sharding, _capi
+from oracle import oracle as O
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(local); dev = torch.device("cuda", local)
 dist.init_process_group("nccl", device_id=dev)
@@ -58,6 +59,17 @@ gr, gz = mr.download(), mz.download()
 for j in range(a, b):
     assert np.array_equal(gr[j - a], P.inner_sum_eval_column(S.cts[j], S.rpt, S.rows, S.gal, S.evks)[0])
     assert np.array_equal(gz[j - a], P.inner_sum_eval_column(S.cts[j], S.bpt, S.rows, S.gal, S.evks)[0])
+# config E on the column shard (fhe/ligero.go:336-342: the ring switch sits inside the per-column worker loop, so it shards with the
+# columns): every rank loads the ring-switch key and switches its own MatR / MatZ block; no exchange is involved
+logNs = 10 if P.logN >= 12 else 6
+Ps = O.Params(logNs, q=P.q[:1], p=P.p)
+rs_evk = P.keygen_ringswitch(S.sk, Ps.keygen_sk(9), logNs, 11)
+be.SetRingSwitchServer(fhe.RingSwitchServer(be, rs_evk, logNs))
+for store, lvl1 in ((mr, gr), (mz, gz)):
+    small = be.RingSwitch().RingSwitchNew(store).download()
+    assert small.shape == (b - a, 2, 1, 1 << logNs)
+    for j in range(b - a):
+        assert np.array_equal(small[j], P.ringswitch(lvl1[j], rs_evk, logNs)), "ring-switched column %%d differs on rank %%d" %% (a + j, rank)
 # wire format on the column shards: every rank marshals its own MatR / MatZ block, the blocks concatenated in rank order are the
 # MatR / MatZ sections of EncryptedProof.WriteTo (fhe/ligero.go:665-679)
 from oracle import oracle as O

@@ -161,11 +161,12 @@ def work_per_job(k, np_, logN):
     blk = N // 2 * min(11, logN)                # butterflies of the block levels of one limb
     w = {}
     w["k_intt_c1"] = {"butterflies": k * blk, "other": 0}
+    # base-conversion products are 64 x 32-bit (2 IMAD.WIDE where a butterfly's Shoup product takes 5): `weighted` counts them as 0.4
     w["k_modup"] = {"butterflies": sum(c * nd * N // 2 + c * (KP - nd) * N // 2 for nd in dig),
-                    "other": sum(nd * N + (KP - nd) * nd * N for nd in dig)}
+                    "other": sum(nd * N + (KP - nd) * nd * N for nd in dig), "other_weighted": sum(nd * N + 0.4 * (KP - nd) * nd * N for nd in dig)}
     w["k_mac"] = {"butterflies": sum(KP - nd for nd in dig) * blk, "other": 0, "macs": beta * 2 * KP * N}
     w["k_pintt"] = {"butterflies": 2 * np_ * blk, "other": 0}
-    w["k_down_pre"] = {"butterflies": 2 * (c * np_ * N // 2 + c * k * N // 2), "other": 2 * (np_ * N + k * np_ * N)}
+    w["k_down_pre"] = {"butterflies": 2 * (c * np_ * N // 2 + c * k * N // 2), "other": 2 * (np_ * N + k * np_ * N), "other_weighted": 2 * (np_ * N + 0.4 * k * np_ * N)}
     w["k_down"] = {"butterflies": 2 * k * blk, "other": 2 * k * N}
     # chained rescale from level k-1 to 1 (fhe/ligero.go:331-333): limb i takes part in the steps that drop the limbs above it
     steps = sum(l for l in range(2, k))         # sum over dropped limbs l = k-1 .. 2 of the l limbs below: (x_i - r_l) q_l^-1
@@ -174,6 +175,7 @@ def work_per_job(k, np_, logN):
     w["k_rs_apply"] = {"butterflies": 2 * min(2, k) * blk, "other": 0}
     for v in w.values():
         v["modmuls"] = v["butterflies"] + v["other"]
+        v["butterfly_equivalents"] = v["butterflies"] + v.get("other_weighted", v["other"])     # multiplier-pipe weight of a butterfly = 1
         v.setdefault("macs", 0)
     return w
 
@@ -521,8 +523,9 @@ def main():
     np_ = len(p)
     limb_b = N * 8
     # integer ceiling: the product's own 3-product Shoup butterfly, register-resident, on every SM (lmn_bench_int_peak), this run
-    pk = C.c_double()
+    pk, pk_prod = C.c_double(), C.c_double()
     _capi.check(lib.lmn_bench_int_peak(be.ctx, C.byref(pk)))
+    _capi.check(lib.lmn_bench_product_butterfly(be.ctx, C.byref(pk_prod)))
     sm_mhz = clocks.get("sm_mhz") or 1965.0
     # butterflies/s if the multiplier pipe did nothing but one butterfly's multiplies: 5 IMAD.WIDE at 4.4 cycles per warp and sub-partition
     # + 6 IMAD-class instructions at 2 (profiles/r2c_int_pipe_probe.txt, profiles/sass_summary.txt) = 34 pipe cycles
@@ -533,7 +536,15 @@ def main():
     mac_bfly = jobs_avg * work["k_mac"]["butterflies"]
     roofline = {"kernel": "k_mac (k_mac_rd: block NTT of the base-converted digits + gadget MAC; the dominant kernel)", "bound": "int",
                 "achieved": mac_bfly / mac_avg_s / 1e9, "peak": pk.value / 1e9, "unit": "Gbutterfly/s", "frac": mac_bfly / mac_avg_s / pk.value,
-                "peak_source": "lmn_bench_int_peak, this run: the product's own 3-product Shoup butterfly (ntt_blk.cuh bfly_ct3), register-resident on all SMs, no loads or barriers",
+                "peak_source": "lmn_bench_int_peak, this run: the fastest butterfly formulation measured on this part (tools/int_pipe_probe.cu k_bfly<1>: 3-product Shoup quotient, middle sum as IMAD.WIDE's 64-bit addend, plain adds, lazy [0,3q)), register-resident, 64 warps per SM launched, nothing else in the loop",
+                "fractions": {
+                    "vs_butterfly_ceiling": mac_bfly / mac_avg_s / pk.value,
+                    "vs_product_butterfly_register_resident": mac_bfly / mac_avg_s / max(pk_prod.value, 1.0),
+                    "multiplier_pipe_time_model": None,      # filled below from the SASS mix, gadget MACs and reductions included
+                    "ncu_sm__pipe_fmaheavy_cycles_active_pct": NCU_FMAHEAVY.get("k_mac"),
+                    "ncu_capture": "profiles/r2g_mac_kernel.csv (round-2 end state; k_mac_rd unchanged since)",
+                    "bar": "the 60 % bar is read against vs_butterfly_ceiling (the strictest of the three); the pipe-time model and ncu's fmaheavy counter say how busy the multiplier pipe is, not how close the kernel is to the best butterfly rate"},
+                "product_butterfly_register_resident": pk_prod.value / 1e9,
                 "peak_fmaheavy_only": fma_bound / 1e9,
                 "peak_fmaheavy_only_note": "148 SMs x 4 sub-partitions x 32 lanes x %.0f MHz / 34 multiplier-pipe cycles per butterfly (5 IMAD.WIDE of 4.4 cycles + 6 IMAD of 2, measured by tools/int_pipe_probe.cu and counted in the SASS): the butterfly ceiling above is %.0f %% of it because a butterfly also needs about 32 issue slots and 26 ALU cycles" % (sm_mhz, 100 * pk.value / fma_bound),
                 "frac_of_fmaheavy_only": mac_bfly / mac_avg_s / fma_bound,
@@ -543,6 +554,11 @@ def main():
                 "traffic": (NCU_MAC_TRAFFIC_PER_JOB_D * jobs_avg if args.config == "D" else None),
                 "traffic_source": "NOT measured by this run: a constant from " + NCU_TRAFFIC_CAPTURE["k_mac"] + ", dram__bytes_read.sum + dram__bytes_write.sum scaled per job; re-capture when the kernel changes",
                 "ncu_fmaheavy_pct": NCU_FMAHEAVY.get("k_mac")}
+    # multiplier-pipe time of one launch from the measured issue rates (IMAD.WIDE 4.4 cycles, IMAD / IMAD.X 2 cycles per warp and sub-partition,
+    # profiles/r2c_int_pipe_probe.txt) x the kernel's compiled mix: 5 IMAD.WIDE + 6.2 IMAD per butterfly (profiles/sass_summary.txt) and, per gadget
+    # MAC (a 64x64 -> 128-bit multiply-accumulate of both key components, Montgomery reduction amortised over the digits), 4 IMAD.WIDE + 2 IMAD
+    pipe_cycles = mac_bfly * (5 * 4.4 + 6.2 * 2) + jobs_avg * work["k_mac"]["macs"] * (4 * 4.4 + 2 * 2)
+    roofline["fractions"]["multiplier_pipe_time_model"] = pipe_cycles / (148 * 4 * 32 * sm_mhz * 1e6) / mac_avg_s
     # the same kernel against HBM (it is not HBM-bound: kept so the reader sees both ceilings)
     mac_bytes = jobs_avg * (2 * k + 2 * (k + np_)) * limb_b + beta * 2 * (k + np_) * limb_b
     roofline_hbm = {"kernel": "k_mac", "bound": "hbm", "achieved": mac_bytes / mac_avg_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
@@ -581,9 +597,10 @@ def main():
             continue
         breakdown[name] = {"ms": round(ms, 3), "launches": cnt, "jobs": jb}
         if name in work and jb and ms > 0:
-            units = jb * work[name]["modmuls"]
-            kernel_rooflines[name] = {"bound": "int", "unit": "Gmodmul/s", "achieved": units / (ms * 1e-3) / 1e9, "peak": pk.value / 1e9,
+            units = jb * work[name]["butterfly_equivalents"]
+            kernel_rooflines[name] = {"bound": "int", "unit": "Gbutterfly-equivalent/s", "achieved": units / (ms * 1e-3) / 1e9, "peak": pk.value / 1e9,
                                       "frac": units / (ms * 1e-3) / pk.value, "modmuls_per_job": work[name]["modmuls"],
+                                      "butterfly_equivalents_per_job": work[name]["butterfly_equivalents"],
                                       "butterflies_per_job": work[name]["butterflies"], "jobs": jb, "ms": round(ms, 3),
                                       "share_of_step": ms / ms_per_step, "ncu_fmaheavy_pct": NCU_FMAHEAVY.get(name)}
     _capi.check(lib.lmn_profile_enable(be.ctx, 0))

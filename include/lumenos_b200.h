@@ -338,8 +338,12 @@ int lmn_profile_enable(lmn_ctx *ctx, uint32_t mask);
 int lmn_profile_read(lmn_ctx *ctx, int kernel_id, double *ms, uint64_t *launches, uint64_t *jobs, int reset);
 int lmn_kernel_count(void);
 const char *lmn_kernel_name(int kernel_id);
-/* measured ceiling of the NTT butterfly instruction mix on the integer pipes (register-resident, all SMs) */
+/* measured ceiling of the NTT butterfly on the integer pipes: the fastest formulation found on this part (3-product Shoup quotient,
+ * middle sum folded into IMAD.WIDE's 64-bit addend, plain adds, lazy [0, 3q); tools/int_pipe_probe.cu k_bfly<1>), register-resident,
+ * 64 warps per SM, nothing else in the loop */
 int lmn_bench_int_peak(lmn_ctx *ctx, double *butterflies_per_s);
+/* the same network with the butterfly the block kernels are built with (ntt_blk.cuh bfly_ct3), for comparison with the ceiling */
+int lmn_bench_product_butterfly(lmn_ctx *ctx, double *butterflies_per_s);
 
 #ifdef __cplusplus
 }

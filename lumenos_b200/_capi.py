@@ -66,6 +66,7 @@ SIGNATURES = {
     "lmn_kernel_count": (C.c_int, []),
     "lmn_kernel_name": (C.c_char_p, [C.c_int]),
     "lmn_bench_int_peak": (C.c_int, [vp, C.POINTER(C.c_double)]),
+    "lmn_bench_product_butterfly": (C.c_int, [vp, C.POINTER(C.c_double)]),
     "lmn_comm_unique_id": (C.c_int, [C.c_char_p]),
     "lmn_comm_init": (C.c_int, [vp, C.c_char_p, C.c_int, C.c_int]),
     "lmn_comm_destroy": (C.c_int, [vp]),

@@ -669,6 +669,16 @@ int lmn_bench_int_peak(lmn_ctx *c, double *butterflies_per_s) {
     return 0;
 }
 
+int lmn_bench_product_butterfly(lmn_ctx *c, double *butterflies_per_s) {
+    if (!c || !butterflies_per_s) return fail(LMN_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> g(c->mu);
+    cudaSetDevice(c->device);
+    int sms = 0; CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
+    *butterflies_per_s = measure_peak_butterflies(c->stream, c->d_mods, sms, 1);
+    CK(cudaGetLastError());
+    return 0;
+}
+
 // ---------------- keys ----------------
 int lmn_load_galois_key(lmn_ctx *c, uint64_t gal_el, const uint64_t *evk) {
     if (!c || !evk) return fail(LMN_ERR_INVALID, "null argument");

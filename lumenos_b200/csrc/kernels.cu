@@ -836,9 +836,12 @@ void launch_ring_decimate(const Launch &L, const DeviceTables &T, const KsJobs &
 }
 
 // =====================================================================================================
-// integer-pipe ceiling: the radix-8 butterfly network of the block transforms (ntt_blk.cuh: bfly_ct3, the 3-product Shoup butterfly
-// every NTT kernel of the product uses) on register-resident data (no loads, no barriers), all SMs busy.  Denominator of the
-// integer roofline of the NTT-bound kernels.
+// integer-pipe ceiling: the radix-8 butterfly network of the block transforms on register-resident data (no loads, no barriers), 64
+// warps per SM, in the FASTEST formulation measured on this part - tools/int_pipe_probe.cu k_bfly<1>: 3-product Shoup quotient with
+// the middle sum as the 64-bit addend of IMAD.WIDE, plain 64-bit add and subtract, lazy [0, 3q) - and with nothing else in the loop
+// (values wrap mod 2^64 after a few rounds; the instruction stream, which is what is timed, does not depend on them).  This is the
+// denominator of the integer roofline; the product's own butterfly (bfly_ct3, ALU-pinned carries) is timed beside it.
+template <int PRODUCT>
 __global__ void __launch_bounds__(256) k_peak_bfly(const ModDev *mods, int rounds, u64 *sink) {
     const u64 q = mods[0].q;
     const FwdMod fm = {q, 0 - q, mods[0].q3, (unsigned)mods[0].pad[0]};
@@ -848,29 +851,34 @@ __global__ void __launch_bounds__(256) k_peak_bfly(const ModDev *mods, int round
     ulonglong2 w[7];
 #pragma unroll
     for (int r = 0; r < 7; r++) { w[r].x = (mods[0].ninv + r * 977) % q; w[r].y = mods[0].ninvs + r; }
+#define LMN_PB(x, y, tw) do { if (PRODUCT) bfly_ct3(x, y, tw, fm); else bfly_ct3_probe(x, y, tw, fm); } while (0)
     for (int it = 0; it < rounds; it++) {
 #pragma unroll
-        for (int r = 0; r < 4; r++) bfly_ct3(a[r], a[r + 4], w[0], fm);
-        bfly_ct3(a[0], a[2], w[1], fm); bfly_ct3(a[1], a[3], w[1], fm);
-        bfly_ct3(a[4], a[6], w[2], fm); bfly_ct3(a[5], a[7], w[2], fm);
+        for (int r = 0; r < 4; r++) LMN_PB(a[r], a[r + 4], w[0]);
+        LMN_PB(a[0], a[2], w[1]); LMN_PB(a[1], a[3], w[1]);
+        LMN_PB(a[4], a[6], w[2]); LMN_PB(a[5], a[7], w[2]);
 #pragma unroll
-        for (int r = 0; r < 4; r++) bfly_ct3(a[2 * r], a[2 * r + 1], w[3 + r], fm);
-#pragma unroll
-        for (int r = 0; r < 8; r++) a[r] = csub(a[r] >> 6, q);   // keep values bounded (cheap, ALU pipe)
+        for (int r = 0; r < 4; r++) LMN_PB(a[2 * r], a[2 * r + 1], w[3 + r]);
     }
+#undef LMN_PB
     u64 x = 0;
 #pragma unroll
     for (int r = 0; r < 8; r++) x ^= a[r];
     if (x == 0x1234567) sink[0] = x;
 }
-double measure_peak_butterflies(cudaStream_t stream, const ModDev *mods, int sm_count) {
+// product = 0: the ceiling above; 1: the same network with the product's own butterfly
+double measure_peak_butterflies(cudaStream_t stream, const ModDev *mods, int sm_count, int product) {
     u64 *sink = nullptr;
     if (cudaMalloc(&sink, 8) != cudaSuccess) return 0.0;
-    const int rounds = 4096, blocks = sm_count * 8, threads = 256;
+    const int rounds = 4096, blocks = sm_count * 8, threads = 256;      // 64 warps per SM
+    auto launch = [&](int r) {
+        if (product) k_peak_bfly<1><<<blocks, threads, 0, stream>>>(mods, r, sink);
+        else k_peak_bfly<0><<<blocks, threads, 0, stream>>>(mods, r, sink);
+    };
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
-    k_peak_bfly<<<blocks, threads, 0, stream>>>(mods, 64, sink);   // warm-up
+    launch(64);   // warm-up
     cudaEventRecord(e0, stream);
-    k_peak_bfly<<<blocks, threads, 0, stream>>>(mods, rounds, sink);
+    launch(rounds);
     cudaEventRecord(e1, stream);
     cudaEventSynchronize(e1);
     float ms = 0; cudaEventElapsedTime(&ms, e0, e1);

@@ -111,7 +111,7 @@ struct LaunchScope {        // RAII: counts the launch and brackets it with even
     ~LaunchScope();
 };
 // peak rate of the NTT butterfly instruction mix on the integer pipes, register-resident (no memory traffic)
-double measure_peak_butterflies(cudaStream_t stream, const ModDev *mods, int sm_count);
+double measure_peak_butterflies(cudaStream_t stream, const ModDev *mods, int sm_count, int product = 0);
 
 // ---- elementwise / operator level ----
 void launch_addsub(const Launch &L, const DeviceTables &T, int level, const u64 *a, const u64 *b, u64 *o, int sub);

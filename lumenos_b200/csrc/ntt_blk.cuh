@@ -69,10 +69,50 @@ __device__ __forceinline__ u64 mul_shoup_approx(u64 y, u64 w, u64 ws, u64 nq, un
         "}" : "=l"(r) : "l"(y), "l"(w), "l"(ws), "l"(nq), "r"(z));
     return r;
 }
+// The same lazy product in the formulation of tools/int_pipe_probe.cu (k_bfly<1>): the sum of the two middle products rides into the
+// high product as the 64-bit addend of IMAD.WIDE, and nothing is pinned to the ALU pipe.  5 IMAD.WIDE + 4 IMAD per butterfly; it is
+// the fastest register-resident butterfly measured on this part (1169 Gbutterfly/s) and therefore the ceiling lmn_bench_int_peak
+// reports.  Inside the block kernels it was A/B-tested against the ALU-pinned form above (build with -DLMN_BFLY_MADWIDE and / or
+// -DLMN_BFLY_PLAINADD; results in DESIGN.md section 4).
+__device__ __forceinline__ u64 mul_shoup_approx_mw(u64 y, u64 w, u64 ws, u64 nq) {
+    u64 r;
+    asm("{\n\t"
+        ".reg .u32 yl, yh, wl, wh, sl, sh, nl, nh, alo, ahi, clo, chi, mlo, mhi, mc, hl, hh, tlo, thi;\n\t"
+        ".reg .u64 a, c, ad, hi, t;\n\t"
+        "mov.b64 {yl, yh}, %1;\n\t" "mov.b64 {wl, wh}, %2;\n\t" "mov.b64 {sl, sh}, %3;\n\t" "mov.b64 {nl, nh}, %4;\n\t"
+        "mul.wide.u32 a, yl, sh;\n\t" "mul.wide.u32 c, yh, sl;\n\t"
+        "mov.b64 {alo, ahi}, a;\n\t" "mov.b64 {clo, chi}, c;\n\t"
+        "add.cc.u32 mlo, alo, clo;\n\t" "addc.cc.u32 mhi, ahi, chi;\n\t" "addc.u32 mc, 0, 0;\n\t"
+        "mov.b64 ad, {mhi, mc};\n\t"
+        "mad.wide.u32 hi, yh, sh, ad;\n\t"
+        "mov.b64 {hl, hh}, hi;\n\t"
+        "mul.wide.u32 t, yl, wl;\n\t" "mad.wide.u32 t, hl, nl, t;\n\t"
+        "mov.b64 {tlo, thi}, t;\n\t"
+        "mad.lo.u32 thi, yl, wh, thi;\n\t" "mad.lo.u32 thi, yh, wl, thi;\n\t"
+        "mad.lo.u32 thi, hl, nh, thi;\n\t" "mad.lo.u32 thi, hh, nl, thi;\n\t"
+        "mov.b64 %0, {tlo, thi};\n\t"
+        "}" : "=l"(r) : "l"(y), "l"(w), "l"(ws), "l"(nq));
+    return r;
+}
+#ifdef LMN_BFLY_MADWIDE
+#define LMN_MUL_APPROX(y, w, ws, m) mul_shoup_approx_mw(y, w, ws, (m).nq)
+#else
+#define LMN_MUL_APPROX(y, w, ws, m) mul_shoup_approx(y, w, ws, (m).nq, (m).z)
+#endif
 __device__ __forceinline__ void bfly_ct3(u64 &x, u64 &y, const ulonglong2 w, const FwdMod &m) {
-    const u64 t = mul_shoup_approx(y, w.x, w.y, m.nq, m.z);
+    const u64 t = LMN_MUL_APPROX(y, w.x, w.y, m);
     y = x - t + m.q3;
+#ifdef LMN_BFLY_PLAINADD
+    x = x + t;
+#else
     x = add64_alu(x, t, m.z);
+#endif
+}
+// the probe's butterfly, whatever the build flags say (k_peak_bfly)
+__device__ __forceinline__ void bfly_ct3_probe(u64 &x, u64 &y, const ulonglong2 w, const FwdMod &m) {
+    const u64 t = mul_shoup_approx_mw(y, w.x, w.y, m.nq);
+    y = x - t + m.q3;
+    x = x + t;
 }
 
 constexpr int RA_THREADS = 256;
@@ -160,7 +200,7 @@ __device__ __forceinline__ void bfly_gs3(u64 &x, u64 &y, const ulonglong2 w, con
     const u64 s = x + y;
     const u64 d = x - y + q4;
     x = s >= q4 ? s - q4 : s;
-    y = mul_shoup_approx(d, w.x, w.y, m.nq, m.z);
+    y = LMN_MUL_APPROX(d, w.x, w.y, m);
 }
 template <class F>
 __device__ __forceinline__ void r8_inv_f(u64 (&a)[8], F tw_of, const FwdMod &m, u64 q4) {

@@ -108,6 +108,15 @@ int lmn_store_download(const lmn_store *s, uint32_t first, uint32_t count, uint6
 /* per-limb copies: Go's Coeffs is [][]uint64 (one slice per limb), and cgo may not pass pointer-to-pointer */
 int lmn_store_upload_limb(lmn_store *s, uint32_t ct, uint32_t poly, uint32_t limb, const uint64_t *host);
 int lmn_store_download_limb(const lmn_store *s, uint32_t ct, uint32_t poly, uint32_t limb, uint64_t *host);
+/* The same for MANY limbs in one call - the form a Lattigo host uses for whole stores (rlwe.Ciphertext.Value[p].Coeffs[limb] is one
+ * slice per limb: core/utils.go:12-33, vdec/prover.go:110-149).  limb_ptrs is a table in C memory with count * 2 * (level+1)
+ * entries in store order, limb_ptrs[((ct - first) * 2 + poly) * (level+1) + limb] -> N uint64 (pageable or pinned; a Go caller pins
+ * the slices with runtime.Pinner for the duration of the call).  The limbs are packed into / unpacked from two
+ * alternating 32 MiB pinned buffers by up to 8 host threads while the other buffer's one cudaMemcpyAsync runs on the context's copy
+ * stream: no synchronisation per limb.  upload: the caller's memory is free when the call returns, the data is visible to work queued
+ * on the context afterwards.  download: waits for the work already queued on the context and returns with the data in place. */
+int lmn_store_upload_limbs(lmn_store *s, uint32_t first, uint32_t count, const uint64_t *const *limb_ptrs);
+int lmn_store_download_limbs(const lmn_store *s, uint32_t first, uint32_t count, uint64_t *const *limb_ptrs);
 /* pinned host staging owned by the library (cudaHostAlloc) */
 int lmn_host_alloc(size_t bytes, void **out);
 void lmn_host_free(void *p);

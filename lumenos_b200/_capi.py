@@ -47,6 +47,8 @@ SIGNATURES = {
     "lmn_store_bytes": (C.c_size_t, [vp]),
     "lmn_store_upload": (C.c_int, [vp, C.c_uint32, C.c_uint32, vp]),
     "lmn_store_download": (C.c_int, [vp, C.c_uint32, C.c_uint32, vp]),
+    "lmn_store_upload_limbs": (C.c_int, [vp, C.c_uint32, C.c_uint32, vp]),
+    "lmn_store_download_limbs": (C.c_int, [vp, C.c_uint32, C.c_uint32, vp]),
     "lmn_store_upload_limb": (C.c_int, [vp, C.c_uint32, C.c_uint32, C.c_uint32, vp]),
     "lmn_store_download_limb": (C.c_int, [vp, C.c_uint32, C.c_uint32, C.c_uint32, vp]),
     "lmn_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(vp)]),

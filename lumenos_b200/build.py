@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.environ.get("LUMENOS_B200_SO") or os.path.join(HERE, "liblumenos_b200.so")   # override: A/B builds of tuning variants
-SOURCES = ["api.cu", "api_client.cu", "api_comm.cu", "api_static.cu", "kernels_comm.cu", "kernels.cu", "kernels_blk.cu", "kernels_mac.cu", "kernels_commit.cu", "kernels_client.cu", "plan.cpp"]
+SOURCES = ["api.cu", "api_client.cu", "api_comm.cu", "api_static.cu", "api_limbs.cu", "kernels_comm.cu", "kernels.cu", "kernels_blk.cu", "kernels_mac.cu", "kernels_commit.cu", "kernels_client.cu", "plan.cpp"]
 HEADERS = ["device.cuh", "ntt_blk.cuh", "tma.cuh", "kernels.cuh", "commit.cuh", "client.cuh", "comm.cuh", "api_internal.hpp", "plan.hpp", "hostmath.hpp", os.path.join("..", "..", "include", "lumenos_b200.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--fmad=false",

@@ -156,6 +156,7 @@ int stage_begin(lmn_ctx *c, size_t total) {
     if (!c->stage_ev) CK(cudaEventCreateWithFlags(&c->stage_ev, cudaEventDisableTiming));
     if (c->h_stage_cap < total) {
         if (c->h_stage) cudaFreeHost(c->h_stage);
+    if (c->limb_stage && c->limb_stage_free) c->limb_stage_free(c->limb_stage);
         c->h_stage = nullptr; c->h_stage_cap = 0;
         CK(cudaHostAlloc((void **)&c->h_stage, total, cudaHostAllocDefault));
         c->h_stage_cap = total;

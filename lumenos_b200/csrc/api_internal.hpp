@@ -71,6 +71,7 @@ struct lmn_ctx {
     u64 *ws_ser = nullptr; size_t ws_ser_cap = 0;           // serialised leaves of the Merkle build (pooled: no allocation per Commit)
     ulonglong2 *ws_scalar = nullptr;
     uint32_t ws_jobs = 0;
+    void *limb_stage = nullptr; void (*limb_stage_free)(void *) = nullptr;   // pinned staging of lmn_store_upload_limbs / download_limbs (api_limbs.cu)
     uint64_t launches = 0;
     Profiler prof;
     std::mutex mu;

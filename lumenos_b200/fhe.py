@@ -121,6 +121,34 @@ class CiphertextStore:
         data = _u64(data)
         check(_capi.lib().lmn_store_upload_limb(self.h, ct, poly, limb, _ptr(data)))
 
+    @staticmethod
+    def limb_table(limbs):
+        """C pointer table over a sequence of per-limb uint64 arrays in store order (ct, poly, limb): what a Go host builds from
+        ct.Value[p].Coeffs[l] (core/utils.go:12-33) after pinning the slices"""
+        tab = (C.c_void_p * len(limbs))()
+        for i, a in enumerate(limbs):
+            if a.dtype != np.uint64 or not a.flags.c_contiguous:
+                raise ValueError("every limb must be a contiguous uint64 array")
+            tab[i] = a.ctypes.data
+        return tab
+
+    def upload_limbs(self, limbs, first=0, count=None, table=None):
+        """limbs: count * 2 * (level+1) separate arrays of N uint64 (any host memory) -> ciphertexts [first, first + count)"""
+        count = self.count - first if count is None else count
+        table = self.limb_table(limbs) if table is None else table
+        if len(table) != count * 2 * (self.level + 1):
+            raise ValueError("the table needs count * 2 * (level + 1) limbs")
+        check(_capi.lib().lmn_store_upload_limbs(self.h, first, count, table))
+        return self
+
+    def download_limbs(self, limbs, first=0, count=None, table=None):
+        count = self.count - first if count is None else count
+        table = self.limb_table(limbs) if table is None else table
+        if len(table) != count * 2 * (self.level + 1):
+            raise ValueError("the table needs count * 2 * (level + 1) limbs")
+        check(_capi.lib().lmn_store_download_limbs(self.h, first, count, table))
+        return limbs
+
     def download(self, first=0, count=None):
         count = self.count - first if count is None else count
         out = np.empty(self.shape(count), np.uint64)

@@ -176,6 +176,51 @@ def test_commit_prove_bit_exact(logN, rows, cols, k, batch):
     be.Close()
 
 
+@pytest.mark.parametrize("logN,k,n_ct", [(6, 4, 7), (12, 3, 5), (14, 12, 24)])
+def test_limb_table_upload_download_roundtrip(logN, k, n_ct):
+    """lmn_store_upload_limbs / lmn_store_download_limbs: the host holds one separately allocated slice per limb (Lattigo's
+    Coeffs[limb], core/utils.go:12-33); the batched calls must move exactly the bytes the per-limb and the contiguous calls move,
+    for ranges inside the store, for chunks smaller and larger than the 32 MiB staging buffer (24 cts at D = 72 MiB), back to back"""
+    from lumenos_b200 import fhe
+    S = scenario(6, 32, 16, 4) if logN == 6 else None
+    if S is None:
+        from lumenos_b200 import hostutil as H
+        q, p = H.generate_moduli(logN, k)
+        params = fhe.BGVParameters(logN, q, p, T, [H.psi_of(m, logN) for m in q], [H.psi_of(m, logN) for m in p])
+        be = fhe.ServerBFV(fhe.PrimeField(T, H.field_roots_forward(16, T)), params)
+    else:
+        be = S.backend()
+    N, L = 1 << logN, k - 1
+    rng = np.random.default_rng(logN)
+    st = be.NewStore(n_ct + 2, L)
+    base = rng.integers(0, 2**60, size=(n_ct + 2, 2, k, N), dtype=np.uint64)
+    st.upload(base)
+    # separately allocated limbs, not adjacent in memory (a spacer between consecutive allocations)
+    limbs, spacers = [], []
+    for _ in range(n_ct * 2 * k):
+        limbs.append(rng.integers(0, 2**50, size=N, dtype=np.uint64))
+        spacers.append(np.empty(257, np.uint8))
+    st.upload_limbs(limbs, first=1, count=n_ct)
+    want = base.copy()
+    want[1:1 + n_ct] = np.stack(limbs).reshape(n_ct, 2, k, N)
+    assert_same(st.download(), want, "store after the batched limb upload")
+    assert_same(st.download_limb(1, 1, k - 1), limbs[2 * k - 1], "one limb through the per-limb call")
+    # a kernel queued after the upload sees the data (stream order, no host synchronisation in between)
+    st.upload_limbs(limbs[::-1], first=1, count=n_ct)
+    be.Add((st, 1), (st, 1), (st, 0))                                     # st[0] = st[1] + st[1]: values below 2^50, so no reduction happens
+    out = [np.zeros(N, np.uint64) for _ in range((n_ct + 2) * 2 * k)]
+    st.download_limbs(out)
+    want[1:1 + n_ct] = np.stack(limbs[::-1]).reshape(n_ct, 2, k, N)
+    got = np.stack(out).reshape(n_ct + 2, 2, k, N)
+    assert_same(got[1:], want[1:], "batched limb download")
+    assert_same(got[0], want[1] * np.uint64(2), "a kernel queued behind the upload read the uploaded limbs")
+    with pytest.raises(fhe.LumenosError, match="out of bounds"):
+        st.upload_limbs(limbs, first=3, count=n_ct)
+    with pytest.raises(ValueError):
+        st.upload_limbs(limbs[:-1], first=1, count=n_ct)
+    be.Close()
+
+
 def test_trim_releases_the_pools_and_results_do_not_change():
     """lmn_ctx_trim: a context that has committed and proved holds its batch workspaces and the serialised leaves; trimming returns
     them to the driver (free device memory grows by what the call reports), and the next Commit / Prove regrows them and produces
